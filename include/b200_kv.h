@@ -1,0 +1,203 @@
+/*
+ * b200_kv.h -- C ABI of libb200kv.so: the B200 (sm_100a) paged-KV-cache hot path.
+ *
+ * Every entry point takes plain device/host pointers, sizes, strides and enums; there are no
+ * torch (or any C++) types in any signature.  Each function replaces one op of the reference's
+ * `vllm._C` extension (or of its MSCCL++ KV-transfer layer); the reference interface it replaces
+ * is cited as file:line relative to the reference tree.  The reference-facing Python binding
+ * (`vllm_splitwise_b200._C`) is a thin ctypes layer over exactly these symbols; see
+ * INTEGRATION.md for the stub a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - all strides are in ELEMENTS of the tensor they describe (as torch's .stride()).
+ *   - `stream` is a cudaStream_t passed as an opaque pointer (NULL = legacy default stream).
+ *   - every function returns B200_OK (0) or a negative b200_status_t; nothing throws.
+ *     No launch is followed by a device sync -- asynchronous faults surface at the caller's next
+ *     sync, exactly as in the reference (csrc/attention/attention_kernels.cu has no post-launch
+ *     check either).
+ *   - functions never allocate device memory and never synchronise, so the attention and
+ *     reshape_and_cache entry points are CUDA-graph capturable (reference: decode is captured,
+ *     vllm/worker/model_runner.py:826-834).
+ */
+#ifndef B200_KV_H_
+#define B200_KV_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_KV_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define B200_API __attribute__((visibility("default")))
+#else
+#define B200_API
+#endif
+
+typedef void* b200_stream_t; /* cudaStream_t */
+
+typedef enum {
+  B200_OK = 0,
+  B200_ERR_HEAD_SIZE = -1,  /* reference: TORCH_CHECK "Unsupported head size"  attention_kernels.cu:674 */
+  B200_ERR_BLOCK_SIZE = -2, /* reference: TORCH_CHECK "Unsupported block size" attention_kernels.cu:706 */
+  B200_ERR_DTYPE = -3,      /* reference: TORCH_CHECK "Unsupported data type"  attention_kernels.cu:732,745 */
+  B200_ERR_ARG = -4,        /* null pointer / negative size / inconsistent head counts */
+  B200_ERR_ALIGN = -5,      /* cache chunk not 16-byte aligned (bulk-copy requirement) */
+  B200_ERR_CUDA = -6,       /* a CUDA runtime call failed; see b200_kv_last_cuda_error() */
+  B200_ERR_DEVICE = -7,     /* swap_blocks: src and dst on different GPUs (cache_kernels.cu:28-32) */
+  B200_ERR_TIMEOUT = -8     /* kv wait: bounded spin expired (kv_comm_kernels.cu:7) */
+} b200_status_t;
+
+typedef enum {
+  B200_F32 = 0,
+  B200_F16 = 1,
+  B200_BF16 = 2,
+  B200_U8_E5M2 = 3 /* uint8 storage holding fp8 e5m2, unscaled (kv_cache_dtype == "fp8_e5m2") */
+} b200_dtype_t;
+
+B200_API const char* b200_kv_strerror(int status);
+B200_API const char* b200_kv_last_cuda_error(void);
+B200_API int b200_kv_abi_version(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Paged attention decode.
+ * Replaces: paged_attention_v1 (csrc/ops.h:5-17, csrc/attention/attention_kernels.cu:711-747)
+ *           paged_attention_v2 (csrc/ops.h:19-34, csrc/attention/attention_kernels.cu:901-940)
+ *
+ *   out[s,h,:] = softmax_t( scale * q[s,h,:].K[t,:] + alibi[h]*(t - ctx_s + 1) ) . V[t,:]
+ *   for t < context_lens[s], kv head = h / (num_heads / num_kv_heads).
+ *
+ * Layouts (reference vllm/worker/cache_engine.py:60-75):
+ *   query        [num_seqs, num_heads, head_size]            T, row stride q_stride
+ *   key_cache    [num_blocks, num_kv_heads, head_size/x, block_size, x]   x = 16/sizeof(cache elt)
+ *   value_cache  [num_blocks, num_kv_heads, head_size, block_size]
+ *   block_tables int32 [num_seqs, max_num_blocks_per_seq], context_lens int32 [num_seqs]
+ *   out          [num_seqs, num_heads, head_size] T, dense
+ * v2 only (caller-allocated scratch, reference paged_attn.py:83-93), P = max_num_partitions:
+ *   tmp_out [num_seqs, num_heads, P, head_size] T; exp_sums, max_logits f32 [num_seqs, num_heads, P]
+ *   partition p covers tokens [512p, 512p+512) exactly as in the reference.
+ * Optional workspace (v1 only): when the (seq, kv_head) grid cannot fill the GPU the library may
+ *   split the context and merge in a second kernel; it needs b200_paged_attention_workspace_bytes()
+ *   bytes of caller-owned scratch.  workspace == NULL disables splitting (never an error).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  void* out;
+  const void* query;
+  const void* key_cache;
+  const void* value_cache;
+  const int32_t* block_tables;
+  const int32_t* context_lens;
+  const float* alibi_slopes; /* [num_heads] f32 or NULL */
+  float scale;
+  int32_t num_seqs;
+  int32_t num_heads;
+  int32_t num_kv_heads;
+  int32_t head_size;  /* 64, 80, 96, 112, 128, 256 */
+  int32_t block_size; /* 8, 16, 32 */
+  int32_t max_context_len;
+  int32_t max_num_blocks_per_seq;
+  int64_t q_stride;
+  int64_t kv_block_stride;
+  int64_t kv_head_stride;
+  int32_t query_dtype; /* b200_dtype_t: F32/F16/BF16 */
+  int32_t cache_dtype; /* == query_dtype ("auto") or B200_U8_E5M2 */
+  /* v2 scratch */
+  float* exp_sums;
+  float* max_logits;
+  void* tmp_out;
+  int32_t max_num_partitions;
+  /* v1 optional scratch */
+  void* workspace;
+  int64_t workspace_bytes;
+  int32_t device; /* CUDA device ordinal the pointers live on, or -1 = current device */
+  int32_t reserved;
+} b200_paged_attn_args_t;
+
+B200_API int b200_paged_attention_v1(const b200_paged_attn_args_t* args, b200_stream_t stream);
+B200_API int b200_paged_attention_v2(const b200_paged_attn_args_t* args, b200_stream_t stream);
+B200_API int64_t b200_paged_attention_workspace_bytes(const b200_paged_attn_args_t* args);
+
+/* ------------------------------------------------------------------------------------------
+ * Cache writes and block moves.
+ * ------------------------------------------------------------------------------------------ */
+
+/* Replaces reshape_and_cache (csrc/cache.h:18-24, csrc/cache_kernels.cu:154-268).
+ * key/value [num_tokens, num_heads, head_size] with row strides key_stride/value_stride;
+ * slot_mapping int64 [num_tokens], negative = padding (skipped). src_dtype F32/F16/BF16;
+ * cache_dtype == src_dtype or U8_E5M2 (saturating RNE convert, quant_utils.cuh:164-192). */
+B200_API int b200_reshape_and_cache(const void* key, const void* value, void* key_cache, void* value_cache,
+                           const int64_t* slot_mapping, int32_t num_tokens, int32_t num_heads,
+                           int32_t head_size, int32_t block_size, int32_t x, int64_t key_stride,
+                           int64_t value_stride, int64_t num_blocks, int32_t src_dtype,
+                           int32_t cache_dtype, b200_stream_t stream);
+
+/* Replaces copy_blocks (csrc/cache.h:13-16, csrc/cache_kernels.cu:65-150).
+ * key_cache_ptrs/value_cache_ptrs: HOST arrays of num_layers device base addresses;
+ * block_pairs: HOST array [num_pairs][2] = (src_block, dst_block); block_bytes = bytes of one
+ * block of one layer's K (== V).  Tables travel as kernel parameters: no H2D copy, no sync
+ * (the reference does a synchronous .to(device), cache_kernels.cu:129-134). */
+B200_API int b200_copy_blocks(const int64_t* key_cache_ptrs, const int64_t* value_cache_ptrs,
+                     int32_t num_layers, const int64_t* block_pairs, int32_t num_pairs,
+                     int64_t block_bytes, b200_stream_t stream);
+
+typedef enum { B200_SWAP_D2D = 0, B200_SWAP_D2H = 1, B200_SWAP_H2D = 2 } b200_swap_kind_t;
+
+/* Replaces swap_blocks (csrc/cache.h:8-11, csrc/cache_kernels.cu:21-60).
+ * block_pairs HOST [num_pairs][2] (src,dst) in the iteration order of the reference's std::map
+ * (ascending src).  D2D: one gather kernel. D2H/H2D: consecutive (src,dst) runs are merged into one
+ * cudaMemcpyAsync each.  src_device/dst_device: CUDA ordinals or -1 for host. */
+B200_API int b200_swap_blocks(const void* src, void* dst, int64_t block_bytes, const int64_t* block_pairs,
+                     int32_t num_pairs, int32_t kind, int32_t src_device, int32_t dst_device,
+                     b200_stream_t stream);
+
+/* Replaces convert_fp8_e5m2 (csrc/cache.h:26-29, csrc/cache_kernels.cu:272-320): elementwise
+ * {F32,F16,BF16} -> U8_E5M2 or back, numel elements. */
+B200_API int b200_convert_fp8_e5m2(const void* src, void* dst, int64_t numel, int32_t src_dtype,
+                          int32_t dst_dtype, b200_stream_t stream);
+
+/* Replaces cuda_utils (csrc/cuda_utils_kernels.cu:5-35). */
+B200_API int b200_get_device_attribute(int32_t attribute, int32_t device_id);
+B200_API int b200_get_max_shared_memory_per_block_device_attribute(int32_t device_id);
+
+/* ------------------------------------------------------------------------------------------
+ * Splitwise prefill -> decode KV-block transfer over NVLink peer memory.
+ * Replaces the MSCCL++ proxy-channel kernels (csrc/kv_comm_kernels.cu:3-29) and the calls the
+ * reference makes on them (vllm/worker/comm_utils.py:117-147): put / signal+flush / wait.
+ * There is no host proxy: the prompt GPU's kernel stores straight into the token GPU's cache.
+ * ------------------------------------------------------------------------------------------ */
+#define B200_IPC_HANDLE_BYTES 64
+
+/* Export dev_ptr's allocation for another process; offset = dev_ptr - allocation base. */
+B200_API int b200_kv_ipc_export(const void* dev_ptr, unsigned char handle[B200_IPC_HANDLE_BYTES],
+                       int64_t* offset, int64_t* alloc_bytes);
+B200_API int b200_kv_ipc_open(const unsigned char handle[B200_IPC_HANDLE_BYTES], void** base);
+B200_API int b200_kv_ipc_close(void* base);
+/* Same-process multi-GPU: enable dev -> peer access (idempotent). */
+B200_API int b200_kv_enable_peer_access(int32_t dev, int32_t peer_dev);
+
+/* Copy block runs of `num_bufs` buffers to the same byte offsets in their peer-mapped twins.
+ * src_ptrs/dst_ptrs: DEVICE int64 arrays of device addresses (dst = peer mapping), one per buffer
+ * (layer x {K,V}), built once at setup; runs: HOST [num_runs][2] = (block_start, num_blocks) as produced by the
+ * reference's coalesce_blocks (vllm/utils.py:403-426).  One launch, max_ctas CTAs (0 = default).
+ * Replaces nw_cache_out_kernel's put (kv_comm_kernels.cu:11-20); offsets are 64-bit. */
+B200_API int b200_kv_put_blocks(const int64_t* src_ptrs, const int64_t* dst_ptrs, int32_t num_bufs,
+                       const int32_t* runs, int32_t num_runs, int64_t block_bytes,
+                       int32_t max_ctas, b200_stream_t stream);
+
+/* After all prior work on `stream`: system-scope release store of `value` to *remote_flag (a
+ * peer-mapped uint64).  Replaces nw_cache_out_signal_kernel (kv_comm_kernels.cu:22-29). */
+B200_API int b200_kv_signal(uint64_t* remote_flag, uint64_t value, b200_stream_t stream);
+
+/* Enqueue a one-warp kernel that acquire-spins until *local_flag >= value or max_spins polls
+ * passed; on expiry it sets *timeout_flag (device int32, may be NULL) to 1 and returns.
+ * Replaces nw_cache_in_kernel (kv_comm_kernels.cu:3-9). */
+B200_API int b200_kv_wait(const uint64_t* local_flag, uint64_t value, int64_t max_spins,
+                 int32_t* timeout_flag, b200_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_KV_H_ */

@@ -1,0 +1,53 @@
+// TEST INFRASTRUCTURE ONLY -- not part of the product path.
+//
+// Minimal pybind11 front for the *unmodified* reference CUDA kernels so that the GPU parity
+// tests and bench.py can run the reference's own paged_attention / cache ops next to ours on
+// identical inputs.  The kernels themselves are compiled straight from
+// /root/reference/csrc/{attention/attention_kernels.cu,cache_kernels.cu,cuda_utils_kernels.cu}
+// by oracle/build_ref.sh; nothing from the reference is copied into this repository.  The
+// prototypes below restate csrc/ops.h:5-34, csrc/cache.h:8-29 and csrc/cuda_utils.h.
+#include <torch/extension.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+void paged_attention_v1(torch::Tensor& out, torch::Tensor& query, torch::Tensor& key_cache,
+                        torch::Tensor& value_cache, int num_kv_heads, float scale,
+                        torch::Tensor& block_tables, torch::Tensor& context_lens, int block_size,
+                        int max_context_len, const c10::optional<torch::Tensor>& alibi_slopes,
+                        const std::string& kv_cache_dtype);
+
+void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tensor& max_logits,
+                        torch::Tensor& tmp_out, torch::Tensor& query, torch::Tensor& key_cache,
+                        torch::Tensor& value_cache, int num_kv_heads, float scale,
+                        torch::Tensor& block_tables, torch::Tensor& context_lens, int block_size,
+                        int max_context_len, const c10::optional<torch::Tensor>& alibi_slopes,
+                        const std::string& kv_cache_dtype);
+
+void swap_blocks(torch::Tensor& src, torch::Tensor& dst,
+                 const std::map<int64_t, int64_t>& block_mapping);
+void copy_blocks(std::vector<torch::Tensor>& key_caches, std::vector<torch::Tensor>& value_caches,
+                 const std::map<int64_t, std::vector<int64_t>>& block_mapping);
+void reshape_and_cache(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache,
+                       torch::Tensor& value_cache, torch::Tensor& slot_mapping,
+                       const std::string& kv_cache_dtype);
+void convert_fp8_e5m2(torch::Tensor& src_cache, torch::Tensor& dst_cache);
+
+int get_device_attribute(int attribute, int device_id);
+int get_max_shared_memory_per_block_device_attribute(int device_id);
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  pybind11::module ops = m.def_submodule("ops");
+  ops.def("paged_attention_v1", &paged_attention_v1);
+  ops.def("paged_attention_v2", &paged_attention_v2);
+  pybind11::module cache_ops = m.def_submodule("cache_ops");
+  cache_ops.def("swap_blocks", &swap_blocks);
+  cache_ops.def("copy_blocks", &copy_blocks);
+  cache_ops.def("reshape_and_cache", &reshape_and_cache);
+  cache_ops.def("convert_fp8_e5m2", &convert_fp8_e5m2);
+  pybind11::module cuda_utils = m.def_submodule("cuda_utils");
+  cuda_utils.def("get_device_attribute", &get_device_attribute);
+  cuda_utils.def("get_max_shared_memory_per_block_device_attribute",
+                 &get_max_shared_memory_per_block_device_attribute);
+}

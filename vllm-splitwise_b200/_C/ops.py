@@ -1,0 +1,122 @@
+"""vllm._C.ops on the hot path: paged_attention_v1 / paged_attention_v2.
+
+Positional signatures are the reference's (csrc/ops.h:5-34); all tensors are caller-allocated,
+ops write in place and return None, launches go to torch's current stream.
+"""
+import ctypes
+from typing import Optional
+
+import torch
+
+from .. import _lib
+from ._common import device_ctx, dtype_code, require_cuda, stream_ptr
+
+_workspaces = {}  # device index -> uint8 tensor (scratch for the internal split of v1 calls)
+_WORKSPACE_CAP = 512 << 20
+
+
+def _cache_dtype_code(kv_cache_dtype: str, query: torch.Tensor, cache: torch.Tensor) -> int:
+    if kv_cache_dtype == "auto":
+        if cache.dtype != query.dtype:
+            raise RuntimeError(f"Unsupported data type: cache {cache.dtype} with query {query.dtype}")
+        return dtype_code(query, "query")
+    if kv_cache_dtype == "fp8_e5m2":
+        if cache.dtype != torch.uint8:
+            raise RuntimeError(f"Unsupported data type: fp8_e5m2 cache must be uint8, got {cache.dtype}")
+        return _lib.U8_E5M2
+    raise RuntimeError(f"Unsupported data type of kv cache: {kv_cache_dtype}")
+
+
+def _fill_args(out, query, key_cache, value_cache, num_kv_heads, scale, block_tables, context_lens,
+               block_size, max_context_len, alibi_slopes, kv_cache_dtype) -> _lib.PagedAttnArgs:
+    for name, t in (("out", out), ("query", query), ("key_cache", key_cache),
+                    ("value_cache", value_cache), ("block_tables", block_tables),
+                    ("context_lens", context_lens)):
+        require_cuda(t, name)
+    if block_tables.dtype != torch.int32 or context_lens.dtype != torch.int32:
+        raise RuntimeError("block_tables and context_lens must be int32")
+    if query.stride(-1) != 1 or query.stride(1) != query.size(2) or not out.is_contiguous():
+        raise RuntimeError("query must be dense in its last two dims and out contiguous")
+    a = _lib.PagedAttnArgs()
+    a.out = out.data_ptr()
+    a.query = query.data_ptr()
+    a.key_cache = key_cache.data_ptr()
+    a.value_cache = value_cache.data_ptr()
+    a.block_tables = block_tables.data_ptr()
+    a.context_lens = context_lens.data_ptr()
+    if alibi_slopes is not None:
+        if alibi_slopes.dtype != torch.float32:
+            raise RuntimeError("alibi_slopes must be float32")
+        a.alibi_slopes = alibi_slopes.data_ptr()
+    a.scale = float(scale)
+    a.num_seqs, a.num_heads, a.head_size = query.size(0), query.size(1), query.size(2)
+    a.num_kv_heads = int(num_kv_heads)
+    a.block_size = int(block_size)
+    a.max_context_len = int(max_context_len)
+    a.max_num_blocks_per_seq = block_tables.size(1)
+    a.q_stride = query.stride(0)
+    a.kv_block_stride = key_cache.stride(0)
+    a.kv_head_stride = key_cache.stride(1)
+    a.query_dtype = dtype_code(query, "query")
+    a.cache_dtype = _cache_dtype_code(kv_cache_dtype, query, key_cache)
+    a.device = query.device.index if query.device.index is not None else -1
+    return a
+
+
+def _detail(a: _lib.PagedAttnArgs, status: int):
+    if status == _lib.ERR_HEAD_SIZE:
+        return a.head_size
+    if status == _lib.ERR_BLOCK_SIZE:
+        return a.block_size
+    return ""
+
+
+def _workspace_for(a: _lib.PagedAttnArgs, device: torch.device) -> Optional[torch.Tensor]:
+    need = min(_lib.load().b200_paged_attention_workspace_bytes(ctypes.byref(a)), _WORKSPACE_CAP)
+    ws = _workspaces.get(device.index)
+    if ws is None or ws.numel() < need:
+        if torch.cuda.is_current_stream_capturing():
+            return ws  # never allocate inside a CUDA-graph capture; use what exists (or none)
+        ws = torch.empty(need, dtype=torch.uint8, device=device)
+        _workspaces[device.index] = ws
+    return ws
+
+
+def paged_attention_v1(out: torch.Tensor, query: torch.Tensor, key_cache: torch.Tensor,
+                       value_cache: torch.Tensor, num_kv_heads: int, scale: float,
+                       block_tables: torch.Tensor, context_lens: torch.Tensor, block_size: int,
+                       max_context_len: int, alibi_slopes: Optional[torch.Tensor],
+                       kv_cache_dtype: str) -> None:
+    a = _fill_args(out, query, key_cache, value_cache, num_kv_heads, scale, block_tables,
+                   context_lens, block_size, max_context_len, alibi_slopes, kv_cache_dtype)
+    # A small (seq, kv_head) grid cannot fill 148 SMs: give the library scratch so it may split
+    # the context internally.  Large grids never use it, so skip the bookkeeping.
+    if a.num_seqs * a.num_kv_heads < 592 and a.max_context_len >= 512:
+        ws = _workspace_for(a, query.device)
+        if ws is not None:
+            a.workspace = ws.data_ptr()
+            a.workspace_bytes = ws.numel()
+    st = _lib.load().b200_paged_attention_v1(ctypes.byref(a), stream_ptr(query.device))
+    _lib.check(st, "paged_attention_v1", _detail(a, st))
+
+
+def paged_attention_v2(out: torch.Tensor, exp_sums: torch.Tensor, max_logits: torch.Tensor,
+                       tmp_out: torch.Tensor, query: torch.Tensor, key_cache: torch.Tensor,
+                       value_cache: torch.Tensor, num_kv_heads: int, scale: float,
+                       block_tables: torch.Tensor, context_lens: torch.Tensor, block_size: int,
+                       max_context_len: int, alibi_slopes: Optional[torch.Tensor],
+                       kv_cache_dtype: str) -> None:
+    a = _fill_args(out, query, key_cache, value_cache, num_kv_heads, scale, block_tables,
+                   context_lens, block_size, max_context_len, alibi_slopes, kv_cache_dtype)
+    if exp_sums.dtype != torch.float32 or max_logits.dtype != torch.float32:
+        raise RuntimeError("exp_sums and max_logits must be float32")
+    if tmp_out.dtype != query.dtype:
+        raise RuntimeError("tmp_out must have the query dtype")
+    if not (exp_sums.is_contiguous() and max_logits.is_contiguous() and tmp_out.is_contiguous()):
+        raise RuntimeError("v2 scratch tensors must be contiguous")
+    a.exp_sums = exp_sums.data_ptr()
+    a.max_logits = max_logits.data_ptr()
+    a.tmp_out = tmp_out.data_ptr()
+    a.max_num_partitions = exp_sums.size(2)
+    st = _lib.load().b200_paged_attention_v2(ctypes.byref(a), stream_ptr(query.device))
+    _lib.check(st, "paged_attention_v2", _detail(a, st))

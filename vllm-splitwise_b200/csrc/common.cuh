@@ -1,0 +1,235 @@
+// Shared device/host helpers for libb200kv (sm_100a only).
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_fp8.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/b200_kv.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libb200kv is written for sm_100a (B200) only"
+#endif
+
+namespace b200 {
+
+// ---- host-side error plumbing -------------------------------------------------------------
+void set_last_cuda_error(cudaError_t e, const char* where);
+
+#define B200_CUDA_TRY(expr)                            \
+  do {                                                 \
+    cudaError_t e__ = (expr);                          \
+    if (e__ != cudaSuccess) {                          \
+      ::b200::set_last_cuda_error(e__, #expr);         \
+      return B200_ERR_CUDA;                            \
+    }                                                  \
+  } while (0)
+
+#define B200_LAUNCH_CHECK()                            \
+  do {                                                 \
+    cudaError_t e__ = cudaPeekAtLastError();           \
+    if (e__ != cudaSuccess) {                          \
+      ::b200::set_last_cuda_error(e__, "kernel launch"); \
+      (void)cudaGetLastError();                        \
+      return B200_ERR_CUDA;                            \
+    }                                                  \
+  } while (0)
+
+inline int dtype_size(int dt) {
+  switch (dt) {
+    case B200_F32: return 4;
+    case B200_F16: return 2;
+    case B200_BF16: return 2;
+    case B200_U8_E5M2: return 1;
+    default: return 0;
+  }
+}
+
+// RAII device switch for entry points that carry a device ordinal.
+struct DeviceGuard {
+  int prev = -1;
+  bool active = false;
+  cudaError_t set(int dev) {
+    if (dev < 0) return cudaSuccess;
+    cudaError_t e = cudaGetDevice(&prev);
+    if (e != cudaSuccess) return e;
+    if (prev != dev) {
+      e = cudaSetDevice(dev);
+      active = (e == cudaSuccess);
+    }
+    return e;
+  }
+  ~DeviceGuard() {
+    if (active) (void)cudaSetDevice(prev);
+  }
+};
+
+int num_sms(int device);
+
+// ---- device-side PTX helpers --------------------------------------------------------------
+#ifdef __CUDACC__
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+
+// L2 eviction policy for streamed-once data (KV blocks are read exactly once per decode step).
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+
+// 1-D bulk async copy global -> shared (TMA engine, no tensor map), completion on an mbarrier.
+// SASS: UBLKCP.  Requires 16-byte aligned src/dst and size % 16 == 0.
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes,
+                                         uint64_t* bar, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+      "[%0], [%1], %2, [%3], %4;"
+      ::"r"(smem_u32(smem_dst)),
+      "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(policy)
+      : "memory");
+}
+
+__device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_na_v4(void* p, const uint4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+// ---- element conversions ------------------------------------------------------------------
+// fp8 e5m2 is the high byte of an IEEE half, so widening is a byte permute (exact).
+__device__ __forceinline__ float2 e5m2x2_lo_to_float2(uint32_t w) {  // bytes 0,1
+  uint32_t h2 = __byte_perm(w, 0u, 0x1404);
+  return __half22float2(*reinterpret_cast<const __half2*>(&h2));
+}
+__device__ __forceinline__ float2 e5m2x2_hi_to_float2(uint32_t w) {  // bytes 2,3
+  uint32_t h2 = __byte_perm(w, 0u, 0x3424);
+  return __half22float2(*reinterpret_cast<const __half2*>(&h2));
+}
+__device__ __forceinline__ float2 half2_bits_to_float2(uint32_t w) {
+  return __half22float2(*reinterpret_cast<const __half2*>(&w));
+}
+__device__ __forceinline__ float2 bf162_bits_to_float2(uint32_t w) {
+  return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u));
+}
+
+// Unpack one 16-byte vector of cache elements into floats.  N = 16 / sizeof(CT).
+template <typename CT>
+struct Unpack16;
+template <>
+struct Unpack16<float> {
+  static constexpr int N = 4;
+  __device__ __forceinline__ static void run(const uint4& v, float* f) {
+    f[0] = __uint_as_float(v.x); f[1] = __uint_as_float(v.y);
+    f[2] = __uint_as_float(v.z); f[3] = __uint_as_float(v.w);
+  }
+};
+template <>
+struct Unpack16<__half> {
+  static constexpr int N = 8;
+  __device__ __forceinline__ static void run(const uint4& v, float* f) {
+    float2 a = half2_bits_to_float2(v.x), b = half2_bits_to_float2(v.y);
+    float2 c = half2_bits_to_float2(v.z), d = half2_bits_to_float2(v.w);
+    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+  }
+};
+template <>
+struct Unpack16<__nv_bfloat16> {
+  static constexpr int N = 8;
+  __device__ __forceinline__ static void run(const uint4& v, float* f) {
+    float2 a = bf162_bits_to_float2(v.x), b = bf162_bits_to_float2(v.y);
+    float2 c = bf162_bits_to_float2(v.z), d = bf162_bits_to_float2(v.w);
+    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+  }
+};
+template <>
+struct Unpack16<uint8_t> {  // fp8 e5m2
+  static constexpr int N = 16;
+  __device__ __forceinline__ static void run(const uint4& v, float* f) {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float2 lo = e5m2x2_lo_to_float2(w[i]), hi = e5m2x2_hi_to_float2(w[i]);
+      f[4 * i + 0] = lo.x; f[4 * i + 1] = lo.y; f[4 * i + 2] = hi.x; f[4 * i + 3] = hi.y;
+    }
+  }
+};
+
+template <typename T> __device__ __forceinline__ float to_f32(T v);
+template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
+template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+// Saturating RNE narrow to e5m2 with the SAME intrinsics the reference uses
+// (csrc/quantization/fp8_e5m2_kvcache/quant_utils.cuh:164-192) so results are bit-identical.
+template <typename T> __device__ __forceinline__ uint8_t to_e5m2(T v);
+template <> __device__ __forceinline__ uint8_t to_e5m2<float>(float v) {
+  return (uint8_t)__nv_cvt_float_to_fp8(v, __NV_SATFINITE, __NV_E5M2);
+}
+template <> __device__ __forceinline__ uint8_t to_e5m2<__half>(__half v) {
+  return (uint8_t)__nv_cvt_halfraw_to_fp8(static_cast<__half_raw>(v), __NV_SATFINITE, __NV_E5M2);
+}
+template <> __device__ __forceinline__ uint8_t to_e5m2<__nv_bfloat16>(__nv_bfloat16 v) {
+  return (uint8_t)__nv_cvt_bfloat16raw_to_fp8(static_cast<__nv_bfloat16_raw>(v), __NV_SATFINITE, __NV_E5M2);
+}
+// e5m2 -> T following the reference's widening chain (quant_utils.cuh:23-81):
+// fp8 -> half (intrinsic); bf16 goes half -> float -> bf16; float goes half -> float.
+template <typename T> __device__ __forceinline__ T from_e5m2(uint8_t v);
+template <> __device__ __forceinline__ __half from_e5m2<__half>(uint8_t v) {
+  return __half(__nv_cvt_fp8_to_halfraw(v, __NV_E5M2));
+}
+template <> __device__ __forceinline__ float from_e5m2<float>(uint8_t v) {
+  return __half2float(__half(__nv_cvt_fp8_to_halfraw(v, __NV_E5M2)));
+}
+template <> __device__ __forceinline__ __nv_bfloat16 from_e5m2<__nv_bfloat16>(uint8_t v) {
+  return __float2bfloat16(__half2float(__half(__nv_cvt_fp8_to_halfraw(v, __NV_E5M2))));
+}
+
+#endif  // __CUDACC__
+}  // namespace b200
