@@ -1,0 +1,292 @@
+"""TEST INFRASTRUCTURE ONLY -- the parity oracle (CPU, torch + numpy).
+
+Each function restates, in this repository's own words, the reference algorithm it cites
+(file:line relative to the reference tree).  Pinning (see DESIGN.md "Oracle"):
+  * attention: checked against the reference's own torch functions
+    (tests/kernels/test_attention.py:43-111), AST-extracted from /root/reference by
+    oracle/make_golden.py; their outputs are committed under tests/golden/ and re-checked by
+    tests/test_oracle_golden.py on every CPU run.
+  * coalesce_blocks: same, against vllm/utils.py:403-415.
+  * fp8 e5m2 codec: checked on CPU against torch.float8_e5m2 casts for all 65 536 fp16 inputs
+    (finite, in range) and on the GPU box bit-for-bit against the reference's compiled
+    convert_fp8_e5m2 kernel (oracle/_ref).
+  * cache writes / block copies: the reference states them only as inline loops inside GPU tests
+    (tests/kernels/test_cache.py:85-91,148-158,222-226); restated here and pinned on the GPU box
+    bit-for-bit against the reference's compiled kernels (oracle/_ref).
+  * KV transfer: MSCCL++ (third-party, un-vendored, no pinned version:
+    docs/source/splitwise/installing_mscclpp.rst:11-18) -- semantics are "same bytes at the same
+    block offsets" (csrc/kv_comm_kernels.cu:15); parity for fragmented lists is UNPINNED by any
+    reference test, only the all-blocks constant-fill case is (vllm/worker/worker.py:350-386).
+"""
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+PARTITION_SIZE = 512  # reference paged_attn.py:12, attention_kernels.cu:791
+
+
+# --------------------------------------------------------------------------------------------
+# attention
+# --------------------------------------------------------------------------------------------
+def masked_attention(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, scale: float,
+                     bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """One sequence: query [1,H,D], key/value [T,H,D] -> [1,H,D].
+
+    Follows ref_masked_attention (tests/kernels/test_attention.py:43-55): logits are the
+    dtype-native q.k product scaled and widened to fp32, softmax in fp32, probabilities cast to
+    the value dtype, then a dtype-native P.V product.
+    """
+    logits = (torch.einsum("qhd,khd->hqk", query, key) * scale).float()
+    if bias is not None:
+        logits = logits + bias.float()
+    probs = torch.softmax(logits, dim=-1).to(value.dtype)
+    return torch.einsum("hqk,khd->qhd", probs, value)
+
+
+def _gather_sequence(key_cache: torch.Tensor, value_cache: torch.Tensor, table: Sequence[int],
+                     context_len: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Materialise [T,Hkv,D] keys/values of one sequence from the paged layout
+    (key [NB,Hkv,D/x,bs,x], value [NB,Hkv,D,bs]; vllm/worker/cache_engine.py:60-75)."""
+    nb, hkv, dx, bs, x = key_cache.shape
+    n = (context_len + bs - 1) // bs
+    idx = torch.as_tensor(list(table[:n]), dtype=torch.long)
+    k = key_cache.index_select(0, idx).permute(0, 3, 1, 2, 4).reshape(n * bs, hkv, dx * x)
+    v = value_cache.index_select(0, idx).permute(0, 3, 1, 2).reshape(n * bs, hkv, value_cache.shape[2])
+    return k[:context_len], v[:context_len]
+
+
+def single_query_cached_kv_attention(output: torch.Tensor, query: torch.Tensor,
+                                     num_queries_per_kv: int, key_cache: torch.Tensor,
+                                     value_cache: torch.Tensor, block_tables: torch.Tensor,
+                                     context_lens: torch.Tensor, scale: float,
+                                     alibi_slopes: Optional[torch.Tensor]) -> None:
+    """Decode attention over the paged cache, one sequence at a time, gathers vectorised.
+
+    Restates ref_single_query_cached_kv_attention (tests/kernels/test_attention.py:58-111):
+    token j of sequence i lives in block block_tables[i][j // bs] at offset j % bs; GQA repeats
+    each KV head over its query group; the ALiBi bias is slope_h * (j - context_len + 1).
+    """
+    tables = block_tables.cpu().tolist()
+    lens = context_lens.cpu().tolist()
+    for i in range(query.shape[0]):
+        ctx = int(lens[i])
+        keys, values = _gather_sequence(key_cache, value_cache, tables[i], ctx)
+        if num_queries_per_kv > 1:
+            keys = keys.repeat_interleave(num_queries_per_kv, dim=1)
+            values = values.repeat_interleave(num_queries_per_kv, dim=1)
+        bias = None
+        if alibi_slopes is not None:
+            pos = (torch.arange(ctx).int() - ctx + 1).float()
+            bias = alibi_slopes.view(-1, 1, 1) * pos.view(1, 1, -1)
+        out = masked_attention(query[i:i + 1], keys, values, scale, bias)
+        output[i].copy_(out.view(query.shape[1], query.shape[2]))
+
+
+def single_query_cached_kv_attention_loop(output, query, num_queries_per_kv, key_cache,
+                                          value_cache, block_tables, context_lens, scale,
+                                          alibi_slopes) -> None:
+    """Same result with the reference's literal per-token gather (small cases only); used to show
+    that the vectorised gather above addresses the cache exactly as the reference does."""
+    bs = value_cache.shape[3]
+    hkv, d = value_cache.shape[1], value_cache.shape[2]
+    tables = block_tables.cpu().tolist()
+    lens = context_lens.cpu().tolist()
+    for i in range(query.shape[0]):
+        ctx = int(lens[i])
+        ks, vs = [], []
+        for j in range(ctx):
+            blk, off = int(tables[i][j // bs]), j % bs
+            ks.append(key_cache[blk, :, :, off, :].reshape(hkv, d))
+            vs.append(value_cache[blk, :, :, off])
+        keys, values = torch.stack(ks), torch.stack(vs)
+        if num_queries_per_kv > 1:
+            keys = keys.repeat_interleave(num_queries_per_kv, dim=1)
+            values = values.repeat_interleave(num_queries_per_kv, dim=1)
+        bias = None
+        if alibi_slopes is not None:
+            pos = (torch.arange(ctx).int() - ctx + 1).float()
+            bias = alibi_slopes.view(-1, 1, 1) * pos.view(1, 1, -1)
+        output[i].copy_(masked_attention(query[i:i + 1], keys, values, scale, bias)[0])
+
+
+def attention_fp32(query, num_queries_per_kv, key_cache, value_cache, block_tables, context_lens,
+                   scale, alibi_slopes) -> torch.Tensor:
+    """All-fp32 evaluation of the same formula (inputs widened first): the 'true' value both the
+    reference's torch path and any CUDA kernel approximate; used to judge which one is closer."""
+    out = torch.empty(query.shape, dtype=torch.float32)
+    single_query_cached_kv_attention(out, query.float(), num_queries_per_kv, key_cache.float(),
+                                     value_cache.float(), block_tables, context_lens, scale,
+                                     alibi_slopes)
+    return out
+
+
+def v2_partials(query, num_queries_per_kv, key_cache, value_cache, block_tables, context_lens,
+                scale, alibi_slopes, max_num_partitions: int):
+    """Per-partition state of the reference's paged_attention_v2 in fp32
+    (csrc/attention/attention_kernels.cu:456-476 writing :280-290, 404-416): for partition p over
+    tokens [512p, 512p+512): max_logits = max_t logit_t, exp_sums = sum_t e^(logit_t - max),
+    tmp_out = softmax-weighted V (normalised by exp_sum + 1e-6).  Entries of partitions past the
+    context are left NaN (the kernel does not write them)."""
+    s, h, d = query.shape
+    ml = torch.full((s, h, max_num_partitions), float("nan"))
+    es = torch.full((s, h, max_num_partitions), float("nan"))
+    tmp = torch.full((s, h, max_num_partitions, d), float("nan"))
+    tables = block_tables.cpu().tolist()
+    lens = context_lens.cpu().tolist()
+    qf = query.float()
+    for i in range(s):
+        ctx = int(lens[i])
+        keys, values = _gather_sequence(key_cache.float(), value_cache.float(), tables[i], ctx)
+        keys = keys.repeat_interleave(num_queries_per_kv, dim=1)
+        values = values.repeat_interleave(num_queries_per_kv, dim=1)
+        logits = torch.einsum("hd,khd->hk", qf[i], keys) * scale
+        if alibi_slopes is not None:
+            logits = logits + alibi_slopes.view(-1, 1) * (torch.arange(ctx) - ctx + 1).float().view(1, -1)
+        for p in range((ctx + PARTITION_SIZE - 1) // PARTITION_SIZE):
+            lo, hi = p * PARTITION_SIZE, min(ctx, (p + 1) * PARTITION_SIZE)
+            lg = logits[:, lo:hi]
+            m = lg.max(dim=1).values
+            e = torch.exp(lg - m[:, None])
+            ssum = e.sum(dim=1)
+            ml[i, :, p], es[i, :, p] = m, ssum
+            tmp[i, :, p] = torch.einsum("hk,khd->hd", e, values[lo:hi]) / (ssum + 1e-6)[:, None]
+    return es, ml, tmp
+
+
+# --------------------------------------------------------------------------------------------
+# fp8 e5m2 codec (unscaled)
+# --------------------------------------------------------------------------------------------
+E5M2_MAX_NORM = 0x7B  # 57344
+E5M2_NAN = 0x7F
+
+
+def e5m2_from_float32(x: np.ndarray) -> np.ndarray:
+    """float32 -> e5m2 byte, round-to-nearest-even, saturate-to-finite.
+
+    Restates what `__nv_cvt_float_to_fp8(x, __NV_SATFINITE, __NV_E5M2)` computes -- the intrinsic
+    the reference calls in fp8_e5m2_unscaled::vec_conversion (quant_utils.cuh:164-192): values at
+    or above the max normal (57344), and +-Inf, clamp to 0x7B; |x| <= 2^-17 flushes to zero;
+    results below 2^-14 are subnormals with ulp 2^-16; NaN gives the canonical NaN 0x7F (the
+    sm_89+ `cvt.rn.satfinite.e5m2x2.f32` path; the CUDA header's host emulation would keep two
+    payload bits instead).  The sign bit is carried through in every case.
+    """
+    bits = np.ascontiguousarray(x, dtype=np.float32).view(np.uint32).astype(np.int64)
+    sign = (bits >> 31) << 7
+    a = bits & 0x7FFFFFFF
+    exp = (a >> 23) - 127 + 15          # e5m2-biased exponent
+    man = a & 0x7FFFFF
+    # normal results: keep 2 mantissa bits, 21 dropped
+    res_n = (exp << 2) | (man >> 21)
+    rem_n = man & 0x1FFFFF
+    up_n = (rem_n > 0x100000) | ((rem_n == 0x100000) & ((res_n & 1) == 1))
+    res_n = res_n + up_n
+    # subnormal results (exp <= 0): shift in the implicit one
+    shift = np.clip(1 - exp, 0, 40)
+    full = (man | 0x800000)
+    drop = 21 + shift
+    res_s = full >> drop
+    rem_s = full & ((np.int64(1) << drop) - 1)
+    half_s = np.int64(1) << (drop - 1)
+    up_s = (rem_s > half_s) | ((rem_s == half_s) & ((res_s & 1) == 1))
+    res_s = res_s + up_s
+    res = np.where(exp >= 1, res_n, res_s)
+    res = np.where(res > E5M2_MAX_NORM, E5M2_MAX_NORM, res)          # overflow / Inf -> max finite
+    res = np.where(a <= 0x37000000, 0, res)                          # |x| <= 2^-17 -> 0
+    res = np.where(a > 0x7F800000, E5M2_NAN, res)                    # NaN
+    return (res | sign).astype(np.uint8)
+
+
+def e5m2_from_tensor(t: torch.Tensor) -> torch.Tensor:
+    """fp32/fp16/bf16 tensor -> uint8 e5m2 (widening to fp32 is exact, so one rounding step,
+    as in the half/bf16 specialisations at quant_utils.cuh:164-184)."""
+    return torch.from_numpy(e5m2_from_float32(t.detach().cpu().float().numpy())).view(t.shape)
+
+
+def e5m2_to_float16_bits(b: np.ndarray) -> np.ndarray:
+    """e5m2 byte -> IEEE half bit pattern: e5m2 is the high byte of a half
+    (`__nv_cvt_fp8_to_halfraw`, used at quant_utils.cuh:23-29)."""
+    return (b.astype(np.uint16) << 8)
+
+
+def e5m2_to_tensor(b: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    """uint8 e5m2 -> dtype via half (-> float -> bf16 for bf16: quant_utils.cuh:72-81)."""
+    h = torch.from_numpy(e5m2_to_float16_bits(b.detach().cpu().numpy()).view(np.float16).copy())
+    return h.view(b.shape).float().to(dtype)
+
+
+def convert_fp8_e5m2(src: torch.Tensor, dst: torch.Tensor) -> None:
+    """Whole-cache cast either direction (csrc/cache_kernels.cu:272-320)."""
+    if dst.dtype == torch.uint8:
+        dst.copy_(e5m2_from_tensor(src))
+    else:
+        dst.copy_(e5m2_to_tensor(src, dst.dtype))
+
+
+# --------------------------------------------------------------------------------------------
+# cache writes and block moves
+# --------------------------------------------------------------------------------------------
+def reshape_and_cache(key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor,
+                      value_cache: torch.Tensor, slot_mapping: torch.Tensor,
+                      kv_cache_dtype: str = "auto") -> None:
+    """Scatter token i's K/V into slot slot_mapping[i] (negative = padding, skipped).
+
+    key_cache[blk, h, d // x, off, d % x] = key[i, h, d]; value_cache[blk, h, d, off] = value[i, h, d]
+    with blk = slot // bs, off = slot % bs (csrc/cache_kernels.cu:154-210; the reference test
+    states the same as a loop, tests/kernels/test_cache.py:148-158).  fp8: values go through the
+    saturating e5m2 encode first.
+    """
+    n, h, d = key.shape
+    bs, x = key_cache.shape[3], key_cache.shape[4]
+    k, v = key, value
+    if kv_cache_dtype == "fp8_e5m2":
+        k, v = e5m2_from_tensor(key), e5m2_from_tensor(value)
+    k = k.reshape(n, h, d // x, x)
+    for i, slot in enumerate(slot_mapping.cpu().tolist()):
+        if slot < 0:
+            continue
+        blk, off = slot // bs, slot % bs
+        key_cache[blk, :, :, off, :] = k[i]
+        value_cache[blk, :, :, off] = v[i]
+
+
+def copy_blocks(key_caches: List[torch.Tensor], value_caches: List[torch.Tensor],
+                block_mapping: Dict[int, List[int]]) -> None:
+    """For every layer: cache[dst] = cache[src] for K and V (csrc/cache_kernels.cu:65-91;
+    tests/kernels/test_cache.py:85-91).  Sources are read from the pre-call state only when a
+    block is never both a source and a destination, which the block manager guarantees."""
+    for src, dsts in block_mapping.items():
+        for dst in dsts:
+            for kc in key_caches:
+                kc[dst].copy_(kc[src])
+            for vc in value_caches:
+                vc[dst].copy_(vc[src])
+
+
+def swap_blocks(src: torch.Tensor, dst: torch.Tensor, block_mapping: Dict[int, int]) -> None:
+    """dst[d] = src[s] for each mapping entry (csrc/cache_kernels.cu:21-60;
+    tests/kernels/test_cache.py:222-226)."""
+    for s, d in block_mapping.items():
+        dst[d].copy_(src[s])
+
+
+def coalesce_blocks(block_list: Sequence[int]) -> List[Tuple[int, int]]:
+    """Sorted block ids -> (start, length) runs of consecutive ids (vllm/utils.py:403-420)."""
+    runs: List[Tuple[int, int]] = []
+    for b in sorted(block_list):
+        if runs and runs[-1][0] + runs[-1][1] == b:
+            runs[-1] = (runs[-1][0], runs[-1][1] + 1)
+        else:
+            runs.append((b, 1))
+    return runs
+
+
+def kv_put(src_caches: Sequence[torch.Tensor], dst_caches: Sequence[torch.Tensor],
+           runs: Sequence[Tuple[int, int]]) -> None:
+    """Prefill->decode transfer semantics: for each registered buffer and each run, the bytes of
+    blocks [start, start+len) land at the SAME block offsets of the destination buffer
+    (put(dst_mem, off, src_mem, off, bytes), csrc/kv_comm_kernels.cu:15;
+    vllm/worker/comm_utils.py:132-147)."""
+    for s, d in zip(src_caches, dst_caches):
+        for start, n in runs:
+            d[start:start + n].copy_(s[start:start + n])

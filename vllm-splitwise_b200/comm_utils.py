@@ -1,0 +1,254 @@
+"""Splitwise prefill -> decode KV-block transfer: mirror of the reference's
+vllm/worker/comm_utils.py (KVCacheCommunicator :93-147, KVCacheCommManager :150-222) over NVLink
+peer memory instead of MSCCL++ proxy channels.
+
+Same call surface -- `KVCacheCommManager(rank, world_size, num_prompt_workers, init_method)`,
+`.setup_comm(num_layers, kv_cache)`, `.put(sem_id, layer_id, block_start, num_blocks)`,
+`.signal_and_flush(sem_id)`, `.wait(sem_id)`, `.destroy_comm()` -- and the same meaning: after
+`wait(sem)` completes on the token GPU's stream, every byte `put` under `sem` since the previous
+signal is visible in the token GPU's caches at the same block offsets.
+
+What differs is the mechanism.  The reference launches a 1-thread kernel per put that posts a
+trigger to a host FIFO; a host proxy thread turns it into a copy (csrc/kv_comm_kernels.cu:11-20).
+Here the token GPU's cache tensors are mapped into the prompt process once (CUDA IPC, or plain
+peer access inside one process) and `put` is ONE multi-CTA kernel that stores the block runs
+straight into the peer mapping; `signal` is a system-scope release store to a flag in the token
+GPU's memory and `wait` an acquire spin on it.  `put_runs` / `put_layers` batch any number of
+runs and layers into a single launch (the reference needs one launch per run per K/V).
+"""
+import ctypes
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from .utils import MAX_SLOT_IDS
+
+HEAD_TYPES = [0, 1]  # 0 = keys, 1 = values (reference comm_utils.py:16)
+
+
+def pair_rank(rank: int, world_size: int, num_prompt_workers: int) -> int:
+    """Prompt rank r is paired with token rank (r + num_prompt_workers) % world (comm_utils.py:165)."""
+    return (rank + num_prompt_workers) % world_size
+
+
+def is_prompt_rank(rank: int, num_prompt_workers: int) -> bool:
+    return rank < num_prompt_workers
+
+
+def _runs_array(runs: Sequence[Tuple[int, int]]):
+    flat: List[int] = []
+    for start, n in runs:
+        flat += (int(start), int(n))
+    return (ctypes.c_int32 * len(flat))(*flat), len(flat) // 2
+
+
+class KVCacheCommunicator:
+    """put / signal / wait on one prompt<->token pair.
+
+    block_size: bytes of one block of one layer's K (== V), as in the reference (comm_utils.py:199-201).
+    src_table / dst_table: device int64 [2*num_layers] base addresses, order [L0.K, L0.V, L1.K, ...];
+    dst entries are addresses of the PEER's tensors as mapped into this process.
+    remote_flags: address (in this process) of the peer's uint64[MAX_SLOT_IDS] flag array.
+    local_flags: this GPU's flag array (what `wait` polls).
+    """
+
+    def __init__(self, block_size: int, num_layers: int, device: torch.device,
+                 src_table: Optional[torch.Tensor], dst_table: Optional[torch.Tensor],
+                 remote_flags: Optional[int], local_flags: torch.Tensor, my_rank: int, remote_rank: int,
+                 max_ctas: int = 0, wait_max_spins: int = 100000000) -> None:
+        self.block_size = block_size
+        self.num_layers = num_layers
+        self.device = device
+        self.src_table = src_table
+        self.dst_table = dst_table
+        self.remote_flags = remote_flags
+        self.local_flags = local_flags
+        self.my_rank = my_rank
+        self.remote_rank = remote_rank
+        self.max_ctas = max_ctas
+        self.wait_max_spins = wait_max_spins
+        self.sent = [0] * MAX_SLOT_IDS       # signals issued per semaphore (prompt side)
+        self.expected = [0] * MAX_SLOT_IDS   # signals awaited per semaphore (token side)
+        self.timeout_flag = torch.zeros(1, dtype=torch.int32, device=device)
+        self._lib = _lib.load()
+
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _check_sem(self, sem_id: int) -> None:
+        if not 0 <= sem_id < MAX_SLOT_IDS:
+            raise ValueError(f"sem_id {sem_id} out of range [0, {MAX_SLOT_IDS})")
+
+    def _put(self, first_buf: int, num_bufs: int, runs: Sequence[Tuple[int, int]]) -> None:
+        if self.src_table is None or self.dst_table is None:
+            raise RuntimeError("put() called on a rank that has no outgoing KV connection")
+        arr, n = _runs_array(runs)
+        if n == 0:
+            return
+        with torch.cuda.device(self.device):
+            st = self._lib.b200_kv_put_blocks(self.src_table.data_ptr() + 8 * first_buf,
+                                              self.dst_table.data_ptr() + 8 * first_buf, num_bufs, arr, n,
+                                              self.block_size, self.max_ctas, self._stream())
+        _lib.check(st, "kv put")
+
+    # ---- reference surface -------------------------------------------------------------
+    def put(self, sem_id: int, layer_id: int, block_start: int, num_blocks: int) -> None:
+        """K and V blocks [block_start, block_start+num_blocks) of one layer (comm_utils.py:132-147)."""
+        self._check_sem(sem_id)
+        self._put(2 * layer_id, 2, [(block_start, num_blocks)])
+
+    def signal_and_flush(self, sem_id: int) -> None:
+        self._check_sem(sem_id)
+        if self.remote_flags is None:
+            raise RuntimeError("signal_and_flush() called on a rank that has no outgoing KV connection")
+        self.sent[sem_id] += 1
+        with torch.cuda.device(self.device):
+            st = self._lib.b200_kv_signal(self.remote_flags + 8 * sem_id, self.sent[sem_id], self._stream())
+        _lib.check(st, "kv signal")
+
+    def wait(self, sem_id: int) -> None:
+        self._check_sem(sem_id)
+        self.expected[sem_id] += 1
+        with torch.cuda.device(self.device):
+            st = self._lib.b200_kv_wait(self.local_flags.data_ptr() + 8 * sem_id, self.expected[sem_id],
+                                        self.wait_max_spins, self.timeout_flag.data_ptr(), self._stream())
+        _lib.check(st, "kv wait")
+
+    # ---- batched extensions ------------------------------------------------------------
+    def put_runs(self, sem_id: int, layer_id: int, runs: Sequence[Tuple[int, int]]) -> None:
+        """All coalesced runs of one layer (K and V) in one launch."""
+        self._check_sem(sem_id)
+        self._put(2 * layer_id, 2, runs)
+
+    def put_layers(self, sem_id: int, first_layer: int, num_layers: int, runs: Sequence[Tuple[int, int]]) -> None:
+        """The same runs for a range of layers (K and V) in one launch."""
+        self._check_sem(sem_id)
+        self._put(2 * first_layer, 2 * num_layers, runs)
+
+    def timed_out(self) -> bool:
+        """True if any wait() expired (synchronises; for tests / health checks)."""
+        return bool(self.timeout_flag.item())
+
+
+class KVCacheCommManager:
+    """Bootstrap + registration (reference comm_utils.py:150-222).
+
+    Cross-process (one process per GPU): handles travel through `torch.distributed`
+    (`group`, default = the world group the worker already created, reference worker.py:427-432);
+    `init_method` ("tcp://ip:port") is only used to create a gloo group when none exists -- it takes
+    the place of the reference's MSCCL++ bootstrap address.
+    Single process: pass `peer_kv_cache` (+ optional `peer_flags`) to `setup_comm` to wire this rank
+    to tensors of another GPU (peer access) or of the same GPU (loopback, tests).
+    """
+
+    def __init__(self, rank: int, world_size: int, num_prompt_workers: int,
+                 init_method: Optional[str] = None, group=None, device: Optional[torch.device] = None) -> None:
+        self.rank = rank
+        self.world_size = world_size
+        self.num_prompt_workers = num_prompt_workers
+        self.corr_worker_rank = pair_rank(rank, world_size, num_prompt_workers)
+        self.is_prompt = is_prompt_rank(rank, num_prompt_workers)
+        self.init_method = init_method
+        self.group = group
+        self.device = torch.device(device) if device is not None else None
+        self.kvcache_comm: Optional[KVCacheCommunicator] = None
+        self._opened: List[int] = []
+        self._keepalive: List[torch.Tensor] = []
+
+    # -- helpers ---------------------------------------------------------------------------
+    def _export(self, t: torch.Tensor) -> Tuple[bytes, int]:
+        handle = (ctypes.c_ubyte * _lib.IPC_HANDLE_BYTES)()
+        off, size = ctypes.c_int64(), ctypes.c_int64()
+        st = _lib.load().b200_kv_ipc_export(t.data_ptr(), handle, ctypes.byref(off), ctypes.byref(size))
+        _lib.check(st, "kv ipc export")
+        return bytes(handle), off.value
+
+    def _open(self, handle: bytes, cache: dict) -> int:
+        if handle not in cache:  # several tensors can live in one allocation: map it once
+            buf = (ctypes.c_ubyte * _lib.IPC_HANDLE_BYTES).from_buffer_copy(handle)
+            base = ctypes.c_void_p()
+            st = _lib.load().b200_kv_ipc_open(buf, ctypes.byref(base))
+            _lib.check(st, "kv ipc open")
+            cache[handle] = base.value
+            self._opened.append(base.value)
+        return cache[handle]
+
+    def _ensure_group(self):
+        import torch.distributed as dist
+        if self.group is not None:
+            return self.group
+        if not dist.is_initialized():
+            if not self.init_method:
+                raise RuntimeError("torch.distributed is not initialised and no init_method was given")
+            dist.init_process_group("gloo", init_method=self.init_method, rank=self.rank,
+                                    world_size=self.world_size)
+        return dist.group.WORLD
+
+    # -- reference surface -------------------------------------------------------------------
+    def setup_comm(self, num_layers: int, kv_cache: List[Tuple[torch.Tensor, torch.Tensor]],
+                   peer_kv_cache: Optional[List[Tuple[torch.Tensor, torch.Tensor]]] = None,
+                   peer_flags: Optional[torch.Tensor] = None, max_ctas: int = 0) -> None:
+        device = kv_cache[0][0].device if self.device is None else self.device
+        self.device = device
+        k0 = kv_cache[0][0]
+        block_size = (k0.numel() * k0.element_size()) // k0.size(0)  # bytes (comm_utils.py:199-201)
+        local_flags = torch.zeros(MAX_SLOT_IDS, dtype=torch.int64, device=device)
+        bufs = [kv_cache[l][ht] for l in range(num_layers) for ht in HEAD_TYPES]
+        src_table = torch.tensor([t.data_ptr() for t in bufs], dtype=torch.int64, device=device)
+        dst_table, remote_flags = None, None
+
+        if peer_kv_cache is not None:
+            # single-process wiring (another GPU of this process, or loopback on the same GPU)
+            peer_dev = peer_kv_cache[0][0].device
+            if peer_dev != device:
+                st = _lib.load().b200_kv_enable_peer_access(device.index, peer_dev.index)
+                _lib.check(st, "kv enable peer access")
+            pbufs = [peer_kv_cache[l][ht] for l in range(num_layers) for ht in HEAD_TYPES]
+            dst_table = torch.tensor([t.data_ptr() for t in pbufs], dtype=torch.int64, device=device)
+            flags = peer_flags if peer_flags is not None else local_flags
+            remote_flags = flags.data_ptr()
+            self._keepalive += [flags] + pbufs
+        else:
+            import torch.distributed as dist
+            group = self._ensure_group()
+            mine = {"rank": self.rank, "bufs": [self._export(t) for t in bufs],
+                    "flags": self._export(local_flags)}
+            everyone: List[Optional[dict]] = [None] * self.world_size
+            dist.all_gather_object(everyone, mine, group=group)
+            if self.is_prompt:
+                peer = everyone[self.corr_worker_rank]
+                opened: dict = {}
+                with torch.cuda.device(device):
+                    addrs = [self._open(h, opened) + off for h, off in peer["bufs"]]
+                    fh, foff = peer["flags"]
+                    remote_flags = self._open(fh, opened) + foff
+                dst_table = torch.tensor(addrs, dtype=torch.int64, device=device)
+            dist.barrier(group=group)
+
+        self.kvcache_comm = KVCacheCommunicator(block_size, num_layers, device, src_table, dst_table, remote_flags,
+                                                local_flags, self.rank, self.corr_worker_rank, max_ctas=max_ctas)
+
+    def destroy_comm(self) -> None:
+        if self.device is not None and self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        for base in self._opened:
+            _lib.load().b200_kv_ipc_close(base)
+        self._opened = []
+        self._keepalive = []
+        self.kvcache_comm = None
+
+    def wait(self, sem_id: int) -> None:
+        self.kvcache_comm.wait(sem_id)
+
+    def signal_and_flush(self, sem_id: int) -> None:
+        self.kvcache_comm.signal_and_flush(sem_id)
+
+    def put(self, sem_id: int, layer_id: int, block_start: int, num_blocks: int) -> None:
+        self.kvcache_comm.put(sem_id, layer_id, block_start, num_blocks)
+
+    def put_runs(self, sem_id: int, layer_id: int, runs: Sequence[Tuple[int, int]]) -> None:
+        self.kvcache_comm.put_runs(sem_id, layer_id, runs)
+
+    def put_layers(self, sem_id: int, first_layer: int, num_layers: int, runs: Sequence[Tuple[int, int]]) -> None:
+        self.kvcache_comm.put_layers(sem_id, first_layer, num_layers, runs)
