@@ -1,0 +1,461 @@
+#!/usr/bin/env python
+"""bench.py -- the paged-KV decode hot path on B200, one JSON line per run.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3tp8|c3tp2|c4] [--version v1|v2]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...        # the reference's CPU path (oracle port) on the host cores
+
+Step       = one layer-call of the decode path over one batch: reshape_and_cache of the step's new
+             token per sequence, then paged_attention (v1 signature by default) over the whole context.
+             Consecutive steps cycle over `--layers` distinct layer caches, each far larger than L2,
+             with distinct physical blocks per (sequence, position), so nothing is served from L2.
+Workload   = BASELINE.json configs[1] (C2: Llama-2-7B decode shape, 32 heads, head 128, block 16,
+             batch 64, ctx 4096, fp16) per GPU.  N > 1: every rank holds the same per-GPU shape -- the
+             KV-head shard of an N-times-wider model (weak scaling; KV-head sharding has no collective,
+             SURVEY 8e); block tables are replicated.  `--workload c3tp8` etc. run the other configs.
+value      = algorithmic GB/s of the whole job with inputs resident in HBM (bytes formula: BASELINE.md
+             section 3), device-timed with CUDA events, max over ranks.
+e2e        = same metric through the reference-facing API (PagedAttentionImpl.reshape_and_cache +
+             forward_decode) with the step's query/key/value/block_tables/context_lens/slot_mapping
+             coming from pinned HOST memory and the output copied back to the host every step, copies
+             and the per-step sync inside the timed region.  (The KV cache itself is the path's
+             persistent device state, as in the reference's CacheEngine.)
+roofline   = attention kernel only: algorithmic bytes per launch / mean launch duration (CUDA events on
+             the launching stream inside the timed region) against MEASURED_PEAKS.json hbm_gbs.
+cpu_baseline = the oracle port of the reference's torch CPU path (tests/kernels/test_attention.py:58-111)
+             on the host cores, on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import math
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "paged_attention_decode_hbm_throughput"
+UNIT = "GB/s"
+FALLBACK_HBM_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md fallback, used only if MEASURED_PEAKS.json is absent
+
+# name -> per-GPU shape.  Hq/Hkv are heads ON ONE GPU.
+WORKLOADS = {
+    "c2": dict(desc="C2 Llama-2-7B decode: 32 q / 32 kv heads, head 128, block 16, batch 64, ctx 4096, fp16",
+               S=64, Hq=32, Hkv=32, D=128, bs=16, ctx=4096, dtype="float16", kv="auto"),
+    "c3tp8": dict(desc="C3 Llama-2-70B GQA tp=8 shard: 8 q / 1 kv head, head 128, block 16, batch 256, ctx 4096, bf16",
+                  S=256, Hq=8, Hkv=1, D=128, bs=16, ctx=4096, dtype="bfloat16", kv="auto"),
+    "c3tp4": dict(desc="C3 Llama-2-70B GQA tp=4 shard: 16 q / 2 kv heads, batch 256, ctx 4096, bf16",
+                  S=256, Hq=16, Hkv=2, D=128, bs=16, ctx=4096, dtype="bfloat16", kv="auto"),
+    "c3tp2": dict(desc="C3 Llama-2-70B GQA tp=2 shard: 32 q / 4 kv heads, batch 256, ctx 4096, bf16",
+                  S=256, Hq=32, Hkv=4, D=128, bs=16, ctx=4096, dtype="bfloat16", kv="auto"),
+    "c3": dict(desc="C3 Llama-2-70B GQA unsharded: 64 q / 8 kv heads, batch 256, ctx 4096, bf16",
+               S=256, Hq=64, Hkv=8, D=128, bs=16, ctx=4096, dtype="bfloat16", kv="auto"),
+    "c4": dict(desc="C4 Mistral-7B GQA: 32 q / 8 kv heads, head 128, block 16, batch 128, ctx 8192, bf16 query, fp8_e5m2 KV",
+               S=128, Hq=32, Hkv=8, D=128, bs=16, ctx=8192, dtype="bfloat16", kv="fp8_e5m2"),
+    "c1": dict(desc="C1 OPT-125m shape: 12 heads, head 64, block 16, batch 8, ctx 512, fp32",
+               S=8, Hq=12, Hkv=12, D=64, bs=16, ctx=512, dtype="float32", kv="auto"),
+}
+
+
+def elt_bytes(name: str) -> int:
+    return {"float32": 4, "float16": 2, "bfloat16": 2}[name]
+
+
+def attention_bytes(w) -> int:
+    """Algorithmic bytes of one paged_attention call (SURVEY 8d / BASELINE.md section 3):
+    K+V once per KV head + q in + out + block table + context_lens."""
+    cache_elt = 1 if w["kv"] == "fp8_e5m2" else elt_bytes(w["dtype"])
+    kv = w["S"] * w["ctx"] * w["Hkv"] * w["D"] * 2 * cache_elt
+    qo = 2 * w["S"] * w["Hq"] * w["D"] * elt_bytes(w["dtype"])
+    tables = w["S"] * math.ceil(w["ctx"] / w["bs"]) * 4 + w["S"] * 4
+    return kv + qo + tables
+
+
+def reshape_and_cache_bytes(w) -> int:
+    """N tokens x Hkv x D x (K,V) x (read T + write cache elt) + slot_mapping."""
+    cache_elt = 1 if w["kv"] == "fp8_e5m2" else elt_bytes(w["dtype"])
+    return w["S"] * w["Hkv"] * w["D"] * 2 * (elt_bytes(w["dtype"]) + cache_elt) + w["S"] * 8
+
+
+def step_bytes(w) -> int:
+    return attention_bytes(w) + reshape_and_cache_bytes(w)
+
+
+def dist_env():
+    return (int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)),
+            int(os.environ.get("WORLD_SIZE", 1)))
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy bandwidth)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback 6.65 TB/s (B200_PROFILING.md); MEASURED_PEAKS.json absent"
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks under load (NVML in a thread; nvidia-smi as a fallback)
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting", 0x10: "sync_boost"}
+
+    def __init__(self, index: int, period_s: float = 0.01):
+        self.index, self.period = index, period_s
+        self.samples, self.mask, self.max_mhz, self.power = [], 0, None, []
+        self._stop = threading.Event()
+        self._thread = None
+        self._nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nvml = pynvml
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = index
+            if vis:
+                try:
+                    phys = int(vis.split(",")[index])
+                except ValueError:
+                    phys = index
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self._nvml = None
+
+    def _loop(self):
+        n = self._nvml
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM)))
+                self.mask |= int(n.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+                self.power.append(n.nvmlDeviceGetPowerUsage(self._h) / 1000.0)
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def start(self):
+        if self._nvml is not None:
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+            self._thread.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join()
+        if not self.samples:  # NVML unavailable or region shorter than one period: one nvidia-smi reading
+            try:
+                import subprocess
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", "--query-gpu=clocks.sm,clocks.max.sm",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=20)
+                a, b = out.stdout.strip().split(",")
+                self.samples, self.max_mhz = [int(a)], int(b)
+            except Exception:
+                pass
+        reasons = [name for bit, name in self.REASONS.items() if self.mask & bit]
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": reasons, "samples": len(self.samples),
+                "power_w_max": round(max(self.power), 1) if self.power else None}
+
+
+# ---------------------------------------------------------------------------------------------
+# workload construction (device)
+# ---------------------------------------------------------------------------------------------
+def build_device_workload(w, num_layers, device, seed):
+    """Layer caches by the reference fixture recipe (vllm/utils.py:366-392), distinct physical blocks per
+    (sequence, position) in a random permutation (SURVEY 8d rule 1), one spare block per sequence."""
+    import torch
+    from vllm_splitwise_b200.utils import create_kv_caches_with_random
+    dt = getattr(torch, w["dtype"])
+    S, ctx, bs = w["S"], w["ctx"], w["bs"]
+    nblk = math.ceil(ctx / bs)
+    NB = S * nblk
+    g = torch.Generator().manual_seed(seed)
+    bt = torch.randperm(NB, generator=g)[:S * nblk].view(S, nblk).to(torch.int32)
+    kcs, vcs = create_kv_caches_with_random(NB, bs, num_layers, w["Hkv"], w["D"], w["kv"], dt, seed, device)
+    scale = float(w["D"] ** -0.5)
+    host = dict(
+        q=torch.empty(S, w["Hq"], w["D"], dtype=dt).uniform_(-scale, scale, generator=g).pin_memory(),
+        key=torch.empty(S, w["Hkv"], w["D"], dtype=dt).uniform_(-scale, scale, generator=g).pin_memory(),
+        value=torch.empty(S, w["Hkv"], w["D"], dtype=dt).uniform_(-scale, scale, generator=g).pin_memory(),
+        bt=bt.pin_memory(),
+        cl=torch.full((S,), ctx, dtype=torch.int32).pin_memory(),
+        # the step's new token is the last one of the context: slot = table[(ctx-1)//bs]*bs + (ctx-1)%bs
+        slots=(bt[:, (ctx - 1) // bs].long() * bs + (ctx - 1) % bs).pin_memory(),
+        out=torch.empty(S, w["Hq"], w["D"], dtype=dt).pin_memory(),
+    )
+    dev = {k: v.to(device) for k, v in host.items()}
+    return dict(kcs=kcs, vcs=vcs, host=host, dev=dev, scale=scale, NB=NB)
+
+
+class Meta:
+    """Duck-typed InputMetadata (vllm/model_executor/input_metadata.py) for the op wrapper."""
+
+    def __init__(self, slot_mapping, block_tables, context_lens, max_context_len, kv_cache_dtype):
+        self.slot_mapping = slot_mapping
+        self.block_tables = block_tables
+        self.context_lens = context_lens
+        self.max_context_len = max_context_len
+        self.kv_cache_dtype = kv_cache_dtype
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU baseline (oracle port of the reference torch path) -- rank 0 only
+# ---------------------------------------------------------------------------------------------
+def cpu_sample_inputs(w, n_seqs, seed=0):
+    """CPU tensors of the first n_seqs sequences of the workload shape (same recipe, compact cache)."""
+    import torch
+    dt = getattr(torch, w["dtype"])
+    nblk = math.ceil(w["ctx"] / w["bs"])
+    NB = n_seqs * nblk
+    g = torch.Generator().manual_seed(seed)
+    scale = float(w["D"] ** -0.5)
+    cache_elt = 1 if w["kv"] == "fp8_e5m2" else elt_bytes(w["dtype"])
+    x = 16 // cache_elt
+    kc = torch.empty(NB, w["Hkv"], w["D"] // x, w["bs"], x, dtype=torch.float32).uniform_(-scale, scale, generator=g)
+    vc = torch.empty(NB, w["Hkv"], w["D"], w["bs"], dtype=torch.float32).uniform_(-scale, scale, generator=g)
+    if w["kv"] == "fp8_e5m2":
+        from oracle import paged_kv_oracle as O
+        kc, vc = O.e5m2_to_tensor(O.e5m2_from_tensor(kc), dt), O.e5m2_to_tensor(O.e5m2_from_tensor(vc), dt)
+    else:
+        kc, vc = kc.to(dt), vc.to(dt)
+    q = torch.empty(n_seqs, w["Hq"], w["D"], dtype=dt).uniform_(-scale, scale, generator=g)
+    bt = torch.randperm(NB, generator=g).view(n_seqs, nblk).to(torch.int32)
+    cl = torch.full((n_seqs,), w["ctx"], dtype=torch.int32)
+    return q, kc, vc, bt, cl, scale
+
+
+def time_cpu_oracle(w, n_seqs, repeats=1):
+    """Seconds per pass of the oracle over n_seqs sequences (all torch threads)."""
+    import torch
+    from oracle import paged_kv_oracle as O  # the one place bench.py executes oracle/: the CPU baseline
+    q, kc, vc, bt, cl, scale = cpu_sample_inputs(w, n_seqs)
+    out = torch.empty_like(q)
+    best = float("inf")
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        O.single_query_cached_kv_attention(out, q, w["Hq"] // w["Hkv"], kc, vc, bt, cl, scale, None)
+        best = min(best, time.perf_counter() - t0)
+    return best
+
+
+def sample_bytes(w, n_seqs) -> int:
+    return attention_bytes(dict(w, S=n_seqs))
+
+
+def cpu_baseline(w, budget_s=15.0):
+    import torch
+    t1 = time_cpu_oracle(w, 1)
+    n = max(1, min(w["S"], int(budget_s / max(t1, 1e-3))))
+    t = time_cpu_oracle(w, n) if n > 1 else t1
+    return {"value": round(sample_bytes(w, n) / t / 1e9, 3), "unit": UNIT, "cores": torch.get_num_threads(),
+            "kind": "port",
+            "sample": f"attention over the first {n} of {w['S']} sequences (ctx {w['ctx']}, {w['Hq']}q/{w['Hkv']}kv heads), "
+                      f"{t:.2f} s; oracle port of tests/kernels/test_attention.py:58-111 (vectorised gather), torch CPU"}
+
+
+# ---------------------------------------------------------------------------------------------
+# the reference arm: CPU only, rank 0 only
+# ---------------------------------------------------------------------------------------------
+def run_reference(args, w):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return 0
+    import torch
+    torch.set_num_threads(os.cpu_count() or 1)
+    t1 = time_cpu_oracle(w, 1)
+    # bounded sample per step so that (steps + warmup) passes end within a few minutes
+    total_budget = 150.0
+    n = max(1, min(w["S"], int(total_budget / (args.steps + args.warmup) / max(t1, 1e-3))))
+    from oracle import paged_kv_oracle as O
+    q, kc, vc, bt, cl, scale = cpu_sample_inputs(w, n)
+    out = torch.empty_like(q)
+    for _ in range(args.warmup):
+        O.single_query_cached_kv_attention(out, q, w["Hq"] // w["Hkv"], kc, vc, bt, cl, scale, None)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        O.single_query_cached_kv_attention(out, q, w["Hq"] // w["Hkv"], kc, vc, bt, cl, scale, None)
+    dt = time.perf_counter() - t0
+    value = sample_bytes(w, n) * args.steps / dt / 1e9
+    sample = (f"each step = attention over {n} of {w['S']} sequences (ctx {w['ctx']}); oracle port of the reference's "
+              f"torch CPU path (tests/kernels/test_attention.py:58-111), vectorised gather")
+    line = {"impl": "reference", "metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": w["dtype"], "data": "synthetic",
+            "config": {"workload": w["desc"], "version": args.version, "sample": sample},
+            "cpu_baseline": {"value": round(value, 4), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                             "sample": sample},
+            "e2e": {"value": round(value, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+def run_b200(args, w):
+    import torch
+    import torch.distributed as dist
+    rank, local_rank, world = dist_env()
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if args.gpus > 1 and world == 1:
+        raise SystemExit("launch N > 1 with torch.distributed.run (one process per GPU)")
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU path)"
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+
+    from vllm_splitwise_b200 import _lib
+    from vllm_splitwise_b200._C import cache_ops, ops
+    from vllm_splitwise_b200.paged_attn import PagedAttentionImpl
+    lib = _lib.load()
+
+    wl = build_device_workload(w, args.layers, device, seed=rank)
+    d, h = wl["dev"], wl["host"]
+    S, Hq, D = w["S"], w["Hq"], w["D"]
+    P = math.ceil(w["ctx"] / 512)
+    out = torch.empty_like(d["q"])
+    if args.version == "v2":
+        tmp = torch.empty(S, Hq, P, D, dtype=out.dtype, device=device)
+        es = torch.empty(S, Hq, P, dtype=torch.float32, device=device)
+        ml = torch.empty_like(es)
+
+    def attention(layer):
+        if args.version == "v1":
+            ops.paged_attention_v1(out, d["q"], wl["kcs"][layer], wl["vcs"][layer], w["Hkv"], wl["scale"], d["bt"],
+                                   d["cl"], w["bs"], w["ctx"], None, w["kv"])
+        else:
+            ops.paged_attention_v2(out, es, ml, tmp, d["q"], wl["kcs"][layer], wl["vcs"][layer], w["Hkv"], wl["scale"],
+                                   d["bt"], d["cl"], w["bs"], w["ctx"], None, w["kv"])
+
+    def step(i, ev=None):
+        layer = i % args.layers
+        cache_ops.reshape_and_cache(d["key"], d["value"], wl["kcs"][layer], wl["vcs"][layer], d["slots"], w["kv"])
+        if ev is not None:
+            ev[0].record()
+        attention(layer)
+        if ev is not None:
+            ev[1].record()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing ----
+    for i in range(args.warmup):
+        step(i)
+    barrier()
+    attn_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    t_beg, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(local_rank)
+    launches0 = lib.b200_kv_launch_count()
+    sampler.start()
+    barrier()
+    t_beg.record()
+    for i in range(args.steps):
+        step(i, attn_ev[i])
+    t_end.record()
+    barrier()
+    clocks = sampler.stop()
+    launches = lib.b200_kv_launch_count() - launches0
+    total_ms = t_beg.elapsed_time(t_end)
+    attn_ms = sum(a.elapsed_time(b) for a, b in attn_ev) / args.steps
+
+    # ---- end to end through the op wrapper, host buffers ----
+    meta_host_bytes = sum(h[k].numel() * h[k].element_size() for k in ("q", "key", "value", "bt", "cl", "slots"))
+    out_bytes = h["out"].numel() * h["out"].element_size()
+
+    def e2e_step(i):
+        layer = i % args.layers
+        q = h["q"].to(device, non_blocking=True)
+        key = h["key"].to(device, non_blocking=True)
+        value = h["value"].to(device, non_blocking=True)
+        meta = Meta(h["slots"].to(device, non_blocking=True), h["bt"].to(device, non_blocking=True),
+                    h["cl"].to(device, non_blocking=True), w["ctx"], w["kv"])
+        PagedAttentionImpl.reshape_and_cache(key, value, wl["kcs"][layer], wl["vcs"][layer], meta)
+        o = PagedAttentionImpl.forward_decode(q, wl["kcs"][layer], wl["vcs"][layer], meta, w["Hkv"], wl["scale"], None)
+        h["out"].copy_(o, non_blocking=True)
+        torch.cuda.current_stream().synchronize()  # the caller consumes the step's result on the host
+
+    for i in range(args.warmup):
+        e2e_step(i)
+    barrier()
+    e_beg, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e_beg.record()
+    for i in range(args.steps):
+        e2e_step(i)
+    e_end.record()
+    barrier()
+    e2e_ms = e_beg.elapsed_time(e_end)
+
+    # ---- max over ranks ----
+    times = torch.tensor([total_ms, e2e_ms, attn_ms], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    total_ms, e2e_ms, attn_ms = times.tolist()
+
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        job_bytes = step_bytes(w) * args.steps * world
+        value = job_bytes / (total_ms * 1e-3) / 1e9
+        e2e_val = job_bytes / (e2e_ms * 1e-3) / 1e9
+        achieved = attention_bytes(w) / (attn_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 5), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": w["dtype"] if w["kv"] == "auto" else f"{w['dtype']}+fp8_e5m2_kv",
+            "data": "synthetic",
+            "config": {"workload": w["desc"] + (" per GPU (KV-head shard of an N-times-wider model)" if world > 1 else ""),
+                       "version": args.version, "layers_cycled": args.layers,
+                       "l2": "inputs larger than L2: each layer cache is %.2f GB, distinct physical blocks, %d layers cycled"
+                             % (attention_bytes(w) / 1e9, args.layers),
+                       "step": "reshape_and_cache + paged_attention_%s for one layer" % args.version,
+                       "decode_tokens_per_s_per_layer": round(w["S"] * world / (total_ms / args.steps * 1e-3), 1)},
+            "clocks": clocks,
+            "e2e": {"value": round(e2e_val, 2), "unit": UNIT, "h2d_bytes_per_step": meta_host_bytes,
+                    "d2h_bytes_per_step": out_bytes, "ms_per_step": round(e2e_ms / args.steps, 5)},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
+                         "frac": round(achieved / peak, 4), "traffic": args.traffic,
+                         "kernel": "paged_attn_simt_kernel", "kernel_ms": round(attn_ms, 5),
+                         "algorithmic_bytes_per_launch": attention_bytes(w), "peak_source": peak_src,
+                         "frac_of_8TBps_spec": round(achieved / 8000.0, 4)},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(w)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=500)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
+    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c2")
+    ap.add_argument("--version", choices=["v1", "v2"], default="v1")
+    ap.add_argument("--layers", type=int, default=3, help="distinct layer caches cycled by consecutive steps")
+    ap.add_argument("--traffic", type=float, default=None,
+                    help="ncu dram bytes per attention launch, from profiles/ (null unless given)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    w = WORKLOADS[args.workload]
+    return run_reference(args, w) if args.impl == "reference" else run_b200(args, w)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -61,6 +61,9 @@ typedef enum {
 B200_API const char* b200_kv_strerror(int status);
 B200_API const char* b200_kv_last_cuda_error(void);
 B200_API int b200_kv_abi_version(void);
+/* Number of kernels this library has launched in this process (all threads) since load; bench.py
+ * reports the difference across its timed region as "gpu_launches". */
+B200_API uint64_t b200_kv_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------
  * Paged attention decode.

@@ -50,7 +50,7 @@ def _gather_sequence(key_cache: torch.Tensor, value_cache: torch.Tensor, table: 
     (key [NB,Hkv,D/x,bs,x], value [NB,Hkv,D,bs]; vllm/worker/cache_engine.py:60-75)."""
     nb, hkv, dx, bs, x = key_cache.shape
     n = (context_len + bs - 1) // bs
-    idx = torch.as_tensor(list(table[:n]), dtype=torch.long)
+    idx = torch.as_tensor(list(table[:n]), dtype=torch.long, device=key_cache.device)
     k = key_cache.index_select(0, idx).permute(0, 3, 1, 2, 4).reshape(n * bs, hkv, dx * x)
     v = value_cache.index_select(0, idx).permute(0, 3, 1, 2).reshape(n * bs, hkv, value_cache.shape[2])
     return k[:context_len], v[:context_len]
@@ -77,7 +77,7 @@ def single_query_cached_kv_attention(output: torch.Tensor, query: torch.Tensor,
             values = values.repeat_interleave(num_queries_per_kv, dim=1)
         bias = None
         if alibi_slopes is not None:
-            pos = (torch.arange(ctx).int() - ctx + 1).float()
+            pos = (torch.arange(ctx, device=query.device).int() - ctx + 1).float()
             bias = alibi_slopes.view(-1, 1, 1) * pos.view(1, 1, -1)
         out = masked_attention(query[i:i + 1], keys, values, scale, bias)
         output[i].copy_(out.view(query.shape[1], query.shape[2]))
@@ -105,7 +105,7 @@ def single_query_cached_kv_attention_loop(output, query, num_queries_per_kv, key
             values = values.repeat_interleave(num_queries_per_kv, dim=1)
         bias = None
         if alibi_slopes is not None:
-            pos = (torch.arange(ctx).int() - ctx + 1).float()
+            pos = (torch.arange(ctx, device=query.device).int() - ctx + 1).float()
             bias = alibi_slopes.view(-1, 1, 1) * pos.view(1, 1, -1)
         output[i].copy_(masked_attention(query[i:i + 1], keys, values, scale, bias)[0])
 
@@ -114,7 +114,7 @@ def attention_fp32(query, num_queries_per_kv, key_cache, value_cache, block_tabl
                    scale, alibi_slopes) -> torch.Tensor:
     """All-fp32 evaluation of the same formula (inputs widened first): the 'true' value both the
     reference's torch path and any CUDA kernel approximate; used to judge which one is closer."""
-    out = torch.empty(query.shape, dtype=torch.float32)
+    out = torch.empty(query.shape, dtype=torch.float32, device=query.device)
     single_query_cached_kv_attention(out, query.float(), num_queries_per_kv, key_cache.float(),
                                      value_cache.float(), block_tables, context_lens, scale,
                                      alibi_slopes)
@@ -129,9 +129,10 @@ def v2_partials(query, num_queries_per_kv, key_cache, value_cache, block_tables,
     tmp_out = softmax-weighted V (normalised by exp_sum + 1e-6).  Entries of partitions past the
     context are left NaN (the kernel does not write them)."""
     s, h, d = query.shape
-    ml = torch.full((s, h, max_num_partitions), float("nan"))
-    es = torch.full((s, h, max_num_partitions), float("nan"))
-    tmp = torch.full((s, h, max_num_partitions, d), float("nan"))
+    dev = query.device
+    ml = torch.full((s, h, max_num_partitions), float("nan"), device=dev)
+    es = torch.full((s, h, max_num_partitions), float("nan"), device=dev)
+    tmp = torch.full((s, h, max_num_partitions, d), float("nan"), device=dev)
     tables = block_tables.cpu().tolist()
     lens = context_lens.cpu().tolist()
     qf = query.float()
@@ -142,7 +143,7 @@ def v2_partials(query, num_queries_per_kv, key_cache, value_cache, block_tables,
         values = values.repeat_interleave(num_queries_per_kv, dim=1)
         logits = torch.einsum("hd,khd->hk", qf[i], keys) * scale
         if alibi_slopes is not None:
-            logits = logits + alibi_slopes.view(-1, 1) * (torch.arange(ctx) - ctx + 1).float().view(1, -1)
+            logits = logits + alibi_slopes.view(-1, 1) * (torch.arange(ctx, device=dev) - ctx + 1).float().view(1, -1)
         for p in range((ctx + PARTITION_SIZE - 1) // PARTITION_SIZE):
             lo, hi = p * PARTITION_SIZE, min(ctx, (p + 1) * PARTITION_SIZE)
             lg = logits[:, lo:hi]
@@ -210,9 +211,10 @@ def e5m2_to_float16_bits(b: np.ndarray) -> np.ndarray:
 
 
 def e5m2_to_tensor(b: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
-    """uint8 e5m2 -> dtype via half (-> float -> bf16 for bf16: quant_utils.cuh:72-81)."""
-    h = torch.from_numpy(e5m2_to_float16_bits(b.detach().cpu().numpy()).view(np.float16).copy())
-    return h.view(b.shape).float().to(dtype)
+    """uint8 e5m2 -> dtype via half (-> float -> bf16 for bf16: quant_utils.cuh:72-81).  Pure bit
+    placement + exact widenings, done with torch integer ops so it runs on the tensor's device."""
+    h = (b.to(torch.int16) << 8).view(torch.float16)
+    return h.float().to(dtype)
 
 
 def convert_fp8_e5m2(src: torch.Tensor, dst: torch.Tensor) -> None:

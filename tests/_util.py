@@ -57,3 +57,75 @@ def bits(t: torch.Tensor) -> torch.Tensor:
     if t.dtype == torch.float32:
         return t.contiguous().view(torch.int32)
     return t
+
+
+def elt_size(dtype: torch.dtype) -> int:
+    return torch.tensor([], dtype=dtype).element_size()
+
+
+def make_attention_inputs(*, num_seqs, num_heads, head_size, block_size, dtype, kv_cache_dtype="auto", num_blocks,
+                          context_lens, use_alibi=False, seed=0, device="cuda", distinct_blocks=False):
+    """Inputs by the reference's recipe (tests/kernels/test_attention.py:137-173, vllm/utils.py:366-392):
+    q, K, V ~ uniform(-D^-0.5, D^-0.5); block tables drawn with replacement from [0, NB) unless
+    distinct_blocks; alibi slopes ~ randn."""
+    import random
+    from vllm_splitwise_b200.utils import create_kv_caches_with_random
+    random.seed(seed)
+    torch.random.manual_seed(seed)
+    torch.cuda.manual_seed(seed)
+    hq, hkv = num_heads
+    scale = float(1.0 / (head_size ** 0.5))
+    q = torch.empty(num_seqs, hq, head_size, dtype=dtype, device=device).uniform_(-scale, scale)
+    alibi = torch.randn(hq, dtype=torch.float, device=device) if use_alibi else None
+    max_ctx = max(context_lens)
+    nblk = (max_ctx + block_size - 1) // block_size
+    if distinct_blocks:
+        assert num_blocks >= num_seqs * nblk
+        bt = torch.randperm(num_blocks)[:num_seqs * nblk].view(num_seqs, nblk).to(torch.int32).to(device)
+    else:
+        bt = torch.tensor([[random.randint(0, num_blocks - 1) for _ in range(nblk)] for _ in range(num_seqs)],
+                          dtype=torch.int32, device=device)
+    cl = torch.tensor(context_lens, dtype=torch.int32, device=device)
+    kcs, vcs = create_kv_caches_with_random(num_blocks, block_size, 1, hkv, head_size, kv_cache_dtype, dtype, seed,
+                                            device)
+    return dict(q=q, kc=kcs[0], vc=vcs[0], bt=bt, cl=cl, alibi=alibi, scale=scale, max_ctx=max_ctx,
+                hq=hq, hkv=hkv, block_size=block_size, kv_cache_dtype=kv_cache_dtype)
+
+
+def run_v1(ops, a, out=None):
+    out = torch.empty_like(a["q"]) if out is None else out
+    ops.paged_attention_v1(out, a["q"], a["kc"], a["vc"], a["hkv"], a["scale"], a["bt"], a["cl"], a["block_size"],
+                           a["max_ctx"], a["alibi"], a["kv_cache_dtype"])
+    return out
+
+
+def run_v2(ops, a, partition_size=512):
+    q = a["q"]
+    s, h, d = q.shape
+    p = (a["max_ctx"] + partition_size - 1) // partition_size
+    out = torch.empty_like(q)
+    tmp = torch.full((s, h, p, d), float("nan"), dtype=q.dtype, device=q.device)
+    es = torch.full((s, h, p), float("nan"), dtype=torch.float32, device=q.device)
+    ml = torch.full_like(es, float("nan"))
+    ops.paged_attention_v2(out, es, ml, tmp, q, a["kc"], a["vc"], a["hkv"], a["scale"], a["bt"], a["cl"],
+                           a["block_size"], a["max_ctx"], a["alibi"], a["kv_cache_dtype"])
+    return out, es, ml, tmp
+
+
+def dequantized(a):
+    """(key_cache, value_cache) in the query dtype -- what the oracle attends over (the reference test
+    dequantises fp8 caches the same way, test_attention.py:228-244)."""
+    if a["kv_cache_dtype"] != "fp8_e5m2":
+        return a["kc"], a["vc"]
+    from oracle import paged_kv_oracle as O
+    dt = a["q"].dtype
+    return O.e5m2_to_tensor(a["kc"], dt), O.e5m2_to_tensor(a["vc"], dt)
+
+
+def oracle_attention(a):
+    from oracle import paged_kv_oracle as O
+    kc, vc = dequantized(a)
+    ref = torch.empty_like(a["q"])
+    O.single_query_cached_kv_attention(ref, a["q"], a["hq"] // a["hkv"], kc, vc, a["bt"], a["cl"], a["scale"],
+                                       a["alibi"])
+    return ref

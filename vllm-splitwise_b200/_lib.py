@@ -58,6 +58,7 @@ SIGNATURES = {
     "b200_kv_strerror": (c_char_p, [c_int32]),
     "b200_kv_last_cuda_error": (c_char_p, []),
     "b200_kv_abi_version": (c_int32, []),
+    "b200_kv_launch_count": (c_uint64, []),
     "b200_paged_attention_v1": (c_int32, [POINTER(PagedAttnArgs), c_void_p]),
     "b200_paged_attention_v2": (c_int32, [POINTER(PagedAttnArgs), c_void_p]),
     "b200_paged_attention_workspace_bytes": (c_int64, [POINTER(PagedAttnArgs)]),

@@ -6,6 +6,7 @@
 // All four are HBM-bound byte movers: the design rules are coalesced 16-byte accesses,
 // tables carried as kernel parameters (no H2D copy, no sync) and grids sized from the work.
 #include <algorithm>
+#include <atomic>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -23,6 +24,9 @@ void set_last_cuda_error(cudaError_t e, const char* where) {
   snprintf(g_last_cuda_error, sizeof(g_last_cuda_error), "%s: %s (%s)", where,
            cudaGetErrorName(e), cudaGetErrorString(e));
 }
+
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 int num_sms(int device) {
   static int cached[64];
@@ -273,6 +277,8 @@ extern "C" {
 B200_API int b200_kv_abi_version(void) { return B200_KV_ABI_VERSION; }
 
 B200_API const char* b200_kv_last_cuda_error(void) { return g_last_cuda_error; }
+
+B200_API uint64_t b200_kv_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 B200_API const char* b200_kv_strerror(int status) {
   switch (status) {

@@ -17,6 +17,7 @@ namespace b200 {
 
 // ---- host-side error plumbing -------------------------------------------------------------
 void set_last_cuda_error(cudaError_t e, const char* where);
+void count_launch();
 
 #define B200_CUDA_TRY(expr)                            \
   do {                                                 \
@@ -29,6 +30,7 @@ void set_last_cuda_error(cudaError_t e, const char* where);
 
 #define B200_LAUNCH_CHECK()                            \
   do {                                                 \
+    ::b200::count_launch();                            \
     cudaError_t e__ = cudaPeekAtLastError();           \
     if (e__ != cudaSuccess) {                          \
       ::b200::set_last_cuda_error(e__, "kernel launch"); \
