@@ -19,7 +19,7 @@ uint8_t oracle_e5m2_from_f32(float x) {
   memcpy(&bits, &x, 4);
   const uint8_t sign = (uint8_t)((bits >> 31) << 7);
   const uint32_t a = bits & 0x7FFFFFFFu;
-  if (a > 0x7F800000u) return (uint8_t)(sign | 0x7F);      /* NaN -> canonical NaN */
+  if (a > 0x7F800000u) return (uint8_t)0x7F;                /* NaN -> canonical +NaN, sign dropped */
   if (a <= 0x37000000u) return sign;                        /* |x| <= 2^-17 -> 0 */
   const int exp = (int)(a >> 23) - 127 + 15;
   const uint32_t man = a & 0x7FFFFFu;

@@ -178,7 +178,8 @@ def test_swap_blocks(cache_ops, kv_cache_factory, direction, head_size, block_si
     run = {10 + i: 300 + i for i in range(24)}
     srcs = random.sample(sorted(set(range(256)) - set(run)), num_mappings - 24)
     dsts = random.sample(sorted(set(range(256, 512)) - set(run.values())), num_mappings - 24)
-    mapping = dict(run, **dict(zip(srcs, dsts)))
+    mapping = dict(run)
+    mapping.update(zip(srcs, dsts))
     sk, sv = kv_cache_factory(num_blocks, block_size, 1, 8, head_size, "auto", dtype, 0, src_dev)
     dk, dv = kv_cache_factory(num_blocks, block_size, 1, 8, head_size, "auto", dtype, 1, dst_dev)
     if pinned:
