@@ -9,7 +9,8 @@ from ctypes import (POINTER, Structure, c_char_p, c_float, c_int32, c_int64, c_u
                     c_void_p)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libb200kv.so")
+# B200_KV_LIB points at another build of the same library (development: `make FAST=1 OUTDIR=...`)
+LIB_PATH = os.environ.get("B200_KV_LIB") or os.path.join(_HERE, "lib", "libb200kv.so")
 
 B200_OK = 0
 ERR_HEAD_SIZE, ERR_BLOCK_SIZE, ERR_DTYPE, ERR_ARG, ERR_ALIGN, ERR_CUDA, ERR_DEVICE, ERR_TIMEOUT = (

@@ -118,6 +118,14 @@ __device__ __forceinline__ uint64_t l2_policy_evict_first() {
 // SASS: UBLKCP.  Requires 16-byte aligned src/dst and size % 16 == 0.
 __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes,
                                          uint64_t* bar, uint64_t policy) {
+#ifdef B200_ATTN_NO_HINT
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+  (void)policy;
+  return;
+#endif
   asm volatile(
       "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
       "[%0], [%1], %2, [%3], %4;"

@@ -46,7 +46,8 @@ struct AttnParams {
   int partition_blocks;  // KV blocks per partition; 0 = whole context
   int max_num_partitions;
   int write_partials;    // 1: tmp_out/exp_sums/max_logits, 0: final out
-  int nstages;
+  int nstages;           // ring depth; always a multiple of nconsumers (see simt_smem_plan)
+  int nconsumers;        // consumer warps that take blocks (<= kConsumerWarps)
   long long q_stride;
   long long kv_block_stride;
   long long kv_head_stride;
@@ -143,7 +144,11 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_simt_kernel(const __g
     const unsigned char* kbase = static_cast<const unsigned char*>(p.k_cache) + (long long)kvh * p.kv_head_stride * (long long)sizeof(CT);
     const unsigned char* vbase = static_cast<const unsigned char*>(p.v_cache) + (long long)kvh * p.kv_head_stride * (long long)sizeof(CT);
     const long long blk_bytes = p.kv_block_stride * (long long)sizeof(CT);
+#ifdef B200_ATTN_NO_HINT
+    const uint64_t pol = 0;
+#else
     const uint64_t pol = l2_policy_evict_first();
+#endif
     int phys_next = lane < nblk ? table[lane] : 0;
     int stage = 0, fill = 0;  // fill = how many times the ring has wrapped
     for (int base = 0; base < nblk; base += 32) {
@@ -187,7 +192,12 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_simt_kernel(const __g
       for (int i = 0; i < VIT; ++i) acc[g][i] = 0.f;
     }
 
-    for (int n = warp; n < nblk; n += NW) {
+    // Blocks go to the active consumer warps round-robin.  nst % nwa == 0, so every fill of a given
+    // stage is consumed by the SAME warp, in program order: a parity wait can only tell adjacent
+    // phases apart, and bulk copies land out of order, so a different warp waiting for fill f+1 of a
+    // stage could otherwise slip through while fill f is still in flight.
+    const int nwa = p.nconsumers;
+    for (int n = warp; n < nblk && warp < nwa; n += nwa) {
       const int stage = n % nst;
       const uint32_t parity = (n / nst) & 1;
       const unsigned char* ks = stages + (size_t)stage * SM::kStageBytes;
@@ -382,14 +392,19 @@ int launch_simt(const AttnParams& p, int head_size, int block_size, int gt, dim3
                 int smem_budget, cudaStream_t stream);
 
 template <typename CT>
-inline bool simt_smem_plan(int head_size, int block_size, int gt, int smem_budget, int* nstages, int* smem_bytes) {
+inline bool simt_smem_plan(int head_size, int block_size, int gt, int smem_budget, int* nstages, int* nconsumers,
+                           int* smem_bytes) {
   const int kbytes = head_size * block_size * (int)sizeof(CT);
   const int stage = 2 * kbytes;
   const int fixed = gt * head_size * 4 + kConsumerWarps * gt * block_size * 4 +
                     kConsumerWarps * gt * head_size * 4 + kConsumerWarps * gt * 2 * 4 + 2 * 32 * 8;
   int n = (smem_budget - fixed) / stage;
   if (n > 16) n = 16;
+  // ring depth must be a multiple of the number of consuming warps (same warp per stage, see kernel)
+  const int nwa = n < kConsumerWarps ? n : kConsumerWarps;
+  if (nwa > 0) n = n / nwa * nwa;
   *nstages = n;
+  *nconsumers = nwa;
   *smem_bytes = n * stage + fixed;
   return n >= 2;
 }
