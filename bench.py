@@ -86,6 +86,16 @@ def step_bytes(w) -> int:
     return attention_bytes(w) + reshape_and_cache_bytes(w)
 
 
+def max_over_ranks(values, device, world):
+    """Element-wise MAX of a list of floats over all ranks (identity when world == 1)."""
+    import torch
+    t = torch.tensor(list(values), dtype=torch.float64, device=device)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.tolist()
+
+
 def dist_env():
     return (int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)),
             int(os.environ.get("WORLD_SIZE", 1)))
@@ -398,10 +408,7 @@ def run_b200(args, w):
     e2e_ms = e_beg.elapsed_time(e_end)
 
     # ---- max over ranks ----
-    times = torch.tensor([total_ms, e2e_ms, attn_ms], dtype=torch.float64, device=device)
-    if world > 1:
-        dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms, attn_ms = times.tolist()
+    total_ms, e2e_ms, attn_ms = max_over_ranks([total_ms, e2e_ms, attn_ms], device, world)
 
     if rank == 0:
         peak, peak_src = measured_peak()

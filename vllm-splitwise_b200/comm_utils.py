@@ -36,6 +36,22 @@ def is_prompt_rank(rank: int, num_prompt_workers: int) -> bool:
     return rank < num_prompt_workers
 
 
+def exchange_peer_info(group, rank: int, world_size: int, num_prompt_workers: int, mine: dict) -> Optional[dict]:
+    """All ranks publish `mine` (IPC handles of their cache buffers and flags); a prompt rank gets back
+    the record of its token rank (pair_rank), a token rank gets None.  Collective over `group` (any
+    torch.distributed backend; the records are pickled, so gloo is enough).  This replaces the MSCCL++
+    bootstrap + `make_connection` + `register_memory` exchange (reference comm_utils.py:158-197)."""
+    import torch.distributed as dist
+    everyone: List[Optional[dict]] = [None] * world_size
+    dist.all_gather_object(everyone, mine, group=group)
+    for r, rec in enumerate(everyone):
+        if rec is None or rec.get("rank") != r:
+            raise RuntimeError(f"KV comm bootstrap: bad record from rank {r}")
+    if not is_prompt_rank(rank, num_prompt_workers):
+        return None
+    return everyone[pair_rank(rank, world_size, num_prompt_workers)]
+
+
 def _runs_array(runs: Sequence[Tuple[int, int]]):
     flat: List[int] = []
     for start, n in runs:
@@ -214,10 +230,8 @@ class KVCacheCommManager:
             group = self._ensure_group()
             mine = {"rank": self.rank, "bufs": [self._export(t) for t in bufs],
                     "flags": self._export(local_flags)}
-            everyone: List[Optional[dict]] = [None] * self.world_size
-            dist.all_gather_object(everyone, mine, group=group)
-            if self.is_prompt:
-                peer = everyone[self.corr_worker_rank]
+            peer = exchange_peer_info(group, self.rank, self.world_size, self.num_prompt_workers, mine)
+            if peer is not None:
                 opened: dict = {}
                 with torch.cuda.device(device):
                     addrs = [self._open(h, opened) + off for h, off in peer["bufs"]]
