@@ -179,3 +179,23 @@ def test_two_gpu_peer_scatter():
     src_on_1 = [(k.to(d1), v.to(d1)) for k, v in src]
     _check(src_on_1, dst, before, {l: blocks for l in range(L)})
     m.destroy_comm()
+
+
+def test_two_process_ipc_transfer_bit_exact():
+    """One process per GPU (the deployment shape): handles cross processes by CUDA IPC, the prompt rank's
+    kernel stores into the token rank's cache, release/acquire flags order it.  Runs the C5 harness at a
+    small size; it verifies the received blocks bit for bit and exits non-zero on any mismatch."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", "29631", os.path.join(root, "tools", "kv_transfer_bench.py"),
+           "--prompts", "3", "--layers", "4", "--prompt-tokens", "512", "--iters", "2", "--warmup", "1"]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
+    lines = [json.loads(l) for l in res.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 6 and all(l["bit_exact"] for l in lines)

@@ -1,0 +1,203 @@
+#!/usr/bin/env python
+"""C5: Splitwise prefill -> decode KV-block transfer over NVLink, one process per GPU.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        tools/kv_transfer_bench.py [--prompts 8] [--layers 40] [--iters 5]
+
+N even: ranks [0, N/2) are prompt GPUs, rank r sends to token rank r + N/2 (reference comm_utils.py:165;
+N=8 is BASELINE config 5: 4 prefill -> 4 decode GPUs).  Shape = Llama-2-13B tp=4 shard: 40 layers, 10 KV
+heads/GPU, head 128, block 16, fp16 -> block_bytes 40 960; a 2048-token prompt = 128 blocks =
+419 430 400 B per GPU pair.
+
+For every (block-list pattern, mode) it times `--iters` rounds of `--prompts` prompts in flight and
+verifies on the token GPU, bit for bit, that exactly the transferred blocks arrived (checksum of int64
+words against the value the prompt side computed on its source blocks, untouched blocks still zero).
+Timing: CUDA events per rank from a common barrier to (prompt) the end of the signal kernel and (token)
+the end of the wait kernel; the MAX over the ranks of a pair set is the transfer time.
+Prints one JSON line per (pattern, mode) on rank 0.
+
+modes   bulk       one put_layers launch per prompt (all layers, all runs) + signal
+        per_layer  one put_runs launch per layer per prompt (how the attention backends call it while
+                   prefill is still computing, flash_attn.py:81-86) + signal
+        nccl       baseline: torch.distributed batch_isend_irecv, one P2P op per (layer, K|V, run)
+"""
+import argparse
+import json
+import os
+import random
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+NVLINK_MEASURED_GBS = 770.0   # peer copy per direction, /opt/skills/guides/B200_PROFILING.md
+NVLINK_NOMINAL_GBS = 900.0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--prompts", type=int, default=8, help="prompts in flight per round")
+    ap.add_argument("--layers", type=int, default=40)
+    ap.add_argument("--kv-heads", type=int, default=10)
+    ap.add_argument("--head-size", type=int, default=128)
+    ap.add_argument("--block-size", type=int, default=16)
+    ap.add_argument("--prompt-tokens", type=int, default=2048)
+    ap.add_argument("--iters", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=2)
+    ap.add_argument("--max-ctas", type=int, default=0)
+    ap.add_argument("--modes", default="bulk,per_layer,nccl")
+    ap.add_argument("--patterns", default="contiguous,fragmented")
+    ap.add_argument("--nccl-max-prompts", type=int, default=2, help="cap for the fragmented NCCL baseline")
+    args = ap.parse_args()
+
+    import torch
+    import torch.distributed as dist
+    from vllm_splitwise_b200.comm_utils import KVCacheCommManager
+    from vllm_splitwise_b200.utils import coalesce_blocks, kv_cache_shapes
+
+    rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
+    assert world % 2 == 0, "needs an even number of ranks"
+    npw = world // 2
+    is_prompt = rank < npw
+    peer = (rank + npw) % world
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    boot = dist.new_group(backend="gloo")
+
+    L, H, D, bs = args.layers, args.kv_heads, args.head_size, args.block_size
+    blocks_per_prompt = (args.prompt_tokens + bs - 1) // bs
+    NB = args.prompts * blocks_per_prompt * 2  # room for non-adjacent fragmented ids
+    kshape, vshape = kv_cache_shapes(NB, bs, H, D, torch.half)
+    g = torch.Generator(device=dev).manual_seed(1234 + (rank % npw))
+    kv = []
+    for _ in range(L):
+        if is_prompt:
+            k = torch.randint(-2 ** 15, 2 ** 15 - 1, kshape, dtype=torch.int16, device=dev, generator=g).view(torch.half)
+            v = torch.randint(-2 ** 15, 2 ** 15 - 1, vshape, dtype=torch.int16, device=dev, generator=g).view(torch.half)
+        else:
+            k = torch.zeros(kshape, dtype=torch.half, device=dev)
+            v = torch.zeros(vshape, dtype=torch.half, device=dev)
+        kv.append((k, v))
+    block_bytes = H * D * bs * 2
+
+    mgr = KVCacheCommManager(rank, world, npw, group=boot, device=dev)
+    mgr.setup_comm(L, kv)
+    assert mgr.kvcache_comm.block_size == block_bytes
+    mgr.kvcache_comm.max_ctas = args.max_ctas
+
+    def block_lists(pattern, seed):
+        rnd = random.Random(seed)
+        if pattern == "contiguous":
+            return [list(range(p * blocks_per_prompt, (p + 1) * blocks_per_prompt)) for p in range(args.prompts)]
+        ids = list(range(0, NB, 2))  # no two ids adjacent -> every run is a single block
+        rnd.shuffle(ids)
+        return [ids[p * blocks_per_prompt:(p + 1) * blocks_per_prompt] for p in range(args.prompts)]
+
+    def checksum(blocks):
+        """Sum over layers/K/V of the int64 words of the given blocks (wrapping) -- bit-exact fingerprint."""
+        idx = torch.tensor(sorted(blocks), device=dev)
+        tot = torch.zeros((), dtype=torch.int64, device=dev)
+        for k, v in kv:
+            tot += k.view(torch.int64).view(NB, -1)[idx].sum() + v.view(torch.int64).view(NB, -1)[idx].sum()
+        return tot
+
+    def total_sum():
+        tot = torch.zeros((), dtype=torch.int64, device=dev)
+        for k, v in kv:
+            tot += k.view(torch.int64).sum() + v.view(torch.int64).sum()
+        return tot
+
+    def clear_token_side():
+        if not is_prompt:
+            for k, v in kv:
+                k.zero_()
+                v.zero_()
+
+    def run_ours(lists, mode):
+        for p, blocks in enumerate(lists):
+            sem = p % 256
+            runs = coalesce_blocks(blocks)
+            if is_prompt:
+                if mode == "bulk":
+                    mgr.put_layers(sem, 0, L, runs)
+                else:
+                    for layer in range(L):
+                        mgr.put_runs(sem, layer, runs)
+                mgr.signal_and_flush(sem)
+            else:
+                mgr.wait(sem)
+
+    def run_nccl(lists):
+        for blocks in lists:
+            runs = coalesce_blocks(blocks)
+            for k, v in kv:
+                ops = []
+                for t in (k, v):
+                    for s, n in runs:
+                        ops.append(dist.P2POp(dist.isend if is_prompt else dist.irecv, t[s:s + n], peer))
+                for w in dist.batch_isend_irecv(ops):
+                    w.wait()
+
+    results = []
+    for pattern in args.patterns.split(","):
+        for mode in args.modes.split(","):
+            lists = block_lists(pattern, 7)
+            if mode == "nccl" and pattern == "fragmented":
+                lists = lists[:args.nccl_max_prompts]
+            nbytes = sum(len(b) for b in lists) * block_bytes * 2 * L
+            times = []
+            ok = True
+            for it in range(args.warmup + args.iters):
+                clear_token_side()
+                torch.cuda.synchronize()
+                dist.barrier()
+                beg, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                beg.record()
+                if mode == "nccl":
+                    run_nccl(lists)
+                else:
+                    run_ours(lists, mode)
+                end.record()
+                torch.cuda.synchronize()
+                ms = torch.tensor([beg.elapsed_time(end)], dtype=torch.float64, device=dev)
+                dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+                if it >= args.warmup:
+                    times.append(ms.item())
+                # ---- verify: moved blocks match the sender's fingerprint, nothing else was touched ----
+                moved = [b for bl in lists for b in bl]
+                fp = checksum(moved)
+                if is_prompt:
+                    dist.send(fp.view(1), peer)
+                else:
+                    theirs = torch.zeros(1, dtype=torch.int64, device=dev)
+                    dist.recv(theirs, peer)
+                    ok = ok and bool(theirs.item() == fp.item()) and bool(total_sum().item() == fp.item())
+                    if mode != "nccl":
+                        ok = ok and not mgr.kvcache_comm.timed_out()
+            okt = torch.tensor([1 if ok else 0], device=dev)
+            dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+            best, mean = min(times), sum(times) / len(times)
+            per_pair = nbytes / (mean * 1e-3) / 1e9
+            line = {"metric": "kv_transfer_bandwidth_per_gpu_pair", "value": round(per_pair, 2), "unit": "GB/s",
+                    "n_gpus": world, "pairs": npw, "pattern": pattern, "mode": mode, "prompts_in_flight": len(lists),
+                    "bytes_per_pair": nbytes, "ms_mean": round(mean, 4), "ms_best": round(best, 4),
+                    "best_GBps": round(nbytes / (best * 1e-3) / 1e9, 2),
+                    "aggregate_GBps": round(per_pair * npw, 2),
+                    "frac_of_nvlink_measured_770": round(per_pair / NVLINK_MEASURED_GBS, 4),
+                    "frac_of_nvlink_nominal_900": round(per_pair / NVLINK_NOMINAL_GBS, 4),
+                    "runs_per_prompt": len(coalesce_blocks(lists[0])), "bit_exact": bool(okt.item()),
+                    "config": {"workload": f"C5 Llama-2-13B tp=4 shard: {L} layers, {H} kv heads, head {D}, block {bs}, fp16, "
+                                           f"{args.prompt_tokens}-token prompts, {npw} prompt -> {npw} token GPUs"}}
+            results.append(line)
+            if rank == 0:
+                print(json.dumps(line), flush=True)
+    dist.barrier()
+    mgr.destroy_comm()
+    dist.destroy_process_group()
+    return 0 if all(r["bit_exact"] for r in results) else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())
