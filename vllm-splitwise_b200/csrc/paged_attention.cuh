@@ -83,6 +83,80 @@ __device__ __forceinline__ void load_unpack(const unsigned char* p, float* f) {
   }
 }
 
+// Merge the consumer warps' partial (max, sum, acc) states and write either the final output row or
+// the partition partials in the reference's tmp_out / exp_sums / max_logits format.
+// red_acc [NW][GT][D] f32, red_ml [NW][GT][2] f32 (shared memory).
+template <typename T, int D, int GT>
+__device__ __forceinline__ void attn_merge_store(const AttnParams& p, const float* red_acc, const float* red_ml,
+                                                 int ng, int seq, int head0, int part, int tid) {
+  constexpr int NW = kConsumerWarps;
+  T* out = static_cast<T*>(p.out);
+  for (int idx = tid; idx < ng * D; idx += kAttnThreads) {
+    const int g = idx / D, d = idx - g * D;
+    float M = -FLT_MAX;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) M = fmaxf(M, red_ml[(w * GT + g) * 2]);
+    float L = 0.f, A = 0.f;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+      const float sc = __expf(red_ml[(w * GT + g) * 2] - M);
+      L = fmaf(red_ml[(w * GT + g) * 2 + 1], sc, L);
+      A = fmaf(red_acc[(w * GT + g) * D + d], sc, A);
+    }
+    const float o = A * __fdividef(1.f, L + 1e-6f);
+    const long long sh = (long long)seq * p.num_heads + head0 + g;
+    if (p.write_partials) {
+      const long long pi = sh * p.max_num_partitions + part;
+      static_cast<T*>(p.tmp_out)[pi * D + d] = from_f32<T>(o);
+      if (d == 0) {
+        p.exp_sums[pi] = L;
+        p.max_logits[pi] = M;
+      }
+    } else {
+      out[sh * D + d] = from_f32<T>(o);
+    }
+  }
+}
+
+// Producer warp (shared by the SIMT and the tensor-core kernels): walks the block table of `seq`
+// from block b0 (32 entries per coalesced load, the next group prefetched while this one is issued)
+// and streams each (block, kv_head) chunk -- kbytes contiguous bytes of K, then of V -- into ring
+// stage n % nstages with two bulk copies completing on full_bar[stage].
+template <typename CT>
+__device__ __forceinline__ void attn_producer(const AttnParams& p, int seq, int kvh, int b0, int nblk, int lane,
+                                              unsigned char* stages, int stage_bytes, int kbytes,
+                                              uint64_t* full_bar, uint64_t* empty_bar) {
+  const int nst = p.nstages;
+  const int* table = p.block_tables + (long long)seq * p.max_num_blocks_per_seq + b0;
+  const unsigned char* kbase = static_cast<const unsigned char*>(p.k_cache) + (long long)kvh * p.kv_head_stride * (long long)sizeof(CT);
+  const unsigned char* vbase = static_cast<const unsigned char*>(p.v_cache) + (long long)kvh * p.kv_head_stride * (long long)sizeof(CT);
+  const long long blk_bytes = p.kv_block_stride * (long long)sizeof(CT);
+#ifdef B200_ATTN_NO_HINT
+  const uint64_t pol = 0;
+#else
+  const uint64_t pol = l2_policy_evict_first();
+#endif
+  int phys_next = lane < nblk ? table[lane] : 0;
+  int stage = 0, fill = 0;  // fill = how many times the ring has wrapped
+  for (int base = 0; base < nblk; base += 32) {
+    const int phys = phys_next;
+    const int nxt = base + 32 + lane;
+    phys_next = nxt < nblk ? table[nxt] : 0;  // in flight while this group is issued
+    const int cnt = min(32, nblk - base);
+    for (int j = 0; j < cnt; ++j) {
+      const long long pb = __shfl_sync(0xffffffffu, phys, j);
+      if (lane == 0) {
+        if (fill > 0) mbar_wait(&empty_bar[stage], (fill - 1) & 1);
+        unsigned char* dst = stages + (size_t)stage * stage_bytes;
+        mbar_arrive_expect_tx(&full_bar[stage], 2 * kbytes);
+        bulk_g2s(dst, kbase + pb * blk_bytes, kbytes, &full_bar[stage], pol);
+        bulk_g2s(dst + kbytes, vbase + pb * blk_bytes, kbytes, &full_bar[stage], pol);
+      }
+      if (++stage == nst) { stage = 0; ++fill; }
+    }
+  }
+}
+
 template <typename T, typename CT, int D, int BS, int GT>
 __global__ void __launch_bounds__(kAttnThreads) paged_attn_simt_kernel(const __grid_constant__ AttnParams p) {
   using SM = SimtSmem<CT, D, BS, GT>;
@@ -139,35 +213,7 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_simt_kernel(const __g
   __syncthreads();
 
   if (warp == NW) {
-    // ================= producer: block table -> bulk copies into the ring =================
-    const int* table = p.block_tables + (long long)seq * p.max_num_blocks_per_seq + b0;
-    const unsigned char* kbase = static_cast<const unsigned char*>(p.k_cache) + (long long)kvh * p.kv_head_stride * (long long)sizeof(CT);
-    const unsigned char* vbase = static_cast<const unsigned char*>(p.v_cache) + (long long)kvh * p.kv_head_stride * (long long)sizeof(CT);
-    const long long blk_bytes = p.kv_block_stride * (long long)sizeof(CT);
-#ifdef B200_ATTN_NO_HINT
-    const uint64_t pol = 0;
-#else
-    const uint64_t pol = l2_policy_evict_first();
-#endif
-    int phys_next = lane < nblk ? table[lane] : 0;
-    int stage = 0, fill = 0;  // fill = how many times the ring has wrapped
-    for (int base = 0; base < nblk; base += 32) {
-      const int phys = phys_next;
-      const int nxt = base + 32 + lane;
-      phys_next = nxt < nblk ? table[nxt] : 0;  // in flight while this group is issued
-      const int cnt = min(32, nblk - base);
-      for (int j = 0; j < cnt; ++j) {
-        const long long pb = __shfl_sync(0xffffffffu, phys, j);
-        if (lane == 0) {
-          if (fill > 0) mbar_wait(&empty_bar[stage], (fill - 1) & 1);
-          unsigned char* dst = stages + (size_t)stage * SM::kStageBytes;
-          mbar_arrive_expect_tx(&full_bar[stage], SM::kStageBytes);
-          bulk_g2s(dst, kbase + pb * blk_bytes, KB, &full_bar[stage], pol);
-          bulk_g2s(dst + KB, vbase + pb * blk_bytes, KB, &full_bar[stage], pol);
-        }
-        if (++stage == nst) { stage = 0; ++fill; }
-      }
-    }
+    attn_producer<CT>(p, seq, kvh, b0, nblk, lane, stages, SM::kStageBytes, KB, full_bar, empty_bar);
   } else {
     // ================= consumers: online softmax over ring stages =================
     constexpr int NVK = (D / X) * BS;           // 16-byte vectors in a K chunk
@@ -310,32 +356,7 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_simt_kernel(const __g
   }
   __syncthreads();
 
-  // ================= merge the consumer warps' partial states =================
-  for (int idx = tid; idx < ng * D; idx += kAttnThreads) {
-    const int g = idx / D, d = idx - g * D;
-    float M = -FLT_MAX;
-#pragma unroll
-    for (int w = 0; w < NW; ++w) M = fmaxf(M, red_ml[(w * GT + g) * 2]);
-    float L = 0.f, A = 0.f;
-#pragma unroll
-    for (int w = 0; w < NW; ++w) {
-      const float sc = __expf(red_ml[(w * GT + g) * 2] - M);
-      L = fmaf(red_ml[(w * GT + g) * 2 + 1], sc, L);
-      A = fmaf(red_acc[(w * GT + g) * D + d], sc, A);
-    }
-    const float o = A * __fdividef(1.f, L + 1e-6f);
-    const long long sh = (long long)seq * p.num_heads + head0 + g;
-    if (p.write_partials) {
-      const long long pi = sh * p.max_num_partitions + part;
-      static_cast<T*>(p.tmp_out)[pi * D + d] = from_f32<T>(o);
-      if (d == 0) {
-        p.exp_sums[pi] = L;
-        p.max_logits[pi] = M;
-      }
-    } else {
-      out[sh * D + d] = from_f32<T>(o);
-    }
-  }
+  attn_merge_store<T, D, GT>(p, red_acc, red_ml, ng, seq, head0, part, tid);
 }
 
 // Merge of partition partials; same formula as the reference's paged_attention_v2_reduce_kernel
