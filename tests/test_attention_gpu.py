@@ -224,6 +224,54 @@ def test_cuda_graph_capture_and_replay(ops):
 
 
 # ---------------------------------------------------------------------------------------------
+# grouped-query tile shapes of the tensor-core path: partial tiles, more than 8 and more than 16 query
+# heads per KV head (two CTA tiles), MQA; and the SIMT path forced on the same inputs
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("num_heads", [(2, 1), (6, 2), (12, 1), (32, 2), (40, 2), (48, 1)])
+@pytest.mark.parametrize("block_size", [16, 32])
+@pytest.mark.parametrize("dtype,kv_cache_dtype", [(torch.half, "auto"), (torch.bfloat16, "auto"),
+                                                  (torch.half, "fp8_e5m2"), (torch.bfloat16, "fp8_e5m2")])
+def test_group_tiles(ops, num_heads, block_size, dtype, kv_cache_dtype):
+    random.seed(7)
+    ctx = [1, 15, 16, 17, 31, 33, 257, 700, 1025]
+    a = make_attention_inputs(num_seqs=len(ctx), num_heads=num_heads, head_size=128, block_size=block_size,
+                              dtype=dtype, kv_cache_dtype=kv_cache_dtype, num_blocks=512, context_lens=ctx,
+                              use_alibi=(num_heads[0] % 4 == 0), seed=7)
+    ref = oracle_attention(a)
+    atol, rtol = (FP8_ATOL, FP8_RTOL) if kv_cache_dtype == "fp8_e5m2" else (ATOL, RTOL)
+    for out in (run_v1(ops, a), run_v2(ops, a)[0]):
+        ok, err = _close(out, ref, atol, rtol)
+        assert ok, f"max err {err}"
+
+
+@pytest.mark.parametrize("block_size", [16, 32])
+@pytest.mark.parametrize("dtype,kv_cache_dtype", [(torch.half, "auto"), (torch.bfloat16, "auto"),
+                                                  (torch.bfloat16, "fp8_e5m2")])
+def test_stale_tail_grouped(ops, dtype, kv_cache_dtype, block_size):
+    """NaN / Inf bit patterns in the slots past the context of the last block must not reach the
+    output on the tensor-core path either (0 * NaN inside an MMA would)."""
+    ctx = [1, 9, 21, 33, 47, 64]
+    a = make_attention_inputs(num_seqs=len(ctx), num_heads=(16, 2), head_size=128, block_size=block_size,
+                              dtype=dtype, kv_cache_dtype=kv_cache_dtype, num_blocks=64, context_lens=ctx,
+                              distinct_blocks=True)
+    ref = oracle_attention(a)
+    for s, c in enumerate(ctx):
+        blk = int(a["bt"][s, (c - 1) // block_size])
+        off = (c - 1) % block_size + 1
+        if kv_cache_dtype == "auto":
+            a["kc"][blk, :, :, off:, :] = float("nan")
+            a["vc"][blk, :, :, off:] = float("inf")
+        else:
+            a["kc"][blk, :, :, off:, :] = 0x7F   # e5m2 NaN
+            a["vc"][blk, :, :, off:] = 0x7C      # e5m2 +Inf
+    atol, rtol = (FP8_ATOL, FP8_RTOL) if kv_cache_dtype == "fp8_e5m2" else (ATOL, RTOL)
+    for out in (run_v1(ops, a), run_v2(ops, a)[0]):
+        assert torch.isfinite(out).all()
+        ok, err = _close(out, ref, atol, rtol)
+        assert ok, f"max err {err}"
+
+
+# ---------------------------------------------------------------------------------------------
 # BASELINE.json full-size shapes: size-independent properties + sampled oracle check
 # ---------------------------------------------------------------------------------------------
 FULL = {

@@ -2,7 +2,9 @@
 // Replaces the reference launchers (csrc/attention/attention_kernels.cu:606-747, 784-940).
 #include <algorithm>
 
-#include "paged_attention.cuh"
+#include <stdlib.h>
+
+#include "paged_attention_mma.cuh"
 
 namespace b200 {
 namespace {
@@ -55,6 +57,40 @@ AttnParams base_params(const b200_paged_attn_args_t* a) {
   return p;
 }
 
+// Which consumer path a call takes.  Grouped queries (more than one query head per KV head) in f16/bf16
+// with 16- or 32-token blocks go to the tensor-core kernel; everything else (MHA, fp32, block_size 8)
+// stays on the SIMT kernel, which is already at the HBM ceiling for MHA.
+struct TilePlan {
+  bool mma;
+  bool hi;   // mma: tile rows 8..15 in use (more than 8 query heads per KV head)
+  int gt;    // query heads per CTA
+};
+
+TilePlan plan_tile(const b200_paged_attn_args_t* a) {
+  const int group = a->num_heads / a->num_kv_heads;
+  TilePlan t{false, false, group == 1 ? 1 : 8};
+  static const bool force_simt = getenv("B200_ATTN_FORCE_SIMT") != nullptr;  // A/B knob for benchmarks and tests
+  if (!force_simt && group > 1 && (a->query_dtype == B200_F16 || a->query_dtype == B200_BF16) &&
+      (a->block_size == 16 || a->block_size == 32)) {
+    t.mma = true;
+    t.hi = group > 8;
+    t.gt = t.hi ? 16 : 8;
+  }
+  return t;
+}
+
+int dispatch_mma(const b200_paged_attn_args_t* a, const AttnParams& p, bool hi, dim3 grid, int smem_budget,
+                 cudaStream_t stream) {
+  const bool fp8 = a->cache_dtype == B200_U8_E5M2;
+  if (a->query_dtype == B200_F16)
+    return fp8 ? launch_mma<__half, uint8_t>(p, a->head_size, a->block_size, hi, grid, smem_budget, stream)
+               : launch_mma<__half, __half>(p, a->head_size, a->block_size, hi, grid, smem_budget, stream);
+  if (a->query_dtype == B200_BF16)
+    return fp8 ? launch_mma<__nv_bfloat16, uint8_t>(p, a->head_size, a->block_size, hi, grid, smem_budget, stream)
+               : launch_mma<__nv_bfloat16, __nv_bfloat16>(p, a->head_size, a->block_size, hi, grid, smem_budget, stream);
+  return B200_ERR_DTYPE;
+}
+
 int dispatch_simt(const b200_paged_attn_args_t* a, const AttnParams& p, int gt, dim3 grid,
                   int smem_budget, cudaStream_t stream) {
   const bool fp8 = a->cache_dtype == B200_U8_E5M2;
@@ -100,13 +136,21 @@ int launch_reduce(const b200_paged_attn_args_t* a, void* out, const float* exp_s
 
 // Shared-memory budget per CTA: aim for two resident CTAs per SM (2 x ~110 KiB of the 227 KiB),
 // fall back to one when a single ring stage is too large for that (fp32, D=256, bs=32).
-int pick_smem_budget(const b200_paged_attn_args_t* a, int gt) {
+int pick_smem_budget(const b200_paged_attn_args_t* a, const TilePlan& t) {
   const int stage = 2 * a->head_size * a->block_size * dtype_size(a->cache_dtype);
-  const int fixed = gt * a->head_size * 4 + kConsumerWarps * gt * a->block_size * 4 +
-                    kConsumerWarps * gt * a->head_size * 4 + kConsumerWarps * gt * 8 + 512;
+  const int gt = t.gt;
+  const int fixed = t.mma ? kConsumerWarps * kMmaHeads * 8 + 512
+                          : gt * a->head_size * 4 + kConsumerWarps * gt * a->block_size * 4 +
+                                kConsumerWarps * gt * a->head_size * 4 + kConsumerWarps * gt * 8 + 512;
   const int two = 112 * 1024;
-  if ((two - fixed) / stage >= 4) return two;
+  const int merge = t.mma ? kConsumerWarps * kMmaHeads * a->head_size * 4 : 0;  // aliased onto the ring
+  if ((two - fixed) / stage >= 4 && (two - fixed) / stage / 4 * 4 * stage >= merge) return two;
   return 226 * 1024;
+}
+
+int dispatch(const b200_paged_attn_args_t* a, const AttnParams& p, const TilePlan& t, dim3 grid, cudaStream_t stream) {
+  const int budget = pick_smem_budget(a, t);
+  return t.mma ? dispatch_mma(a, p, t.hi, grid, budget, stream) : dispatch_simt(a, p, t.gt, grid, budget, stream);
 }
 
 // Internal split of a v1 call (needs caller workspace): choose the partition length so that the
@@ -149,9 +193,9 @@ B200_API int b200_paged_attention_v1(const b200_paged_attn_args_t* a, b200_strea
   B200_CUDA_TRY(guard.set(a->device));
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   AttnParams p = base_params(a);
-  const int gt = p.group == 1 ? 1 : 8;
+  const TilePlan tile = plan_tile(a);
+  const int gt = tile.gt;
   p.gtiles = (p.group + gt - 1) / gt;
-  const int budget = pick_smem_budget(a, gt);
   int pb = 0, np = 1;
   if (plan_v1_split(a, p.gtiles, num_sms(a->device), &pb, &np)) {
     // carve the workspace: tmp_out | exp_sums | max_logits
@@ -166,7 +210,7 @@ B200_API int b200_paged_attention_v1(const b200_paged_attn_args_t* a, b200_strea
     p.max_num_partitions = np;
     p.write_partials = 1;
     dim3 grid(a->num_kv_heads * p.gtiles, a->num_seqs, np);
-    st = dispatch_simt(a, p, gt, grid, budget, stream);
+    st = dispatch(a, p, tile, grid, stream);
     if (st != B200_OK) return st;
     return launch_reduce(a, a->out, p.exp_sums, p.max_logits, p.tmp_out, np, pb * a->block_size, stream);
   }
@@ -174,7 +218,7 @@ B200_API int b200_paged_attention_v1(const b200_paged_attn_args_t* a, b200_strea
   p.max_num_partitions = 1;
   p.write_partials = 0;
   dim3 grid(a->num_kv_heads * p.gtiles, a->num_seqs, 1);
-  return dispatch_simt(a, p, gt, grid, budget, stream);
+  return dispatch(a, p, tile, grid, stream);
 }
 
 B200_API int b200_paged_attention_v2(const b200_paged_attn_args_t* a, b200_stream_t stream_) {
@@ -186,7 +230,8 @@ B200_API int b200_paged_attention_v2(const b200_paged_attn_args_t* a, b200_strea
   B200_CUDA_TRY(guard.set(a->device));
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   AttnParams p = base_params(a);
-  const int gt = p.group == 1 ? 1 : 8;
+  const TilePlan tile = plan_tile(a);
+  const int gt = tile.gt;
   p.gtiles = (p.group + gt - 1) / gt;
   p.exp_sums = a->exp_sums;
   p.max_logits = a->max_logits;
@@ -198,7 +243,7 @@ B200_API int b200_paged_attention_v2(const b200_paged_attn_args_t* a, b200_strea
   int np = (a->max_context_len + kV2PartitionTokens - 1) / kV2PartitionTokens;
   np = std::max(1, std::min(np, a->max_num_partitions));
   dim3 grid(a->num_kv_heads * p.gtiles, a->num_seqs, np);
-  st = dispatch_simt(a, p, gt, grid, pick_smem_budget(a, gt), stream);
+  st = dispatch(a, p, tile, grid, stream);
   if (st != B200_OK) return st;
   return launch_reduce(a, a->out, a->exp_sums, a->max_logits, a->tmp_out, a->max_num_partitions,
                        kV2PartitionTokens, stream);
