@@ -82,9 +82,13 @@ B200_API uint64_t b200_kv_launch_count(void);
  * v2 only (caller-allocated scratch, reference paged_attn.py:83-93), P = max_num_partitions:
  *   tmp_out [num_seqs, num_heads, P, head_size] T; exp_sums, max_logits f32 [num_seqs, num_heads, P]
  *   partition p covers tokens [512p, 512p+512) exactly as in the reference.
- * Optional workspace (v1 only): when the (seq, kv_head) grid cannot fill the GPU the library may
- *   split the context and merge in a second kernel; it needs b200_paged_attention_workspace_bytes()
- *   bytes of caller-owned scratch.  workspace == NULL disables splitting (never an error).
+ * Optional workspace (v1 only): the library may split contexts into partitions so that its persistent
+ *   grid stays evenly loaded, and combine the partials inside the same kernel; it needs up to
+ *   b200_paged_attention_workspace_bytes() bytes of caller-owned scratch (less is fine: the split is
+ *   limited to what fits).  The first 256 KiB hold reduce tickets: they must be ZERO before the first
+ *   call that uses the buffer and every call leaves them zero again, so one cudaMemset at allocation
+ *   is enough; do not share one workspace between calls that may run concurrently.
+ *   workspace == NULL disables splitting (never an error).
  * ------------------------------------------------------------------------------------------ */
 typedef struct {
   void* out;

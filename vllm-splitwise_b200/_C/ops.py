@@ -12,7 +12,7 @@ from .. import _lib
 from ._common import device_ctx, dtype_code, require_cuda, stream_ptr
 
 _workspaces = {}  # device index -> uint8 tensor (scratch for the internal split of v1 calls)
-_WORKSPACE_CAP = 512 << 20
+_WORKSPACE_CAP = 256 << 20
 
 
 def _cache_dtype_code(kv_cache_dtype: str, query: torch.Tensor, cache: torch.Tensor) -> int:
@@ -77,7 +77,9 @@ def _workspace_for(a: _lib.PagedAttnArgs, device: torch.device) -> Optional[torc
     if ws is None or ws.numel() < need:
         if torch.cuda.is_current_stream_capturing():
             return ws  # never allocate inside a CUDA-graph capture; use what exists (or none)
-        ws = torch.empty(need, dtype=torch.uint8, device=device)
+        # zero-filled: the head of the workspace holds the in-kernel reduce tickets, which every call
+        # leaves at zero again (include/b200_kv.h)
+        ws = torch.zeros(need, dtype=torch.uint8, device=device)
         _workspaces[device.index] = ws
     return ws
 
@@ -89,9 +91,9 @@ def paged_attention_v1(out: torch.Tensor, query: torch.Tensor, key_cache: torch.
                        kv_cache_dtype: str) -> None:
     a = _fill_args(out, query, key_cache, value_cache, num_kv_heads, scale, block_tables,
                    context_lens, block_size, max_context_len, alibi_slopes, kv_cache_dtype)
-    # A small (seq, kv_head) grid cannot fill 148 SMs: give the library scratch so it may split
-    # the context internally.  Large grids never use it, so skip the bookkeeping.
-    if a.num_seqs * a.num_kv_heads < 592 and a.max_context_len >= 512:
+    # Scratch that lets the library split long contexts into partitions so that the persistent grid's last
+    # round is full whatever the batch / head count is (partials are combined inside the same kernel).
+    if a.max_context_len >= 256:
         ws = _workspace_for(a, query.device)
         if ws is not None:
             a.workspace = ws.data_ptr()

@@ -211,6 +211,16 @@ template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; 
 template <> __device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
 template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
 
+// load past L1 (data written by another CTA of the same launch)
+template <typename T> __device__ __forceinline__ float ldcg_f32(const T* p);
+template <> __device__ __forceinline__ float ldcg_f32<float>(const float* p) { return __ldcg(p); }
+template <> __device__ __forceinline__ float ldcg_f32<__half>(const __half* p) {
+  return __half2float(__ushort_as_half(__ldcg(reinterpret_cast<const unsigned short*>(p))));
+}
+template <> __device__ __forceinline__ float ldcg_f32<__nv_bfloat16>(const __nv_bfloat16* p) {
+  return __bfloat162float(__ushort_as_bfloat16(__ldcg(reinterpret_cast<const unsigned short*>(p))));
+}
+
 template <typename T> __device__ __forceinline__ T from_f32(float v);
 template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
 template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }

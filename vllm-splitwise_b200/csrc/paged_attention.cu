@@ -1,6 +1,7 @@
 // Host side of b200_paged_attention_v1/v2: argument checks, grid/partition planning, dispatch.
 // Replaces the reference launchers (csrc/attention/attention_kernels.cu:606-747, 784-940).
 #include <algorithm>
+#include <atomic>
 
 #include <stdlib.h>
 
@@ -49,6 +50,7 @@ AttnParams base_params(const b200_paged_attn_args_t* a) {
   p.scale = a->scale;
   p.num_heads = a->num_heads;
   p.num_kv_heads = a->num_kv_heads;
+  p.num_seqs = a->num_seqs;
   p.group = a->num_heads / a->num_kv_heads;
   p.max_num_blocks_per_seq = a->max_num_blocks_per_seq;
   p.q_stride = a->q_stride;
@@ -79,98 +81,150 @@ TilePlan plan_tile(const b200_paged_attn_args_t* a) {
   return t;
 }
 
-int dispatch_mma(const b200_paged_attn_args_t* a, const AttnParams& p, bool hi, dim3 grid, int smem_budget,
-                 cudaStream_t stream) {
+int dispatch_mma(const b200_paged_attn_args_t* a, const AttnParams& p, int gt, int budget, int sms, cudaStream_t stream) {
   const bool fp8 = a->cache_dtype == B200_U8_E5M2;
   if (a->query_dtype == B200_F16)
-    return fp8 ? launch_mma<__half, uint8_t>(p, a->head_size, a->block_size, hi, grid, smem_budget, stream)
-               : launch_mma<__half, __half>(p, a->head_size, a->block_size, hi, grid, smem_budget, stream);
+    return fp8 ? launch_mma<__half, uint8_t>(p, a->head_size, a->block_size, gt, budget, sms, stream)
+               : launch_mma<__half, __half>(p, a->head_size, a->block_size, gt, budget, sms, stream);
   if (a->query_dtype == B200_BF16)
-    return fp8 ? launch_mma<__nv_bfloat16, uint8_t>(p, a->head_size, a->block_size, hi, grid, smem_budget, stream)
-               : launch_mma<__nv_bfloat16, __nv_bfloat16>(p, a->head_size, a->block_size, hi, grid, smem_budget, stream);
+    return fp8 ? launch_mma<__nv_bfloat16, uint8_t>(p, a->head_size, a->block_size, gt, budget, sms, stream)
+               : launch_mma<__nv_bfloat16, __nv_bfloat16>(p, a->head_size, a->block_size, gt, budget, sms, stream);
   return B200_ERR_DTYPE;
 }
 
-int dispatch_simt(const b200_paged_attn_args_t* a, const AttnParams& p, int gt, dim3 grid,
-                  int smem_budget, cudaStream_t stream) {
+int dispatch_simt(const b200_paged_attn_args_t* a, const AttnParams& p, int gt, int budget, int sms, cudaStream_t stream) {
   const bool fp8 = a->cache_dtype == B200_U8_E5M2;
+  const int hs = a->head_size, bs = a->block_size;
   switch (a->query_dtype) {
     case B200_F32:
-      return fp8 ? launch_simt<float, uint8_t>(p, a->head_size, a->block_size, gt, grid, smem_budget, stream)
-                 : launch_simt<float, float>(p, a->head_size, a->block_size, gt, grid, smem_budget, stream);
+      return fp8 ? launch_simt<float, uint8_t>(p, hs, bs, gt, budget, sms, stream)
+                 : launch_simt<float, float>(p, hs, bs, gt, budget, sms, stream);
     case B200_F16:
-      return fp8 ? launch_simt<__half, uint8_t>(p, a->head_size, a->block_size, gt, grid, smem_budget, stream)
-                 : launch_simt<__half, __half>(p, a->head_size, a->block_size, gt, grid, smem_budget, stream);
+      return fp8 ? launch_simt<__half, uint8_t>(p, hs, bs, gt, budget, sms, stream)
+                 : launch_simt<__half, __half>(p, hs, bs, gt, budget, sms, stream);
     case B200_BF16:
-      return fp8 ? launch_simt<__nv_bfloat16, uint8_t>(p, a->head_size, a->block_size, gt, grid, smem_budget, stream)
-                 : launch_simt<__nv_bfloat16, __nv_bfloat16>(p, a->head_size, a->block_size, gt, grid, smem_budget, stream);
+      return fp8 ? launch_simt<__nv_bfloat16, uint8_t>(p, hs, bs, gt, budget, sms, stream)
+                 : launch_simt<__nv_bfloat16, __nv_bfloat16>(p, hs, bs, gt, budget, sms, stream);
     default:
       return B200_ERR_DTYPE;
   }
 }
 
-int launch_reduce(const b200_paged_attn_args_t* a, void* out, const float* exp_sums, const float* max_logits,
-                  const void* tmp_out, int max_parts, int partition_tokens, cudaStream_t stream) {
-  dim3 grid(a->num_heads, a->num_seqs);
-  const size_t smem = (size_t)max_parts * sizeof(float);
-  switch (a->query_dtype) {
-    case B200_F32:
-      paged_attn_reduce_kernel<float><<<grid, 128, smem, stream>>>((float*)out, exp_sums, max_logits, (const float*)tmp_out,
-                                                                   a->context_lens, a->head_size, max_parts, partition_tokens);
-      break;
-    case B200_F16:
-      paged_attn_reduce_kernel<__half><<<grid, 128, smem, stream>>>((__half*)out, exp_sums, max_logits, (const __half*)tmp_out,
-                                                                    a->context_lens, a->head_size, max_parts, partition_tokens);
-      break;
-    case B200_BF16:
-      paged_attn_reduce_kernel<__nv_bfloat16><<<grid, 128, smem, stream>>>((__nv_bfloat16*)out, exp_sums, max_logits,
-                                                                           (const __nv_bfloat16*)tmp_out, a->context_lens,
-                                                                           a->head_size, max_parts, partition_tokens);
-      break;
-    default:
-      return B200_ERR_DTYPE;
-  }
+// Merge of the v2 partials in a second kernel, launched with programmatic stream serialization so that its
+// launch overlaps the attention kernel's tail (the kernel orders itself with griddepcontrol.wait).
+template <typename T>
+int launch_reduce_t(const b200_paged_attn_args_t* a, int max_parts, int partition_tokens, cudaStream_t stream) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(a->num_heads, a->num_seqs);
+  cfg.blockDim = dim3(128);
+  cfg.dynamicSmemBytes = (size_t)max_parts * sizeof(float);
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, paged_attn_reduce_kernel<T>, static_cast<T*>(a->out),
+                                   static_cast<const float*>(a->exp_sums), static_cast<const float*>(a->max_logits),
+                                   static_cast<const T*>(a->tmp_out), a->context_lens, (int)a->head_size, max_parts,
+                                   partition_tokens));
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
 
-// Shared-memory budget per CTA: aim for two resident CTAs per SM (2 x ~110 KiB of the 227 KiB),
-// fall back to one when a single ring stage is too large for that (fp32, D=256, bs=32).
-int pick_smem_budget(const b200_paged_attn_args_t* a, const TilePlan& t) {
+int launch_reduce(const b200_paged_attn_args_t* a, int max_parts, int partition_tokens, cudaStream_t stream) {
+  switch (a->query_dtype) {
+    case B200_F32: return launch_reduce_t<float>(a, max_parts, partition_tokens, stream);
+    case B200_F16: return launch_reduce_t<__half>(a, max_parts, partition_tokens, stream);
+    case B200_BF16: return launch_reduce_t<__nv_bfloat16>(a, max_parts, partition_tokens, stream);
+    default: return B200_ERR_DTYPE;
+  }
+}
+
+// Shared-memory budget per CTA: aim for two resident CTAs per SM (2 x ~112 KiB of the 227 KiB), fall back
+// to one when a ring of 4 stages does not fit in that (fp32, D=256, bs=32).
+int pick_smem_budget(const b200_paged_attn_args_t* a, const TilePlan& t, int* ctas_per_sm) {
   const int stage = 2 * a->head_size * a->block_size * dtype_size(a->cache_dtype);
-  const int gt = t.gt;
-  const int fixed = t.mma ? kConsumerWarps * kMmaHeads * 8 + 512
-                          : gt * a->head_size * 4 + kConsumerWarps * gt * a->block_size * 4 +
-                                kConsumerWarps * gt * a->head_size * 4 + kConsumerWarps * gt * 8 + 512;
+  const int fixed = t.mma ? 0 : t.gt * a->head_size * 4 + kConsumerWarps * t.gt * a->block_size * 4;
+  const int tail = fixed + kConsumerWarps * t.gt * a->head_size * 4 + kConsumerWarps * t.gt * 8 + 16 + kItemQueue * 8 +
+                   2 * kMaxStages * 8 + 2 * kItemQueue * 8;
   const int two = 112 * 1024;
-  const int merge = t.mma ? kConsumerWarps * kMmaHeads * a->head_size * 4 : 0;  // aliased onto the ring
-  if ((two - fixed) / stage >= 4 && (two - fixed) / stage / 4 * 4 * stage >= merge) return two;
+  if ((two - tail) / stage >= 4) {
+    *ctas_per_sm = 2;
+    return two;
+  }
+  *ctas_per_sm = 1;
   return 226 * 1024;
 }
 
-int dispatch(const b200_paged_attn_args_t* a, const AttnParams& p, const TilePlan& t, dim3 grid, cudaStream_t stream) {
-  const int budget = pick_smem_budget(a, t);
-  return t.mma ? dispatch_mma(a, p, t.hi, grid, budget, stream) : dispatch_simt(a, p, t.gt, grid, budget, stream);
+int dispatch(const b200_paged_attn_args_t* a, const AttnParams& p, const TilePlan& t, int budget, int sms,
+             cudaStream_t stream) {
+  return t.mma ? dispatch_mma(a, p, t.gt, budget, sms, stream) : dispatch_simt(a, p, t.gt, budget, sms, stream);
 }
 
-// Internal split of a v1 call (needs caller workspace): choose the partition length so that the
-// grid covers the SMs a few times over; 0 = do not split.
-int plan_v1_split(const b200_paged_attn_args_t* a, int gtiles, int sms, int* partition_blocks, int* num_parts) {
+// Work counters of the persistent kernel: one per launch in flight, handed out round-robin.  A launch
+// leaves its counter at zero, so a slot is reusable as soon as that launch has finished; 1024 slots means
+// a collision needs more than a thousand attention launches in flight at once on one device.
+constexpr unsigned kSchedSlots = 1024;
+__device__ unsigned int g_sched[kSchedSlots];
+std::atomic<unsigned> g_sched_seq{0};
+
+int attach_sched(AttnParams& p) {
+  static unsigned int* base[64] = {nullptr};
+  int dev = 0;
+  B200_CUDA_TRY(cudaGetDevice(&dev));
+  dev &= 63;
+  if (!base[dev]) {
+    void* sym = nullptr;
+    B200_CUDA_TRY(cudaGetSymbolAddress(&sym, g_sched));
+    base[dev] = static_cast<unsigned int*>(sym);
+  }
+  p.sched = base[dev] + (g_sched_seq.fetch_add(1, std::memory_order_relaxed) % kSchedSlots);
+  return B200_OK;
+}
+
+constexpr int kTicketInts = 1 << 16;                       // head of the v1 workspace: in-kernel reduce tickets
+constexpr int64_t kTicketBytes = (int64_t)kTicketInts * 4;
+constexpr int kMaxSplit = 64;
+
+// Internal split of a v1 call (needs caller workspace).  The persistent grid runs `slots` CTAs; CTA c takes
+// items c, c + slots, ...  With equal contexts the call lasts ceil(items / slots) rounds of
+// (partition_blocks + per-item overhead) block times, so choose the partition count that minimises that:
+// it fills the last round without making items so small that the per-item epilogue shows.
+int plan_v1_split(const b200_paged_attn_args_t* a, int tiles_per_seq, int slots, int* partition_blocks) {
   *partition_blocks = 0;
-  *num_parts = 1;
-  const long long ctas = (long long)a->num_seqs * a->num_kv_heads * gtiles;
+  const long long base_items = (long long)a->num_seqs * tiles_per_seq;
   const int max_blocks = (a->max_context_len + a->block_size - 1) / a->block_size;
-  if (!a->workspace || ctas >= 2LL * sms * 2 || max_blocks < 32) return 0;
-  int want = (int)std::min<long long>((4LL * sms + ctas - 1) / ctas, 64);
-  int pb = std::max(16, (max_blocks + want - 1) / want);
-  int np = (max_blocks + pb - 1) / pb;
-  if (np <= 1) return 0;
-  const long long need = (long long)a->num_seqs * a->num_heads * np *
-                         ((long long)a->head_size * dtype_size(a->query_dtype) + 8);
-  if (need > a->workspace_bytes) return 0;
-  *partition_blocks = pb;
-  *num_parts = np;
-  return 1;
+  if (!a->workspace || base_items > kTicketInts || max_blocks < 16) return 1;
+  if (const char* e = getenv("B200_ATTN_SPLIT")) {  // tuning knob: force a partition count
+    const int np = std::max(1, std::min(atoi(e), kMaxSplit));
+    if (np == 1) return 1;
+    *partition_blocks = (max_blocks + np - 1) / np;
+    return (max_blocks + *partition_blocks - 1) / *partition_blocks;
+  }
+  const double overhead = 2.0;  // per-item prologue + epilogue, in block times
+  const int min_pb = 8;
+  double best_cost = 0;
+  int best_np = 1, best_pb = 0;
+  for (int np = 1; np <= kMaxSplit; ++np) {
+    const int pb = (max_blocks + np - 1) / np;
+    if (np > 1 && pb < min_pb) break;
+    const int np_eff = (max_blocks + pb - 1) / pb;
+    if (np_eff != np) continue;
+    const long long rounds = (base_items * np + slots - 1) / slots;
+    double cost = (double)rounds * (pb + overhead);
+    if (np > 1) cost *= 1.03;  // partials cost a little: prefer no split on a near tie
+    const long long need = kTicketBytes + base_items / tiles_per_seq * a->num_heads * np *
+                                              ((long long)a->head_size * dtype_size(a->query_dtype) + 8) + 64;
+    if (np > 1 && need > a->workspace_bytes) break;
+    if (np == 1 || cost < best_cost) {
+      best_cost = cost;
+      best_np = np;
+      best_pb = np == 1 ? 0 : pb;
+    }
+  }
+  *partition_blocks = best_pb;
+  return best_np;
 }
 
 }  // namespace
@@ -182,8 +236,9 @@ extern "C" {
 
 B200_API int64_t b200_paged_attention_workspace_bytes(const b200_paged_attn_args_t* a) {
   if (!a || a->num_seqs <= 0 || a->num_heads <= 0) return 0;
-  // upper bound used by plan_v1_split: at most 64 partitions
-  return (int64_t)a->num_seqs * a->num_heads * 64 * ((int64_t)a->head_size * dtype_size(a->query_dtype) + 8);
+  // tickets + room for the largest split plan_v1_split may choose
+  return kTicketBytes + 64 +
+         (int64_t)a->num_seqs * a->num_heads * kMaxSplit * ((int64_t)a->head_size * dtype_size(a->query_dtype) + 8);
 }
 
 B200_API int b200_paged_attention_v1(const b200_paged_attn_args_t* a, b200_stream_t stream_) {
@@ -194,31 +249,31 @@ B200_API int b200_paged_attention_v1(const b200_paged_attn_args_t* a, b200_strea
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   AttnParams p = base_params(a);
   const TilePlan tile = plan_tile(a);
-  const int gt = tile.gt;
-  p.gtiles = (p.group + gt - 1) / gt;
-  int pb = 0, np = 1;
-  if (plan_v1_split(a, p.gtiles, num_sms(a->device), &pb, &np)) {
-    // carve the workspace: tmp_out | exp_sums | max_logits
+  p.gtiles = (p.group + tile.gt - 1) / tile.gt;
+  p.tiles_per_seq = a->num_kv_heads * p.gtiles;
+  const int sms = num_sms(a->device);
+  int ctas_per_sm = 2;
+  const int budget = pick_smem_budget(a, tile, &ctas_per_sm);
+  int pb = 0;
+  const int np = plan_v1_split(a, p.tiles_per_seq, ctas_per_sm * sms, &pb);
+  p.partition_blocks = pb;
+  p.max_num_partitions = np;
+  p.always_partials = 0;
+  if (np > 1) {
+    // carve the workspace: tickets | tmp_out | exp_sums | max_logits
     const long long rows = (long long)a->num_seqs * a->num_heads * np;
     unsigned char* ws = static_cast<unsigned char*>(a->workspace);
-    p.tmp_out = ws;
-    long long off = rows * a->head_size * dtype_size(a->query_dtype);
+    p.tickets = reinterpret_cast<int*>(ws);
+    p.tmp_out = ws + kTicketBytes;
+    long long off = kTicketBytes + rows * a->head_size * dtype_size(a->query_dtype);
     off = (off + 15) / 16 * 16;
     p.exp_sums = reinterpret_cast<float*>(ws + off);
     p.max_logits = p.exp_sums + rows;
-    p.partition_blocks = pb;
-    p.max_num_partitions = np;
-    p.write_partials = 1;
-    dim3 grid(a->num_kv_heads * p.gtiles, a->num_seqs, np);
-    st = dispatch(a, p, tile, grid, stream);
-    if (st != B200_OK) return st;
-    return launch_reduce(a, a->out, p.exp_sums, p.max_logits, p.tmp_out, np, pb * a->block_size, stream);
   }
-  p.partition_blocks = 0;
-  p.max_num_partitions = 1;
-  p.write_partials = 0;
-  dim3 grid(a->num_kv_heads * p.gtiles, a->num_seqs, 1);
-  return dispatch(a, p, tile, grid, stream);
+  p.total_items = (long long)np * a->num_seqs * p.tiles_per_seq;
+  st = attach_sched(p);
+  if (st != B200_OK) return st;
+  return dispatch(a, p, tile, budget, sms, stream);
 }
 
 B200_API int b200_paged_attention_v2(const b200_paged_attn_args_t* a, b200_stream_t stream_) {
@@ -231,22 +286,26 @@ B200_API int b200_paged_attention_v2(const b200_paged_attn_args_t* a, b200_strea
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   AttnParams p = base_params(a);
   const TilePlan tile = plan_tile(a);
-  const int gt = tile.gt;
-  p.gtiles = (p.group + gt - 1) / gt;
+  p.gtiles = (p.group + tile.gt - 1) / tile.gt;
+  p.tiles_per_seq = a->num_kv_heads * p.gtiles;
   p.exp_sums = a->exp_sums;
   p.max_logits = a->max_logits;
   p.tmp_out = a->tmp_out;
   p.partition_blocks = kV2PartitionTokens / a->block_size;
   p.max_num_partitions = a->max_num_partitions;
-  p.write_partials = 1;
+  p.always_partials = 1;
   // partitions actually needed for max_context_len (never more than the caller's scratch holds)
   int np = (a->max_context_len + kV2PartitionTokens - 1) / kV2PartitionTokens;
   np = std::max(1, std::min(np, a->max_num_partitions));
-  dim3 grid(a->num_kv_heads * p.gtiles, a->num_seqs, np);
-  st = dispatch(a, p, tile, grid, stream);
+  p.total_items = (long long)np * a->num_seqs * p.tiles_per_seq;
+  const int sms = num_sms(a->device);
+  int ctas_per_sm = 2;
+  const int budget = pick_smem_budget(a, tile, &ctas_per_sm);
+  st = attach_sched(p);
   if (st != B200_OK) return st;
-  return launch_reduce(a, a->out, a->exp_sums, a->max_logits, a->tmp_out, a->max_num_partitions,
-                       kV2PartitionTokens, stream);
+  st = dispatch(a, p, tile, budget, sms, stream);
+  if (st != B200_OK) return st;
+  return launch_reduce(a, a->max_num_partitions, kV2PartitionTokens, stream);
 }
 
 }  // extern "C"

@@ -1,23 +1,28 @@
-// Paged-KV attention decode for sm_100a: kernel templates.
+// Paged-KV attention decode for sm_100a: persistent kernel skeleton + the SIMT consumer.
 //
 // Replaces the reference's paged_attention_kernel / v1 / v2 / v2_reduce
 // (csrc/attention/attention_kernels.cu:83-575).  Same math (fp32 logits, fp32 softmax with the
 // 1e-6 guard on the denominator, fp32 P.V accumulation, tail tokens of the last block masked on
 // both the logit and the V side) -- different execution model:
 //
-//  * grid = (kv_head x q-group tile, seq, partition): the query heads that share a KV head are
-//    processed by ONE CTA, so every KV block is read from HBM once per KV head (the reference
-//    reads it once per QUERY head, grid.x = num_heads, attention_kernels.cu:131-134).
-//  * a producer warp walks the block table (32 entries per coalesced load, prefetched one group
-//    ahead) and streams each (block, kv_head) chunk -- contiguous D*bs*elt bytes for K and for V --
-//    into a shared-memory ring with cp.async.bulk (TMA engine, SASS UBLKCP) completing on
-//    mbarriers.  Tens of KiB are in flight per SM without costing a register.
-//  * consumer warps take ring stages round-robin and run an online (flash-decoding) softmax, so
+//  * PERSISTENT grid: (resident CTAs per SM) x (SM count) CTAs loop over work items
+//    (partition, sequence, kv-head tile).  All query heads that share a KV head are processed by ONE
+//    item, so every KV block is read from HBM once per KV head (the reference reads it once per QUERY
+//    head, grid.x = num_heads, attention_kernels.cu:131-134).  Items are small (a partition of the
+//    context), so 148 SMs stay evenly loaded whatever the batch / head count is, and the copy pipeline
+//    below never drains between items.
+//  * a producer warp walks the block table (one coalesced load per group of ring slots) and streams each
+//    (block, kv_head) chunk -- contiguous D*bs*elt bytes for K and for V -- into a shared-memory ring
+//    with cp.async.bulk (TMA engine, SASS UBLKCP) completing on mbarriers; each lane owns one ring slot,
+//    so address math and barrier polls run 16-32 wide and only the copy issue itself is serial.
+//  * consumer warps own ring slots round-robin and run an online (flash-decoding) softmax, so
 //    shared memory is O(stage), not O(context) as in the reference's v1 (attention_kernels.cu:640-649),
-//    and the context is walked once, not twice.
-//  * per-warp partial states are merged once at the end; with partitions (v2, or the internal
-//    split used to fill the GPU) the partial state goes out in the reference's own
-//    tmp_out / exp_sums / max_logits format.
+//    and the context is walked once, not twice.  Two consumers exist: SIMT (this file; MHA, fp32,
+//    block_size 8) and warp-level tensor cores (paged_attention_mma.cuh; grouped queries).
+//  * per-warp partial states are merged per item; with partitions the partial state goes out in the
+//    reference's own tmp_out / exp_sums / max_logits format and is combined either by the last CTA to
+//    finish a sequence's partitions (v1, in-kernel, self-resetting tickets) or by
+//    paged_attn_reduce_kernel (v2 signature, the reference's formula :484-575).
 #pragma once
 
 #include <float.h>
@@ -37,38 +42,326 @@ struct AttnParams {
   float* exp_sums;
   float* max_logits;
   void* tmp_out;
+  int* tickets;          // [num_seqs * tiles_per_seq], zero between launches; non-null = in-kernel reduce
+  unsigned int* sched;   // work counter of this launch (zero between launches, self-resetting)
   float scale;
+  int num_seqs;
   int num_heads;
   int num_kv_heads;
   int group;             // num_heads / num_kv_heads
   int gtiles;            // ceil(group / GT)
+  int tiles_per_seq;     // num_kv_heads * gtiles
   int max_num_blocks_per_seq;
   int partition_blocks;  // KV blocks per partition; 0 = whole context
   int max_num_partitions;
-  int write_partials;    // 1: tmp_out/exp_sums/max_logits, 0: final out
-  int nstages;           // ring depth; always a multiple of nconsumers (see simt_smem_plan)
+  int always_partials;   // 1: v2 signature (every item writes tmp_out/exp_sums/max_logits)
+  int nstages;           // ring depth; always a multiple of nconsumers
   int nconsumers;        // consumer warps that take blocks (<= kConsumerWarps)
+  long long total_items; // max_num_partitions * num_seqs * tiles_per_seq
   long long q_stride;
   long long kv_block_stride;
   long long kv_head_stride;
 };
 
 constexpr int kConsumerWarps = 4;
+constexpr int kConsumerThreads = kConsumerWarps * 32;
 constexpr int kAttnThreads = (kConsumerWarps + 1) * 32;
+constexpr int kMaxStages = 32;
+constexpr int kItemQueue = 4;  // work items the producer may run ahead of the consumers
 
-template <typename CT, int D, int BS, int GT>
-struct SimtSmem {
-  static constexpr int kKBytes = D * BS * (int)sizeof(CT);
-  static constexpr int kStageBytes = 2 * kKBytes;
-  static constexpr int kFixedBytes =
-      GT * D * 4 +                           // q (fp32)
-      kConsumerWarps * GT * BS * 4 +         // per-warp probabilities
-      kConsumerWarps * GT * D * 4 +          // per-warp accumulators for the final merge
-      kConsumerWarps * GT * 2 * 4 +          // per-warp (max, sum)
-      2 * 32 * 8;                            // mbarriers (up to 32 stages)
-  static constexpr int kMaxStages = 32;
+// One unit of work of the persistent grid.
+struct ItemInfo {
+  int seq, part, kvh, tile, head0, ng;  // tile = kvh * gtiles + gt; first query head of the tile, valid heads in it
+  int ctx, nblk_ctx;              // context length (tokens, blocks)
+  int b0, nblk;                   // first block and block count of this partition (nblk == 0: nothing to read)
+  int nparts;                     // partitions this sequence has (0 for an empty context)
 };
 
+template <int GT, int BS>
+__device__ __forceinline__ ItemInfo decode_item(const AttnParams& p, long long item) {
+  ItemInfo it;
+  const int per_part = p.num_seqs * p.tiles_per_seq;
+  it.part = (int)(item / per_part);
+  const int rem = (int)(item - (long long)it.part * per_part);
+  it.seq = rem / p.tiles_per_seq;
+  it.tile = rem - it.seq * p.tiles_per_seq;
+  it.kvh = it.tile / p.gtiles;
+  const int gt = it.tile - it.kvh * p.gtiles;
+  it.head0 = it.kvh * p.group + gt * GT;
+  it.ng = min(GT, p.group - gt * GT);
+  it.ctx = p.context_lens[it.seq];
+  it.nblk_ctx = (it.ctx + BS - 1) / BS;
+  if (p.partition_blocks > 0) {
+    it.b0 = it.part * p.partition_blocks;
+    it.nblk = max(0, min(it.nblk_ctx, it.b0 + p.partition_blocks) - it.b0);
+    it.nparts = (it.nblk_ctx + p.partition_blocks - 1) / p.partition_blocks;
+  } else {
+    it.b0 = 0;
+    it.nblk = it.nblk_ctx;
+    it.nparts = it.nblk_ctx > 0 ? 1 : 0;
+  }
+  return it;
+}
+
+__device__ __forceinline__ void consumer_bar() {  // the 4 consumer warps only; the producer never joins
+  asm volatile("bar.sync 1, %0;" ::"n"(kConsumerThreads) : "memory");
+}
+
+// ---- producer ---------------------------------------------------------------------------------
+// Ring position of the producer, carried across items: global block index modulo the ring depth and
+// the number of times the ring has wrapped.
+struct RingPos {
+  int slot0;
+  int fill0;
+};
+
+// Streams blocks [b0, b0+nblk) of one item into the ring.  Lane j of the warp handles block n0 + j of each
+// group of G = min(nstages, 32) blocks, i.e. its own ring slot: the block-table load, the 64-bit address
+// math, the empty-barrier poll and the expect_tx arrive all run G lanes wide; only UBLKCP itself is issued
+// lane by lane.  Lanes whose slot is still being consumed keep polling while the others issue.
+template <typename CT>
+__device__ __forceinline__ void attn_produce_item(const AttnParams& p, const ItemInfo& it, RingPos& pos, int lane,
+                                                  unsigned char* stages, int stage_bytes, int kbytes,
+                                                  uint64_t* full_bar, uint64_t* empty_bar, uint64_t pol) {
+  const int nst = p.nstages;
+  const int G = nst < 32 ? nst : 32;
+  const int* table = p.block_tables + (long long)it.seq * p.max_num_blocks_per_seq + it.b0;
+  const unsigned char* kbase = static_cast<const unsigned char*>(p.k_cache) + (long long)it.kvh * p.kv_head_stride * (long long)sizeof(CT);
+  const unsigned char* vbase = static_cast<const unsigned char*>(p.v_cache) + (long long)it.kvh * p.kv_head_stride * (long long)sizeof(CT);
+  const long long blk_bytes = p.kv_block_stride * (long long)sizeof(CT);
+  const int nblk = it.nblk;
+  int phys_next = (lane < G && lane < nblk) ? table[lane] : 0;
+  for (int n0 = 0; n0 < nblk; n0 += G) {
+    const int phys = phys_next;
+    const int nn = n0 + G + lane;
+    phys_next = (lane < G && nn < nblk) ? table[nn] : 0;  // in flight while this group is issued
+    int slot = pos.slot0 + lane, fill = pos.fill0;
+    if (slot >= nst) { slot -= nst; ++fill; }
+    bool pending = lane < G && n0 + lane < nblk;
+    const long long off = (long long)phys * blk_bytes;
+    unsigned char* dst = stages + (size_t)slot * stage_bytes;
+    while (__any_sync(0xffffffffu, pending)) {
+      if (pending && (fill == 0 || mbar_try_wait(&empty_bar[slot], (fill - 1) & 1))) {
+        mbar_arrive_expect_tx(&full_bar[slot], 2 * kbytes);
+        bulk_g2s(dst, kbase + off, kbytes, &full_bar[slot], pol);
+        bulk_g2s(dst + kbytes, vbase + off, kbytes, &full_bar[slot], pol);
+        pending = false;
+      }
+    }
+    const int cnt = min(G, nblk - n0);
+    pos.slot0 += cnt;
+    if (pos.slot0 >= nst) { pos.slot0 -= nst; ++pos.fill0; }
+  }
+}
+
+// ---- per-item epilogue (the 128 consumer threads) -------------------------------------------------
+// Merge the consumer warps' partial (max, sum, acc) states of one item and write either the final output
+// rows or the partition partials in the reference's tmp_out / exp_sums / max_logits format.
+// red_acc [NW][GT][D] f32, red_ml [NW][GT][2] f32 (shared memory).  Returns nothing; `partial` says which.
+template <typename T, int D, int GT>
+__device__ __forceinline__ void attn_merge_store(const AttnParams& p, const ItemInfo& it, const float* red_acc,
+                                                 const float* red_ml, bool partial, int ctid) {
+  constexpr int NW = kConsumerWarps;
+  T* out = static_cast<T*>(p.out);
+  for (int idx = ctid; idx < it.ng * D; idx += kConsumerThreads) {
+    const int g = idx / D, d = idx - g * D;
+    float M = -FLT_MAX;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) M = fmaxf(M, red_ml[(w * GT + g) * 2]);
+    float L = 0.f, A = 0.f;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+      const float sc = __expf(red_ml[(w * GT + g) * 2] - M);
+      L = fmaf(red_ml[(w * GT + g) * 2 + 1], sc, L);
+      A = fmaf(red_acc[(w * GT + g) * D + d], sc, A);
+    }
+    const float o = A * __fdividef(1.f, L + 1e-6f);
+    const long long sh = (long long)it.seq * p.num_heads + it.head0 + g;
+    if (partial) {
+      const long long pi = sh * p.max_num_partitions + it.part;
+      static_cast<T*>(p.tmp_out)[pi * D + d] = from_f32<T>(o);
+      if (d == 0) {
+        p.exp_sums[pi] = L;
+        p.max_logits[pi] = M;
+      }
+    } else {
+      out[sh * D + d] = from_f32<T>(o);
+    }
+  }
+}
+
+// Combine the partitions of one (sequence, head tile): the reference's v2 reduce formula
+// (attention_kernels.cu:484-575): out = sum_j tmp_j * exp_sums_j * e^(max_j - max) / (sum + 1e-6).
+// Run by the 128 consumer threads of the CTA that finished the sequence's last partition; partials of
+// the other partitions were written by other CTAs, so they are read past L1 (ld.global.cg).
+template <typename T, int D>
+__device__ __forceinline__ void attn_reduce_in_kernel(const AttnParams& p, const ItemInfo& it, int ctid) {
+  T* out = static_cast<T*>(p.out);
+  const T* tmp_out = static_cast<const T*>(p.tmp_out);
+  const int np = it.nparts;
+  for (int idx = ctid; idx < it.ng * D; idx += kConsumerThreads) {
+    const int g = idx / D, d = idx - g * D;
+    const long long sh = (long long)it.seq * p.num_heads + it.head0 + g;
+    const float* ml = p.max_logits + sh * p.max_num_partitions;
+    const float* es = p.exp_sums + sh * p.max_num_partitions;
+    const T* tmp = tmp_out + sh * p.max_num_partitions * D + d;
+    float M = -FLT_MAX;
+    for (int j = 0; j < np; ++j) M = fmaxf(M, __ldcg(ml + j));
+    float sum = 0.f, a = 0.f;
+    for (int j = 0; j < np; ++j) {
+      const float w = __ldcg(es + j) * expf(__ldcg(ml + j) - M);
+      sum += w;
+      a = fmaf(ldcg_f32<T>(tmp + (long long)j * D), w, a);
+    }
+    out[sh * D + d] = from_f32<T>(a * __fdividef(1.f, sum + 1e-6f));
+  }
+}
+
+// ---- the persistent kernel ------------------------------------------------------------------
+// Impl supplies the consumer: types T (query/out) and CT (cache), tile constants D, BS, GT,
+// kKBytes/kStageBytes, kFixedBytes of private shared memory, a per-thread State and
+//   init(State&)                                   once per item, registers only
+//   begin_item(State&, p, it, fixed, warp, lane)   load the item's queries (may use consumer_bar)
+//   block(State&, p, it, ks, vs, blk, fixed, warp, lane)   one KV block from ring memory
+//   end_item(State&, it, red_acc, red_ml, warp, lane)      park the warp's (max, sum, acc) state
+template <class Impl>
+__global__ void __launch_bounds__(kAttnThreads) paged_attn_kernel(const __grid_constant__ AttnParams p) {
+  using T = typename Impl::T;
+  using CT = typename Impl::CT;
+  constexpr int D = Impl::D, BS = Impl::BS, GT = Impl::GT;
+  constexpr int NW = kConsumerWarps;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nst = p.nstages;
+
+  extern __shared__ __align__(128) unsigned char smem[];
+  unsigned char* stages = smem;
+  unsigned char* fixed = smem + (size_t)nst * Impl::kStageBytes;
+  float* red_acc = reinterpret_cast<float*>(fixed + Impl::kFixedBytes);
+  float* red_ml = red_acc + NW * GT * D;
+  int* s_flag = reinterpret_cast<int*>(red_ml + NW * GT * 2);
+  long long* item_q = reinterpret_cast<long long*>(s_flag + 4);  // [kItemQueue] items handed producer -> consumers
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(item_q + kItemQueue);
+  uint64_t* empty_bar = full_bar + kMaxStages;
+  uint64_t* iq_full = empty_bar + kMaxStages;
+  uint64_t* iq_empty = iq_full + kItemQueue;
+
+  if (tid == 0) {
+    for (int s = 0; s < nst; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < kItemQueue; ++s) {
+      mbar_init(&iq_full[s], 1);
+      mbar_init(&iq_empty[s], NW);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (warp == NW) {
+    // ================= producer =================
+#ifdef B200_ATTN_NO_HINT
+    const uint64_t pol = 0;
+#else
+    const uint64_t pol = l2_policy_evict_first();
+#endif
+    // Work items are drawn from a device-wide counter (the first one is blockIdx.x), so CTAs on slower SMs
+    // simply take fewer; every item id is handed to the consumer warps through a small shared-memory queue.
+    RingPos pos{0, 0};
+    long long item = blockIdx.x;
+    for (int k = 0;; ++k) {
+      const int qs = k % kItemQueue;
+      if (lane == 0) {
+        if (k >= kItemQueue) mbar_wait(&iq_empty[qs], ((k / kItemQueue) - 1) & 1);
+        item_q[qs] = item;
+        mbar_arrive(&iq_full[qs]);
+      }
+      if (item >= p.total_items) break;
+      const ItemInfo it = decode_item<GT, BS>(p, item);
+      if (it.nblk > 0)
+        attn_produce_item<CT>(p, it, pos, lane, stages, Impl::kStageBytes, Impl::kKBytes, full_bar, empty_bar, pol);
+      unsigned int raw = 0;
+      if (lane == 0) {
+        raw = atomicAdd(p.sched, 1u);
+        if ((long long)raw == p.total_items - 1) *p.sched = 0u;  // the last draw of the launch: leave the counter at zero
+      }
+      raw = __shfl_sync(0xffffffffu, raw, 0);
+      item = (long long)raw + gridDim.x;
+    }
+    return;
+  }
+
+  // ================= consumers =================
+  // Warp w owns ring slots w, w + nwa, ... (nstages % nwa == 0), i.e. global block indices congruent to w:
+  // every fill of a slot is consumed by the same warp, in order, so a parity wait is unambiguous.
+  const int nwa = p.nconsumers;
+  const bool active = warp < nwa;
+  int my_gi = warp;        // next global block index of this warp
+  int slot = warp;         // = my_gi % nstages
+  uint32_t parity = 0;     // = (my_gi / nstages) & 1
+  int gbase = 0;           // global block index of the current item's first block
+  typename Impl::State st;
+
+  for (int k = 0;; ++k) {
+    const int qs = k % kItemQueue;
+    mbar_wait(&iq_full[qs], (k / kItemQueue) & 1);
+    const long long item = item_q[qs];
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&iq_empty[qs]);
+    if (item >= p.total_items) break;
+    const ItemInfo it = decode_item<GT, BS>(p, item);
+    if (it.nblk == 0) {
+      // nothing to read.  An empty context is softmax over nothing -> zeros (reference: exp_sum = 0, acc = 0);
+      // under the v2 signature the reduce kernel writes them (it sees zero partitions).
+      if (it.nblk_ctx == 0 && it.part == 0 && !p.always_partials) {
+        T* out = static_cast<T*>(p.out);
+        for (int i = tid; i < it.ng * D; i += kConsumerThreads)
+          out[((long long)it.seq * p.num_heads + it.head0) * D + i] = from_f32<T>(0.f);
+      }
+      continue;
+    }
+    Impl::init(st);
+    Impl::begin_item(st, p, it, fixed, warp, lane);
+    if (active) {
+      const int gend = gbase + it.nblk;
+      for (; my_gi < gend; my_gi += nwa) {
+        unsigned char* ks = stages + (size_t)slot * Impl::kStageBytes;
+        mbar_wait(&full_bar[slot], parity);
+        Impl::block(st, p, it, ks, ks + Impl::kKBytes, it.b0 + (my_gi - gbase), fixed, warp, lane);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[slot]);
+        slot += nwa;
+        if (slot >= nst) { slot -= nst; parity ^= 1u; }
+      }
+    }
+    gbase += it.nblk;
+    Impl::end_item(st, it, red_acc, red_ml, warp, lane);
+    consumer_bar();
+    const bool partial = p.always_partials || it.nparts > 1;
+    attn_merge_store<T, D, GT>(p, it, red_acc, red_ml, partial, tid);
+    if (partial && p.tickets != nullptr) {
+      // v1 with an internal split: the CTA that completes the sequence's last partition combines them.
+      __threadfence();
+      consumer_bar();
+      if (tid == 0) {
+        int* ticket = p.tickets + it.seq * p.tiles_per_seq + it.tile;
+        const int prev = atomicAdd(ticket, 1);
+        const int last = prev == it.nparts - 1;
+        if (last) *ticket = 0;  // self-resetting: the array is all-zero again when the kernel ends
+        *s_flag = last;
+      }
+      consumer_bar();
+      if (*s_flag) {
+        __threadfence();
+        attn_reduce_in_kernel<T, D>(p, it, tid);
+      }
+    }
+    consumer_bar();  // red_acc / red_ml / the impl's query tile may be rewritten by the next item
+  }
+}
+
+// ---- SIMT consumer ----------------------------------------------------------------------------
 template <typename CT, int N>
 __device__ __forceinline__ void load_unpack(const unsigned char* p, float* f) {
   // N cache elements starting at p (N * sizeof(CT) is 16, or 8 for fp8 with block_size 8)
@@ -83,270 +376,157 @@ __device__ __forceinline__ void load_unpack(const unsigned char* p, float* f) {
   }
 }
 
-// Merge the consumer warps' partial (max, sum, acc) states and write either the final output row or
-// the partition partials in the reference's tmp_out / exp_sums / max_logits format.
-// red_acc [NW][GT][D] f32, red_ml [NW][GT][2] f32 (shared memory).
-template <typename T, int D, int GT>
-__device__ __forceinline__ void attn_merge_store(const AttnParams& p, const float* red_acc, const float* red_ml,
-                                                 int ng, int seq, int head0, int part, int tid) {
-  constexpr int NW = kConsumerWarps;
-  T* out = static_cast<T*>(p.out);
-  for (int idx = tid; idx < ng * D; idx += kAttnThreads) {
-    const int g = idx / D, d = idx - g * D;
-    float M = -FLT_MAX;
-#pragma unroll
-    for (int w = 0; w < NW; ++w) M = fmaxf(M, red_ml[(w * GT + g) * 2]);
-    float L = 0.f, A = 0.f;
-#pragma unroll
-    for (int w = 0; w < NW; ++w) {
-      const float sc = __expf(red_ml[(w * GT + g) * 2] - M);
-      L = fmaf(red_ml[(w * GT + g) * 2 + 1], sc, L);
-      A = fmaf(red_acc[(w * GT + g) * D + d], sc, A);
-    }
-    const float o = A * __fdividef(1.f, L + 1e-6f);
-    const long long sh = (long long)seq * p.num_heads + head0 + g;
-    if (p.write_partials) {
-      const long long pi = sh * p.max_num_partitions + part;
-      static_cast<T*>(p.tmp_out)[pi * D + d] = from_f32<T>(o);
-      if (d == 0) {
-        p.exp_sums[pi] = L;
-        p.max_logits[pi] = M;
-      }
-    } else {
-      out[sh * D + d] = from_f32<T>(o);
-    }
-  }
-}
+// One token per thread group for Q.K, 16-byte shared-memory vectors, fp32 everywhere.  GT_ query heads of
+// one KV head per item (1 for MHA; 8 for grouped queries that cannot take the tensor-core consumer).
+template <typename T_, typename CT_, int D_, int BS_, int GT_>
+struct SimtImpl {
+  using T = T_;
+  using CT = CT_;
+  static constexpr int D = D_, BS = BS_, GT = GT_;
+  static constexpr int NW = kConsumerWarps;
+  static constexpr int X = 16 / (int)sizeof(CT);
+  static constexpr int kKBytes = D * BS * (int)sizeof(CT);
+  static constexpr int kStageBytes = 2 * kKBytes;
+  static constexpr int kFixedBytes = GT * D * 4 + NW * GT * BS * 4;  // q (fp32) | per-warp probabilities
+  static constexpr int NVK = (D / X) * BS;           // 16-byte vectors in a K chunk
+  static constexpr int KIT = (NVK + 31) / 32;
+  static constexpr int VV = (X < BS) ? X : BS;       // tokens per V vector
+  static constexpr int VBYTES = VV * (int)sizeof(CT);
+  static constexpr int VPR = BS / VV;                // vectors per V row
+  static constexpr int NVV = D * VPR;
+  static constexpr int VIT = (NVV + 31) / 32;
 
-// Producer warp (shared by the SIMT and the tensor-core kernels): walks the block table of `seq`
-// from block b0 (32 entries per coalesced load, the next group prefetched while this one is issued)
-// and streams each (block, kv_head) chunk -- kbytes contiguous bytes of K, then of V -- into ring
-// stage n % nstages with two bulk copies completing on full_bar[stage].
-template <typename CT>
-__device__ __forceinline__ void attn_producer(const AttnParams& p, int seq, int kvh, int b0, int nblk, int lane,
-                                              unsigned char* stages, int stage_bytes, int kbytes,
-                                              uint64_t* full_bar, uint64_t* empty_bar) {
-  const int nst = p.nstages;
-  const int* table = p.block_tables + (long long)seq * p.max_num_blocks_per_seq + b0;
-  const unsigned char* kbase = static_cast<const unsigned char*>(p.k_cache) + (long long)kvh * p.kv_head_stride * (long long)sizeof(CT);
-  const unsigned char* vbase = static_cast<const unsigned char*>(p.v_cache) + (long long)kvh * p.kv_head_stride * (long long)sizeof(CT);
-  const long long blk_bytes = p.kv_block_stride * (long long)sizeof(CT);
-#ifdef B200_ATTN_NO_HINT
-  const uint64_t pol = 0;
-#else
-  const uint64_t pol = l2_policy_evict_first();
-#endif
-  int phys_next = lane < nblk ? table[lane] : 0;
-  int stage = 0, fill = 0;  // fill = how many times the ring has wrapped
-  for (int base = 0; base < nblk; base += 32) {
-    const int phys = phys_next;
-    const int nxt = base + 32 + lane;
-    phys_next = nxt < nblk ? table[nxt] : 0;  // in flight while this group is issued
-    const int cnt = min(32, nblk - base);
-    for (int j = 0; j < cnt; ++j) {
-      const long long pb = __shfl_sync(0xffffffffu, phys, j);
-      if (lane == 0) {
-        if (fill > 0) mbar_wait(&empty_bar[stage], (fill - 1) & 1);
-        unsigned char* dst = stages + (size_t)stage * stage_bytes;
-        mbar_arrive_expect_tx(&full_bar[stage], 2 * kbytes);
-        bulk_g2s(dst, kbase + pb * blk_bytes, kbytes, &full_bar[stage], pol);
-        bulk_g2s(dst + kbytes, vbase + pb * blk_bytes, kbytes, &full_bar[stage], pol);
-      }
-      if (++stage == nst) { stage = 0; ++fill; }
-    }
-  }
-}
-
-template <typename T, typename CT, int D, int BS, int GT>
-__global__ void __launch_bounds__(kAttnThreads) paged_attn_simt_kernel(const __grid_constant__ AttnParams p) {
-  using SM = SimtSmem<CT, D, BS, GT>;
-  constexpr int X = 16 / (int)sizeof(CT);
-  constexpr int KB = SM::kKBytes;
-  constexpr int NW = kConsumerWarps;
-
-  const int seq = blockIdx.y;
-  const int part = blockIdx.z;
-  const int kvh = blockIdx.x / p.gtiles;
-  const int gt = blockIdx.x - kvh * p.gtiles;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int head0 = kvh * p.group + gt * GT;           // first query head of this CTA
-  const int ng = min(GT, p.group - gt * GT);            // valid query heads in this tile
-
-  const int ctx = p.context_lens[seq];
-  const int nblk_ctx = (ctx + BS - 1) / BS;
-  int b0 = 0, b1 = nblk_ctx;
-  if (p.partition_blocks > 0) {
-    b0 = part * p.partition_blocks;
-    b1 = min(nblk_ctx, b0 + p.partition_blocks);
-  }
-  T* out = static_cast<T*>(p.out);
-  if (b0 >= b1) {
-    // empty context: softmax over nothing -> zeros (reference: exp_sum = 0, acc = 0)
-    if (!p.write_partials && part == 0)
-      for (int i = tid; i < ng * D; i += kAttnThreads)
-        out[((long long)seq * p.num_heads + head0) * D + i] = from_f32<T>(0.f);
-    return;
-  }
-  const int nblk = b1 - b0;
-  const int nst = p.nstages;
-
-  extern __shared__ __align__(128) unsigned char smem[];
-  unsigned char* stages = smem;
-  float* q_s = reinterpret_cast<float*>(smem + (size_t)nst * SM::kStageBytes);
-  float* plog = q_s + GT * D;
-  float* red_acc = plog + NW * GT * BS;
-  float* red_ml = red_acc + NW * GT * D;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(red_ml + NW * GT * 2);
-  uint64_t* empty_bar = full_bar + SM::kMaxStages;
-
-  if (tid == 0) {
-    for (int s = 0; s < nst; ++s) {
-      mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
-    }
-    mbar_fence_init();
-  }
-  {
-    const T* q = static_cast<const T*>(p.q) + (long long)seq * p.q_stride + (long long)head0 * D;
-    for (int i = tid; i < GT * D; i += kAttnThreads) q_s[i] = (i < ng * D) ? to_f32<T>(q[i]) : 0.f;
-  }
-  __syncthreads();
-
-  if (warp == NW) {
-    attn_producer<CT>(p, seq, kvh, b0, nblk, lane, stages, SM::kStageBytes, KB, full_bar, empty_bar);
-  } else {
-    // ================= consumers: online softmax over ring stages =================
-    constexpr int NVK = (D / X) * BS;           // 16-byte vectors in a K chunk
-    constexpr int KIT = (NVK + 31) / 32;
-    constexpr int VV = (X < BS) ? X : BS;       // tokens per V vector
-    constexpr int VBYTES = VV * (int)sizeof(CT);
-    constexpr int VPR = BS / VV;                // vectors per V row
-    constexpr int NVV = D * VPR;
-    constexpr int VIT = (NVV + 31) / 32;
-    const int tok = lane % BS;
-    const int vpart = lane % VPR;
-    float* plog_w = plog + warp * GT * BS;
-
+  struct State {
     float m_run[GT], l_run[GT], alibi[GT];
     float acc[GT][VIT];
+  };
+
+  __device__ __forceinline__ static void init(State& st) {
 #pragma unroll
     for (int g = 0; g < GT; ++g) {
-      m_run[g] = -FLT_MAX;
-      l_run[g] = 0.f;
-      alibi[g] = (p.alibi_slopes != nullptr && g < ng) ? p.alibi_slopes[head0 + g] : 0.f;
+      st.m_run[g] = -FLT_MAX;
+      st.l_run[g] = 0.f;
 #pragma unroll
-      for (int i = 0; i < VIT; ++i) acc[g][i] = 0.f;
+      for (int i = 0; i < VIT; ++i) st.acc[g][i] = 0.f;
     }
+  }
 
-    // Blocks go to the active consumer warps round-robin.  nst % nwa == 0, so every fill of a given
-    // stage is consumed by the SAME warp, in program order: a parity wait can only tell adjacent
-    // phases apart, and bulk copies land out of order, so a different warp waiting for fill f+1 of a
-    // stage could otherwise slip through while fill f is still in flight.
-    const int nwa = p.nconsumers;
-    for (int n = warp; n < nblk && warp < nwa; n += nwa) {
-      const int stage = n % nst;
-      const uint32_t parity = (n / nst) & 1;
-      const unsigned char* ks = stages + (size_t)stage * SM::kStageBytes;
-      const unsigned char* vs = ks + KB;
-      const int blk = b0 + n;
-      mbar_wait(&full_bar[stage], parity);
+  __device__ __forceinline__ static void begin_item(State& st, const AttnParams& p, const ItemInfo& it,
+                                                    unsigned char* fixed, int warp, int lane) {
+    float* q_s = reinterpret_cast<float*>(fixed);
+    const T* q = static_cast<const T*>(p.q) + (long long)it.seq * p.q_stride + (long long)it.head0 * D;
+    for (int i = warp * 32 + lane; i < GT * D; i += kConsumerThreads) q_s[i] = (i < it.ng * D) ? to_f32<T>(q[i]) : 0.f;
+#pragma unroll
+    for (int g = 0; g < GT; ++g)
+      st.alibi[g] = (p.alibi_slopes != nullptr && g < it.ng) ? p.alibi_slopes[it.head0 + g] : 0.f;
+    consumer_bar();
+  }
 
-      // ---- logits: one token per thread group, 16-byte vectors, fp32 accumulate ----
-      float s[GT];
+  __device__ __forceinline__ static void block(State& st, const AttnParams& p, const ItemInfo& it,
+                                               const unsigned char* ks, const unsigned char* vs, int blk,
+                                               unsigned char* fixed, int warp, int lane) {
+    const float* q_s = reinterpret_cast<const float*>(fixed);
+    float* plog_w = reinterpret_cast<float*>(fixed) + GT * D + warp * GT * BS;
+    const int tok = lane % BS;
+    const int vpart = lane % VPR;
+    const int ctx = it.ctx;
+
+    // ---- logits: one token per thread group, 16-byte vectors, fp32 accumulate ----
+    float s[GT];
 #pragma unroll
-      for (int g = 0; g < GT; ++g) s[g] = 0.f;
+    for (int g = 0; g < GT; ++g) s[g] = 0.f;
 #pragma unroll
-      for (int i = 0; i < KIT; ++i) {
-        const int v = lane + 32 * i;
-        if ((NVK % 32 == 0) || v < NVK) {
-          const int chunk = v / BS;
-          float kf[X];
-          load_unpack<CT, X>(ks + v * 16, kf);
+    for (int i = 0; i < KIT; ++i) {
+      const int v = lane + 32 * i;
+      if ((NVK % 32 == 0) || v < NVK) {
+        const int chunk = v / BS;
+        float kf[X];
+        load_unpack<CT, X>(ks + v * 16, kf);
 #pragma unroll
-          for (int g = 0; g < GT; ++g) {
-            const float4* qp = reinterpret_cast<const float4*>(q_s + g * D + chunk * X);
+        for (int g = 0; g < GT; ++g) {
+          const float4* qp = reinterpret_cast<const float4*>(q_s + g * D + chunk * X);
 #pragma unroll
-            for (int e = 0; e < X / 4; ++e) {
-              const float4 qq = qp[e];
-              s[g] = fmaf(qq.x, kf[4 * e + 0], s[g]);
-              s[g] = fmaf(qq.y, kf[4 * e + 1], s[g]);
-              s[g] = fmaf(qq.z, kf[4 * e + 2], s[g]);
-              s[g] = fmaf(qq.w, kf[4 * e + 3], s[g]);
-            }
+          for (int e = 0; e < X / 4; ++e) {
+            const float4 qq = qp[e];
+            s[g] = fmaf(qq.x, kf[4 * e + 0], s[g]);
+            s[g] = fmaf(qq.y, kf[4 * e + 1], s[g]);
+            s[g] = fmaf(qq.z, kf[4 * e + 2], s[g]);
+            s[g] = fmaf(qq.w, kf[4 * e + 3], s[g]);
           }
         }
       }
-      const int t_idx = blk * BS + tok;
-      const bool valid = t_idx < ctx;
-      float corr[GT];
-#pragma unroll
-      for (int g = 0; g < GT; ++g) {
-#pragma unroll
-        for (int m = 16; m >= BS; m >>= 1) s[g] += __shfl_xor_sync(0xffffffffu, s[g], m);
-        float sv = s[g] * p.scale;
-        sv += (alibi[g] != 0.f) ? alibi[g] * (float)(t_idx - ctx + 1) : 0.f;
-        sv = valid ? sv : -FLT_MAX;
-        float bmax = sv;
-#pragma unroll
-        for (int m = BS / 2; m >= 1; m >>= 1) bmax = fmaxf(bmax, __shfl_xor_sync(0xffffffffu, bmax, m));
-        const float m_new = fmaxf(m_run[g], bmax);
-        corr[g] = __expf(m_run[g] - m_new);
-        const float pe = valid ? __expf(sv - m_new) : 0.f;
-        l_run[g] = l_run[g] * corr[g] + (lane < BS ? pe : 0.f);
-        m_run[g] = m_new;
-        if (lane < BS) plog_w[g * BS + tok] = pe;
-      }
-      __syncwarp();
-
-      // ---- P.V: each lane owns VV consecutive tokens of some rows of the [D, BS] tile ----
-      float pv[GT][VV];
-#pragma unroll
-      for (int g = 0; g < GT; ++g) {
-#pragma unroll
-        for (int j = 0; j < VV; j += 4) {
-          const float4 t4 = *reinterpret_cast<const float4*>(plog_w + g * BS + vpart * VV + j);
-          pv[g][j] = t4.x; pv[g][j + 1] = t4.y; pv[g][j + 2] = t4.z; pv[g][j + 3] = t4.w;
-        }
-      }
-      const bool last = (blk == nblk_ctx - 1);
-#pragma unroll
-      for (int i = 0; i < VIT; ++i) {
-        const int v = lane + 32 * i;
-        if ((NVV % 32 == 0) || v < NVV) {
-          float vf[VV];
-          load_unpack<CT, VV>(vs + v * VBYTES, vf);
-          if (last) {
-            // stale slots past the context may hold NaN/Inf bit patterns (reference :342-351)
-#pragma unroll
-            for (int j = 0; j < VV; ++j)
-              if (blk * BS + vpart * VV + j >= ctx) vf[j] = 0.f;
-          }
-#pragma unroll
-          for (int g = 0; g < GT; ++g) {
-            float a = acc[g][i] * corr[g];
-#pragma unroll
-            for (int j = 0; j < VV; ++j) a = fmaf(pv[g][j], vf[j], a);
-            acc[g][i] = a;
-          }
-        }
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&empty_bar[stage]);
     }
-
-    // ---- per-warp totals -> shared memory ----
+    const int t_idx = blk * BS + tok;
+    const bool valid = t_idx < ctx;
+    float corr[GT];
 #pragma unroll
     for (int g = 0; g < GT; ++g) {
-      float l = l_run[g];
+#pragma unroll
+      for (int m = 16; m >= BS; m >>= 1) s[g] += __shfl_xor_sync(0xffffffffu, s[g], m);
+      float sv = s[g] * p.scale;
+      sv += (st.alibi[g] != 0.f) ? st.alibi[g] * (float)(t_idx - ctx + 1) : 0.f;
+      sv = valid ? sv : -FLT_MAX;
+      float bmax = sv;
+#pragma unroll
+      for (int m = BS / 2; m >= 1; m >>= 1) bmax = fmaxf(bmax, __shfl_xor_sync(0xffffffffu, bmax, m));
+      const float m_new = fmaxf(st.m_run[g], bmax);
+      corr[g] = __expf(st.m_run[g] - m_new);
+      const float pe = valid ? __expf(sv - m_new) : 0.f;
+      st.l_run[g] = st.l_run[g] * corr[g] + (lane < BS ? pe : 0.f);
+      st.m_run[g] = m_new;
+      if (lane < BS) plog_w[g * BS + tok] = pe;
+    }
+    __syncwarp();
+
+    // ---- P.V: each lane owns VV consecutive tokens of some rows of the [D, BS] tile ----
+    float pv[GT][VV];
+#pragma unroll
+    for (int g = 0; g < GT; ++g) {
+#pragma unroll
+      for (int j = 0; j < VV; j += 4) {
+        const float4 t4 = *reinterpret_cast<const float4*>(plog_w + g * BS + vpart * VV + j);
+        pv[g][j] = t4.x; pv[g][j + 1] = t4.y; pv[g][j + 2] = t4.z; pv[g][j + 3] = t4.w;
+      }
+    }
+    const bool last = (blk == it.nblk_ctx - 1);
+#pragma unroll
+    for (int i = 0; i < VIT; ++i) {
+      const int v = lane + 32 * i;
+      if ((NVV % 32 == 0) || v < NVV) {
+        float vf[VV];
+        load_unpack<CT, VV>(vs + v * VBYTES, vf);
+        if (last) {
+          // stale slots past the context may hold NaN/Inf bit patterns (reference :342-351)
+#pragma unroll
+          for (int j = 0; j < VV; ++j)
+            if (blk * BS + vpart * VV + j >= ctx) vf[j] = 0.f;
+        }
+#pragma unroll
+        for (int g = 0; g < GT; ++g) {
+          float a = st.acc[g][i] * corr[g];
+#pragma unroll
+          for (int j = 0; j < VV; ++j) a = fmaf(pv[g][j], vf[j], a);
+          st.acc[g][i] = a;
+        }
+      }
+    }
+  }
+
+  __device__ __forceinline__ static void end_item(State& st, const ItemInfo& it, float* red_acc, float* red_ml,
+                                                  int warp, int lane) {
+    const int vpart = lane % VPR;
+#pragma unroll
+    for (int g = 0; g < GT; ++g) {
+      float l = st.l_run[g];
 #pragma unroll
       for (int m = 16; m >= 1; m >>= 1) l += __shfl_xor_sync(0xffffffffu, l, m);
       if (lane == 0) {
-        red_ml[(warp * GT + g) * 2 + 0] = m_run[g];
+        red_ml[(warp * GT + g) * 2 + 0] = st.m_run[g];
         red_ml[(warp * GT + g) * 2 + 1] = l;
       }
 #pragma unroll
       for (int i = 0; i < VIT; ++i) {
-        float a = acc[g][i];
+        float a = st.acc[g][i];
 #pragma unroll
         for (int m = VPR / 2; m >= 1; m >>= 1) a += __shfl_xor_sync(0xffffffffu, a, m);
         const int v = lane + 32 * i;
@@ -354,13 +534,12 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_simt_kernel(const __g
       }
     }
   }
-  __syncthreads();
+};
 
-  attn_merge_store<T, D, GT>(p, red_acc, red_ml, ng, seq, head0, part, tid);
-}
-
-// Merge of partition partials; same formula as the reference's paged_attention_v2_reduce_kernel
-// (attention_kernels.cu:484-575): out = sum_j tmp_j * exp_sums_j * e^(max_j - max) / (sum + 1e-6).
+// ---- v2 signature: separate merge of the partition partials -------------------------------------
+// Same formula as the reference's paged_attention_v2_reduce_kernel (attention_kernels.cu:484-575).
+// Launched with programmatic stream serialization: its CTAs may be resident before the attention
+// kernel has finished; griddepcontrol.wait orders it after that kernel's memory.
 template <typename T>
 __global__ void __launch_bounds__(128) paged_attn_reduce_kernel(
     T* __restrict__ out, const float* __restrict__ exp_sums, const float* __restrict__ max_logits,
@@ -372,6 +551,7 @@ __global__ void __launch_bounds__(128) paged_attn_reduce_kernel(
   const long long sh = (long long)seq * num_heads + head;
   const T* tmp = tmp_out + sh * max_num_partitions * head_size;
   T* o = out + sh * head_size;
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   if (np <= 1) {
     for (int d = threadIdx.x; d < head_size; d += blockDim.x) o[d] = np == 1 ? tmp[d] : from_f32<T>(0.f);
     return;
@@ -407,27 +587,58 @@ __global__ void __launch_bounds__(128) paged_attn_reduce_kernel(
   }
 }
 
-// One instantiation family per (T, CT); defined in attn_inst_*.cu so they compile in parallel.
-template <typename T, typename CT>
-int launch_simt(const AttnParams& p, int head_size, int block_size, int gt, dim3 grid,
-                int smem_budget, cudaStream_t stream);
-
-template <typename CT>
-inline bool simt_smem_plan(int head_size, int block_size, int gt, int smem_budget, int* nstages, int* nconsumers,
-                           int* smem_bytes) {
-  const int kbytes = head_size * block_size * (int)sizeof(CT);
-  const int stage = 2 * kbytes;
-  const int fixed = gt * head_size * 4 + kConsumerWarps * gt * block_size * 4 +
-                    kConsumerWarps * gt * head_size * 4 + kConsumerWarps * gt * 2 * 4 + 2 * 32 * 8;
-  int n = (smem_budget - fixed) / stage;
+// ---- host-side launch plumbing shared by both consumers ---------------------------------------------
+// Ring depth and shared-memory size for a consumer under a per-CTA budget.
+inline bool attn_smem_plan(int stage_bytes, int fixed_bytes, int gt, int head_size, int smem_budget, int* nstages,
+                           int* nconsumers, int* smem_bytes) {
+  const int tail = fixed_bytes + kConsumerWarps * gt * head_size * 4 + kConsumerWarps * gt * 2 * 4 + 16 +
+                   kItemQueue * 8 + 2 * kMaxStages * 8 + 2 * kItemQueue * 8;
+  int n = (smem_budget - tail) / stage_bytes;
   if (n > 16) n = 16;
-  // ring depth must be a multiple of the number of consuming warps (same warp per stage, see kernel)
+  // ring depth must be a multiple of the number of consuming warps (same warp per slot, see the kernel)
   const int nwa = n < kConsumerWarps ? n : kConsumerWarps;
   if (nwa > 0) n = n / nwa * nwa;
   *nstages = n;
   *nconsumers = nwa;
-  *smem_bytes = n * stage + fixed;
+  *smem_bytes = n * stage_bytes + tail;
   return n >= 2;
 }
+
+// Launch the persistent kernel for one consumer: grid = resident CTAs per SM x SMs, capped by the item count.
+template <class Impl>
+int launch_attn(const AttnParams& p_in, int smem_budget, int sms, cudaStream_t stream) {
+  AttnParams p = p_in;
+  int nst = 0, nwa = 0, smem = 0;
+  if (!attn_smem_plan(Impl::kStageBytes, Impl::kFixedBytes, Impl::GT, Impl::D, smem_budget, &nst, &nwa, &smem))
+    return B200_ERR_ARG;
+  p.nstages = nst;
+  p.nconsumers = nwa;
+  auto kern = paged_attn_kernel<Impl>;
+  // per instantiation and per device (function attributes are per device): smem size -> resident CTAs per SM
+  static int occ_smem[64] = {0}, occ_val[64] = {0};
+  int dev = 0;
+  B200_CUDA_TRY(cudaGetDevice(&dev));
+  dev &= 63;
+  if (occ_smem[dev] != smem) {
+    B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int occ = 0;
+    B200_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kAttnThreads, smem));
+    if (occ < 1) return B200_ERR_ARG;
+    occ_val[dev] = occ;
+    occ_smem[dev] = smem;
+  }
+  long long grid = (long long)occ_val[dev] * sms;
+  if (grid > p.total_items) grid = p.total_items;
+  kern<<<(unsigned)grid, kAttnThreads, smem, stream>>>(p);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+// One instantiation family per (T, CT); defined in attn_inst_*.cu / attn_mma_inst_*.cu so they compile in
+// parallel.  gt: query heads per item (SIMT: 1 or 8; MMA: 8 or 16).
+template <typename T, typename CT>
+int launch_simt(const AttnParams& p, int head_size, int block_size, int gt, int smem_budget, int sms, cudaStream_t stream);
+template <typename T, typename CT>
+int launch_mma(const AttnParams& p, int head_size, int block_size, int gt, int smem_budget, int sms, cudaStream_t stream);
 
 }  // namespace b200
