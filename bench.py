@@ -57,6 +57,11 @@ WORKLOADS = {
                S=256, Hq=64, Hkv=8, D=128, bs=16, ctx=4096, dtype="bfloat16", kv="auto"),
     "c4": dict(desc="C4 Mistral-7B GQA: 32 q / 8 kv heads, head 128, block 16, batch 128, ctx 8192, bf16 query, fp8_e5m2 KV",
                S=128, Hq=32, Hkv=8, D=128, bs=16, ctx=8192, dtype="bfloat16", kv="fp8_e5m2"),
+    "refbench": dict(desc="reference benchmark default (benchmarks/kernels/benchmark_paged_attention.py): 64 q / 8 kv heads, "
+                          "head 128, block 16, batch 8, ctx 4096, fp16",
+                     S=8, Hq=64, Hkv=8, D=128, bs=16, ctx=4096, dtype="float16", kv="auto"),
+    "small": dict(desc="small batch: 32 q / 8 kv heads, head 128, block 16, batch 4, ctx 8192, bf16 query, fp8_e5m2 KV",
+                  S=4, Hq=32, Hkv=8, D=128, bs=16, ctx=8192, dtype="bfloat16", kv="fp8_e5m2"),
     "c1": dict(desc="C1 OPT-125m shape: 12 heads, head 64, block 16, batch 8, ctx 512, fp32",
                S=8, Hq=12, Hkv=12, D=64, bs=16, ctx=512, dtype="float32", kv="auto"),
 }

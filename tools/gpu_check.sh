@@ -15,7 +15,7 @@ if [ "${SKIP_TESTS:-0}" != "1" ]; then
 fi
 
 python bench.py > $OUT/bench_c2_v1.json 2> $OUT/bench_c2_v1.err; echo "bench c2 v1 exit $?"; cat $OUT/bench_c2_v1.json
-for wl in c2:v2 c3tp8:v1 c3tp4:v1 c3tp2:v1 c3:v1 c4:v1 c4:v2 c1:v1; do
+for wl in c2:v2 c3tp8:v1 c3tp4:v1 c3tp2:v1 c3:v1 c4:v1 c4:v2 c1:v1 refbench:v1 refbench:v2; do
   w=${wl%%:*}; v=${wl##*:}
   python bench.py --workload $w --version $v --steps 200 --warmup 5 --no-cpu-baseline \
       > $OUT/bench_${w}_${v}.json 2> $OUT/bench_${w}_${v}.err
@@ -29,7 +29,7 @@ if [ "${SKIP_NCU:-0}" != "1" ]; then
       > $OUT/ncu_launches.log 2>&1
   echo "ncu launches exit $?"
   $CMD > $OUT/plain2.log 2>&1 &&
-  ncu --set full --clock-control none --import-source on -k regex:paged_attn_simt -s 4 -c 2 -f -o $OUT/prof_attn_c2 $CMD \
+  ncu --set full --clock-control none --import-source on -k regex:paged_attn_kernel -s 4 -c 2 -f -o $OUT/prof_attn_c2 $CMD \
       > $OUT/ncu_full.log 2>&1
   echo "ncu full exit $?"
 fi

@@ -146,12 +146,20 @@ int launch_reduce(const b200_paged_attn_args_t* a, int max_parts, int partition_
 int pick_smem_budget(const b200_paged_attn_args_t* a, const TilePlan& t, int* ctas_per_sm) {
   const int stage = 2 * a->head_size * a->block_size * dtype_size(a->cache_dtype);
   const int fixed = t.mma ? 0 : t.gt * a->head_size * 4 + kConsumerWarps * t.gt * a->block_size * 4;
-  const int tail = fixed + kConsumerWarps * t.gt * a->head_size * 4 + kConsumerWarps * t.gt * 8 + 16 + kItemQueue * 8 +
+  const int tail = fixed + kConsumerWarps * t.gt * a->head_size * 4 + kConsumerWarps * t.gt * 8 + 16 + kItemQueue * 16 +
                    2 * kMaxStages * 8 + 2 * kItemQueue * 8;
-  const int two = 112 * 1024;
-  if ((two - tail) / stage >= 4) {
-    *ctas_per_sm = 2;
-    return two;
+  // two resident CTAs per SM when each still gets a ring of at least 4 stages, else one.  (Three CTAs with
+  // 12-stage rings fit for 1-byte caches but measured 2 % slower on C4: profiles/README.md.)
+  int want = 2;
+  if (const char* e = getenv("B200_ATTN_CTAS_PER_SM")) want = atoi(e);  // tuning knob
+  for (int c = 3; c >= 1; --c) {
+    if (c > want) continue;
+    const int budget = (227 * 1024) / c - 1024;  // 1 KiB per CTA is reserved by the system
+    const int n = (budget - tail) / stage;
+    if (c == 1 || n >= (c == 3 ? 12 : 4)) {
+      *ctas_per_sm = c;
+      return budget;
+    }
   }
   *ctas_per_sm = 1;
   return 226 * 1024;
@@ -202,25 +210,23 @@ int plan_v1_split(const b200_paged_attn_args_t* a, int tiles_per_seq, int slots,
     *partition_blocks = (max_blocks + np - 1) / np;
     return (max_blocks + *partition_blocks - 1) / *partition_blocks;
   }
-  const double overhead = 2.0;  // per-item prologue + epilogue, in block times
+  // Measured (profiles/r02_split_sweep.txt): with dynamically scheduled items an unsplit call runs at the HBM
+  // ceiling as soon as the items cover ~3/4 of the resident CTAs, and every extra partition costs a few
+  // percent (partials + per-item epilogue).  So split only to fill the machine, never to balance it.
+  if (base_items * 4 >= (long long)slots * 3) return 1;
   const int min_pb = 8;
-  double best_cost = 0;
+  int np = (int)std::min<long long>((slots + base_items - 1) / base_items, kMaxSplit);
+  np = std::min(np, std::max(1, max_blocks / min_pb));
   int best_np = 1, best_pb = 0;
-  for (int np = 1; np <= kMaxSplit; ++np) {
+  for (; np > 1; --np) {
     const int pb = (max_blocks + np - 1) / np;
-    if (np > 1 && pb < min_pb) break;
     const int np_eff = (max_blocks + pb - 1) / pb;
-    if (np_eff != np) continue;
-    const long long rounds = (base_items * np + slots - 1) / slots;
-    double cost = (double)rounds * (pb + overhead);
-    if (np > 1) cost *= 1.03;  // partials cost a little: prefer no split on a near tie
-    const long long need = kTicketBytes + base_items / tiles_per_seq * a->num_heads * np *
+    const long long need = kTicketBytes + (long long)a->num_seqs * a->num_heads * np_eff *
                                               ((long long)a->head_size * dtype_size(a->query_dtype) + 8) + 64;
-    if (np > 1 && need > a->workspace_bytes) break;
-    if (np == 1 || cost < best_cost) {
-      best_cost = cost;
-      best_np = np;
-      best_pb = np == 1 ? 0 : pb;
+    if (need <= a->workspace_bytes) {
+      best_np = np_eff;
+      best_pb = pb;
+      break;
     }
   }
   *partition_blocks = best_pb;

@@ -77,8 +77,10 @@ struct ItemInfo {
   int nparts;                     // partitions this sequence has (0 for an empty context)
 };
 
+// ctx_known >= 0: the context length was already fetched (the producer passes it through the item queue so
+// that consumers do not pay a global-memory round trip per item).
 template <int GT, int BS>
-__device__ __forceinline__ ItemInfo decode_item(const AttnParams& p, long long item) {
+__device__ __forceinline__ ItemInfo decode_item(const AttnParams& p, long long item, int ctx_known = -1) {
   ItemInfo it;
   const int per_part = p.num_seqs * p.tiles_per_seq;
   it.part = (int)(item / per_part);
@@ -89,7 +91,7 @@ __device__ __forceinline__ ItemInfo decode_item(const AttnParams& p, long long i
   const int gt = it.tile - it.kvh * p.gtiles;
   it.head0 = it.kvh * p.group + gt * GT;
   it.ng = min(GT, p.group - gt * GT);
-  it.ctx = p.context_lens[it.seq];
+  it.ctx = ctx_known >= 0 ? ctx_known : p.context_lens[it.seq];
   it.nblk_ctx = (it.ctx + BS - 1) / BS;
   if (p.partition_blocks > 0) {
     it.b0 = it.part * p.partition_blocks;
@@ -194,26 +196,47 @@ __device__ __forceinline__ void attn_merge_store(const AttnParams& p, const Item
 // (attention_kernels.cu:484-575): out = sum_j tmp_j * exp_sums_j * e^(max_j - max) / (sum + 1e-6).
 // Run by the 128 consumer threads of the CTA that finished the sequence's last partition; partials of
 // the other partitions were written by other CTAs, so they are read past L1 (ld.global.cg).
-template <typename T, int D>
-__device__ __forceinline__ void attn_reduce_in_kernel(const AttnParams& p, const ItemInfo& it, int ctid) {
+template <typename T, int D, int GT>
+__device__ __forceinline__ void attn_reduce_in_kernel(const AttnParams& p, const ItemInfo& it, float* scratch, int ctid) {
+  // scratch: shared memory, >= 2 * GT * np floats (the merge buffers are free at this point).
+  // Step 1: all (head, partition) statistics in one round of independent loads.
   T* out = static_cast<T*>(p.out);
   const T* tmp_out = static_cast<const T*>(p.tmp_out);
   const int np = it.nparts;
+  float* ml_s = scratch;
+  float* w_s = scratch + GT * np;
+  const long long sh0 = (long long)it.seq * p.num_heads + it.head0;
+  for (int i = ctid; i < it.ng * np; i += kConsumerThreads) {
+    const int g = i / np, j = i - g * np;
+    ml_s[i] = __ldcg(p.max_logits + (sh0 + g) * p.max_num_partitions + j);
+    w_s[i] = __ldcg(p.exp_sums + (sh0 + g) * p.max_num_partitions + j);
+  }
+  consumer_bar();
+  // Step 2: per output element, weights from shared memory and the partials four loads at a time.
   for (int idx = ctid; idx < it.ng * D; idx += kConsumerThreads) {
     const int g = idx / D, d = idx - g * D;
-    const long long sh = (long long)it.seq * p.num_heads + it.head0 + g;
-    const float* ml = p.max_logits + sh * p.max_num_partitions;
-    const float* es = p.exp_sums + sh * p.max_num_partitions;
-    const T* tmp = tmp_out + sh * p.max_num_partitions * D + d;
+    const T* tmp = tmp_out + (sh0 + g) * p.max_num_partitions * D + d;
     float M = -FLT_MAX;
-    for (int j = 0; j < np; ++j) M = fmaxf(M, __ldcg(ml + j));
+    for (int j = 0; j < np; ++j) M = fmaxf(M, ml_s[g * np + j]);
     float sum = 0.f, a = 0.f;
-    for (int j = 0; j < np; ++j) {
-      const float w = __ldcg(es + j) * expf(__ldcg(ml + j) - M);
+    int j = 0;
+    for (; j + 4 <= np; j += 4) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = ldcg_f32<T>(tmp + (long long)(j + u) * D);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float w = w_s[g * np + j + u] * __expf(ml_s[g * np + j + u] - M);
+        sum += w;
+        a = fmaf(v[u], w, a);
+      }
+    }
+    for (; j < np; ++j) {
+      const float w = w_s[g * np + j] * __expf(ml_s[g * np + j] - M);
       sum += w;
       a = fmaf(ldcg_f32<T>(tmp + (long long)j * D), w, a);
     }
-    out[sh * D + d] = from_f32<T>(a * __fdividef(1.f, sum + 1e-6f));
+    out[(sh0 + g) * D + d] = from_f32<T>(a * __fdividef(1.f, sum + 1e-6f));
   }
 }
 
@@ -241,7 +264,8 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_kernel(const __grid_c
   float* red_ml = red_acc + NW * GT * D;
   int* s_flag = reinterpret_cast<int*>(red_ml + NW * GT * 2);
   long long* item_q = reinterpret_cast<long long*>(s_flag + 4);  // [kItemQueue] items handed producer -> consumers
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(item_q + kItemQueue);
+  int* ctx_q = reinterpret_cast<int*>(item_q + kItemQueue);      // [kItemQueue] their context lengths
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ctx_q + kItemQueue);
   uint64_t* empty_bar = full_bar + kMaxStages;
   uint64_t* iq_full = empty_bar + kMaxStages;
   uint64_t* iq_empty = iq_full + kItemQueue;
@@ -272,13 +296,16 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_kernel(const __grid_c
     long long item = blockIdx.x;
     for (int k = 0;; ++k) {
       const int qs = k % kItemQueue;
+      const bool done = item >= p.total_items;
+      ItemInfo it;
+      if (!done) it = decode_item<GT, BS>(p, item);
       if (lane == 0) {
         if (k >= kItemQueue) mbar_wait(&iq_empty[qs], ((k / kItemQueue) - 1) & 1);
         item_q[qs] = item;
+        ctx_q[qs] = done ? 0 : it.ctx;
         mbar_arrive(&iq_full[qs]);
       }
-      if (item >= p.total_items) break;
-      const ItemInfo it = decode_item<GT, BS>(p, item);
+      if (done) break;
       if (it.nblk > 0)
         attn_produce_item<CT>(p, it, pos, lane, stages, Impl::kStageBytes, Impl::kKBytes, full_bar, empty_bar, pol);
       unsigned int raw = 0;
@@ -307,10 +334,11 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_kernel(const __grid_c
     const int qs = k % kItemQueue;
     mbar_wait(&iq_full[qs], (k / kItemQueue) & 1);
     const long long item = item_q[qs];
+    const int ctx_known = ctx_q[qs];
     __syncwarp();
     if (lane == 0) mbar_arrive(&iq_empty[qs]);
     if (item >= p.total_items) break;
-    const ItemInfo it = decode_item<GT, BS>(p, item);
+    const ItemInfo it = decode_item<GT, BS>(p, item, ctx_known);
     if (it.nblk == 0) {
       // nothing to read.  An empty context is softmax over nothing -> zeros (reference: exp_sum = 0, acc = 0);
       // under the v2 signature the reduce kernel writes them (it sees zero partitions).
@@ -354,7 +382,7 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_kernel(const __grid_c
       consumer_bar();
       if (*s_flag) {
         __threadfence();
-        attn_reduce_in_kernel<T, D>(p, it, tid);
+        attn_reduce_in_kernel<T, D, GT>(p, it, red_acc, tid);  // red_acc: NW*GT*D floats >= 2*GT*64
       }
     }
     consumer_bar();  // red_acc / red_ml / the impl's query tile may be rewritten by the next item
@@ -592,7 +620,7 @@ __global__ void __launch_bounds__(128) paged_attn_reduce_kernel(
 inline bool attn_smem_plan(int stage_bytes, int fixed_bytes, int gt, int head_size, int smem_budget, int* nstages,
                            int* nconsumers, int* smem_bytes) {
   const int tail = fixed_bytes + kConsumerWarps * gt * head_size * 4 + kConsumerWarps * gt * 2 * 4 + 16 +
-                   kItemQueue * 8 + 2 * kMaxStages * 8 + 2 * kItemQueue * 8;
+                   kItemQueue * 16 + 2 * kMaxStages * 8 + 2 * kItemQueue * 8;
   int n = (smem_budget - tail) / stage_bytes;
   if (n > 16) n = 16;
   // ring depth must be a multiple of the number of consuming warps (same warp per slot, see the kernel)
