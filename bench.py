@@ -87,6 +87,18 @@ def reshape_and_cache_bytes(w) -> int:
     return w["S"] * w["Hkv"] * w["D"] * 2 * (elt_bytes(w["dtype"]) + cache_elt) + w["S"] * 8
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per attention launch from the committed ncu --set full capture
+# of the same command (profiles/r02_c2_attn_ncu_full.txt); null for workloads without a capture.
+NCU_TRAFFIC = {"c2": 4_295_611_000 + 4_237_824}
+
+
+def kernel_name(w) -> str:
+    """Which consumer the library's dispatch picks (csrc/paged_attention.cu plan_tile)."""
+    grouped = w["Hq"] != w["Hkv"] and w["dtype"] != "float32" and w["bs"] in (16, 32)
+    return "paged_attn_kernel<MmaImpl> (persistent, mma.sync consumer)" if grouped else \
+        "paged_attn_kernel<SimtImpl> (persistent, SIMT consumer)"
+
+
 def step_bytes(w) -> int:
     return attention_bytes(w) + reshape_and_cache_bytes(w)
 
@@ -437,8 +449,8 @@ def run_b200(args, w):
                     "d2h_bytes_per_step": out_bytes, "ms_per_step": round(e2e_ms / args.steps, 5)},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
-                         "frac": round(achieved / peak, 4), "traffic": args.traffic,
-                         "kernel": "paged_attn_simt_kernel", "kernel_ms": round(attn_ms, 5),
+                         "frac": round(achieved / peak, 4), "traffic": args.traffic if args.traffic is not None else NCU_TRAFFIC.get(args.workload),
+                         "kernel": kernel_name(w), "kernel_ms": round(attn_ms, 5),
                          "algorithmic_bytes_per_launch": attention_bytes(w), "peak_source": peak_src,
                          "frac_of_8TBps_spec": round(achieved / 8000.0, 4)},
         }
