@@ -118,7 +118,7 @@ def main():
     def run_ours(lists, mode):
         for p, blocks in enumerate(lists):
             sem = p % 256
-            runs = coalesce_blocks(blocks)
+            runs = runs_of[id(blocks)]
             if is_prompt:
                 if mode == "bulk":
                     mgr.put_layers(sem, 0, L, runs)
@@ -131,7 +131,7 @@ def main():
 
     def run_nccl(lists):
         for blocks in lists:
-            runs = coalesce_blocks(blocks)
+            runs = runs_of[id(blocks)]
             for k, v in kv:
                 ops = []
                 for t in (k, v):
@@ -146,6 +146,8 @@ def main():
             lists = block_lists(pattern, 7)
             if mode == "nccl" and pattern == "fragmented":
                 lists = lists[:args.nccl_max_prompts]
+            # the scheduler coalesces a prompt's block list once (vllm/utils.py:403-426); not part of the transfer
+            runs_of = {id(b): tuple(map(tuple, coalesce_blocks(b))) for b in lists}
             nbytes = sum(len(b) for b in lists) * block_bytes * 2 * L
             times = []
             ok = True

@@ -52,11 +52,24 @@ def exchange_peer_info(group, rank: int, world_size: int, num_prompt_workers: in
     return everyone[pair_rank(rank, world_size, num_prompt_workers)]
 
 
+_runs_cache: dict = {}
+
+
 def _runs_array(runs: Sequence[Tuple[int, int]]):
+    """ctypes int32 [num_runs][2] for the C ABI.  The worker puts the same coalesced block list once per
+    layer (reference flash_attn.py:81-86), so the last few conversions are cached by content."""
+    key = tuple(map(tuple, runs)) if not isinstance(runs, tuple) else runs
+    hit = _runs_cache.get(key)
+    if hit is not None:
+        return hit
     flat: List[int] = []
     for start, n in runs:
         flat += (int(start), int(n))
-    return (ctypes.c_int32 * len(flat))(*flat), len(flat) // 2
+    out = ((ctypes.c_int32 * len(flat))(*flat), len(flat) // 2)
+    if len(_runs_cache) >= 64:
+        _runs_cache.pop(next(iter(_runs_cache)))
+    _runs_cache[key] = out
+    return out
 
 
 class KVCacheCommunicator:
