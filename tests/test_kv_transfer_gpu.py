@@ -113,6 +113,79 @@ def test_block_lists_bit_exact(dtype, pattern, max_ctas):
     m.destroy_comm()
 
 
+@pytest.mark.parametrize("defer", [True, False])
+@pytest.mark.parametrize("side_stream", [False, True])
+def test_reference_call_pattern_many_semaphores(defer, side_stream):
+    """The backends' loop (flash_attn.py:81-86 + worker.py:327-331): per layer, per semaphore, per coalesced
+    run one put(); signals after the last layer.  Deferred puts leave as one launch per layer; eager puts as
+    one launch each; with a side stream the transfers are ordered after the caller's stream by an event."""
+    from vllm_splitwise_b200.comm_utils import KVCacheCommManager
+    from vllm_splitwise_b200.utils import coalesce_blocks
+    random.seed(11)
+    dev = torch.device("cuda:0")
+    L, NB, hkv, d, bs = 5, 400, 10, 128, 16
+    src = _caches(L, NB, hkv, d, bs, torch.half, dev, 4)
+    dst = [(torch.zeros_like(k), torch.zeros_like(v)) for k, v in src]
+    before = [(k.clone(), v.clone()) for k, v in dst]
+    ids = random.sample(range(300), 240)
+    per_sem = {s: ids[s * 60:(s + 1) * 60] for s in range(4)}     # 4 prompts in the batch, mixed run lengths
+    per_sem[1] = list(range(300, 360))                            # one of them a single contiguous run
+    m = KVCacheCommManager(rank=0, world_size=2, num_prompt_workers=1)
+    m.setup_comm(L, src, peer_kv_cache=dst, defer_puts=defer, use_comm_stream=side_stream)
+    lib = m.kvcache_comm._lib
+    n0 = lib.b200_kv_launch_count()
+    total_runs = 0
+    for layer in range(L):
+        for sem, blocks in per_sem.items():
+            for start, n in coalesce_blocks(blocks):
+                m.put(sem, layer, start, n)
+                total_runs += 1
+    for sem in per_sem:
+        m.signal_and_flush(sem)
+    put_launches = lib.b200_kv_launch_count() - n0 - len(per_sem)
+    if side_stream:   # the consumer's stream must be ordered after the side stream's signals
+        torch.cuda.current_stream().wait_stream(m.kvcache_comm.comm_stream)
+    for sem in per_sem:
+        m.wait(sem)
+    torch.cuda.synchronize()
+    assert not m.kvcache_comm.timed_out()
+    assert put_launches == (L if defer else total_runs), (put_launches, total_runs)
+    moved = sorted(b for bl in per_sem.values() for b in bl)
+    _check(src, dst, before, {l: moved for l in range(L)})
+    m.destroy_comm()
+
+
+def test_deferred_puts_flush_points():
+    """A deferred put is launched by: a put for another layer, flush(), signal, put_runs/put_layers, destroy."""
+    dev = torch.device("cuda:0")
+    src = _caches(3, 32, 2, 64, 16, torch.half, dev, 6)
+    dst = [(torch.zeros_like(k), torch.zeros_like(v)) for k, v in src]
+    m = _manager(src, dst, 3)
+    c = m.kvcache_comm
+    m.put(0, 0, 0, 4)
+    torch.cuda.synchronize()
+    assert not bool(dst[0][0][:4].any())            # still on the host
+    m.put(0, 1, 4, 4)                               # layer change -> layer 0 leaves
+    torch.cuda.synchronize()
+    assert torch.equal(bits(dst[0][0][:4]), bits(src[0][0][:4])) and not bool(dst[1][0].any())
+    m.flush()
+    torch.cuda.synchronize()
+    assert torch.equal(bits(dst[1][1][4:8]), bits(src[1][1][4:8]))
+    m.put(0, 2, 8, 2)
+    m.put(0, 2, 20, 3)
+    assert c._pending_runs == [(8, 2), (20, 3)]
+    m.signal_and_flush(0)
+    m.wait(0)
+    torch.cuda.synchronize()
+    assert c._pending_runs == [] and torch.equal(bits(dst[2][0][20:23]), bits(src[2][0][20:23]))
+    assert not bool(dst[2][0][10:20].any())
+    with pytest.raises(ValueError):
+        m.put(0, 3, 0, 1)                           # layer out of range
+    m.put(0, 0, 30, 0)                              # empty run: nothing queued
+    assert c._pending_runs == []
+    m.destroy_comm()
+
+
 def test_many_runs_exceeding_one_launch_table():
     """More runs than one kernel-parameter table holds (the library splits the launch)."""
     dev = torch.device("cuda:0")
@@ -198,4 +271,4 @@ def test_two_process_ipc_transfer_bit_exact():
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
     lines = [json.loads(l) for l in res.stdout.splitlines() if l.startswith("{")]
-    assert len(lines) == 6 and all(l["bit_exact"] for l in lines)
+    assert len(lines) == 8 and all(l["bit_exact"] for l in lines)

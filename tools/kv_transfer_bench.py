@@ -19,6 +19,10 @@ Prints one JSON line per (pattern, mode) on rank 0.
 modes   bulk       one put_layers launch per prompt (all layers, all runs) + signal
         per_layer  one put_runs launch per layer per prompt (how the attention backends call it while
                    prefill is still computing, flash_attn.py:81-86) + signal
+        ref_api    exactly the reference call pattern: for every layer, for every prompt (semaphore), for every
+                   coalesced run: put(sem, layer, block_start, num_blocks); after the last layer one
+                   signal_and_flush(sem) per prompt (worker.py:327-331).  The manager batches the deferred
+                   puts of a layer into one launch.
         nccl       baseline: torch.distributed batch_isend_irecv, one P2P op per (layer, K|V, run)
 """
 import argparse
@@ -46,7 +50,7 @@ def main():
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--max-ctas", type=int, default=0)
-    ap.add_argument("--modes", default="bulk,per_layer,nccl")
+    ap.add_argument("--modes", default="bulk,per_layer,ref_api,nccl")
     ap.add_argument("--patterns", default="contiguous,fragmented")
     ap.add_argument("--nccl-max-prompts", type=int, default=2, help="cap for the fragmented NCCL baseline")
     args = ap.parse_args()
@@ -115,7 +119,21 @@ def main():
                 k.zero_()
                 v.zero_()
 
+    def run_ref_api(lists):
+        if is_prompt:
+            for layer in range(L):
+                for p, blocks in enumerate(lists):
+                    for s, n in runs_of[id(blocks)]:
+                        mgr.put(p % 256, layer, s, n)
+            for p in range(len(lists)):
+                mgr.signal_and_flush(p % 256)
+        else:
+            for p in range(len(lists)):
+                mgr.wait(p % 256)
+
     def run_ours(lists, mode):
+        if mode == "ref_api":
+            return run_ref_api(lists)
         for p, blocks in enumerate(lists):
             sem = p % 256
             runs = runs_of[id(blocks)]

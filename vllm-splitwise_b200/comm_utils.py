@@ -85,7 +85,8 @@ class KVCacheCommunicator:
     def __init__(self, block_size: int, num_layers: int, device: torch.device,
                  src_table: Optional[torch.Tensor], dst_table: Optional[torch.Tensor],
                  remote_flags: Optional[int], local_flags: torch.Tensor, my_rank: int, remote_rank: int,
-                 max_ctas: int = 0, wait_max_spins: int = 100000000) -> None:
+                 max_ctas: int = 0, wait_max_spins: int = 100000000, defer_puts: bool = True,
+                 comm_stream: Optional["torch.cuda.Stream"] = None) -> None:
         self.block_size = block_size
         self.num_layers = num_layers
         self.device = device
@@ -101,9 +102,36 @@ class KVCacheCommunicator:
         self.expected = [0] * MAX_SLOT_IDS   # signals awaited per semaphore (token side)
         self.timeout_flag = torch.zeros(1, dtype=torch.int32, device=device)
         self._lib = _lib.load()
+        # put() batching: the attention backends call put() once per coalesced run per semaphore per layer
+        # (reference flash_attn.py:81-86).  With defer_puts the runs of one layer are collected on the host
+        # and leave as ONE launch when the layer changes, on flush(), or before signal/wait -- always on the
+        # same stream and before the signal, so the reference's ordering contract is unchanged.
+        self.defer_puts = defer_puts
+        self._pending_layer = -1
+        self._pending_runs: List[Tuple[int, int]] = []
+        # optional side stream: transfers then overlap the prefill compute that follows on the main stream
+        # (the reference's host proxy copies asynchronously too); signal rides the same side stream.
+        self.comm_stream = comm_stream
+        self._fence = torch.cuda.Event() if comm_stream is not None else None
 
     def _stream(self) -> int:
+        if self.comm_stream is not None:
+            return self.comm_stream.cuda_stream
         return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _order_after_current(self) -> None:
+        """Side stream only: what the caller's stream has enqueued so far (the cache writes) happens first."""
+        if self.comm_stream is not None:
+            self._fence.record(torch.cuda.current_stream(self.device))
+            self.comm_stream.wait_event(self._fence)
+
+    def flush(self) -> None:
+        """Launch the deferred puts (one kernel for every run collected for the pending layer)."""
+        if self._pending_runs:
+            layer, runs = self._pending_layer, self._pending_runs
+            self._pending_layer, self._pending_runs = -1, []
+            self._order_after_current()
+            self._put(2 * layer, 2, tuple(runs))
 
     def _check_sem(self, sem_id: int) -> None:
         if not 0 <= sem_id < MAX_SLOT_IDS:
@@ -125,12 +153,27 @@ class KVCacheCommunicator:
     def put(self, sem_id: int, layer_id: int, block_start: int, num_blocks: int) -> None:
         """K and V blocks [block_start, block_start+num_blocks) of one layer (comm_utils.py:132-147)."""
         self._check_sem(sem_id)
-        self._put(2 * layer_id, 2, [(block_start, num_blocks)])
+        if not 0 <= layer_id < self.num_layers:
+            raise ValueError(f"layer_id {layer_id} out of range [0, {self.num_layers})")
+        if self.src_table is None or self.dst_table is None:
+            raise RuntimeError("put() called on a rank that has no outgoing KV connection")
+        if num_blocks <= 0:
+            return
+        if not self.defer_puts:
+            self._order_after_current()
+            self._put(2 * layer_id, 2, [(block_start, num_blocks)])
+            return
+        if layer_id != self._pending_layer:
+            self.flush()
+            self._pending_layer = layer_id
+        self._pending_runs.append((int(block_start), int(num_blocks)))
 
     def signal_and_flush(self, sem_id: int) -> None:
         self._check_sem(sem_id)
         if self.remote_flags is None:
             raise RuntimeError("signal_and_flush() called on a rank that has no outgoing KV connection")
+        self.flush()
+        self._order_after_current()
         self.sent[sem_id] += 1
         with torch.cuda.device(self.device):
             st = self._lib.b200_kv_signal(self.remote_flags + 8 * sem_id, self.sent[sem_id], self._stream())
@@ -138,21 +181,28 @@ class KVCacheCommunicator:
 
     def wait(self, sem_id: int) -> None:
         self._check_sem(sem_id)
+        self.flush()
         self.expected[sem_id] += 1
         with torch.cuda.device(self.device):
+            # always on the caller's stream: the decode kernels that follow on it must see the blocks
             st = self._lib.b200_kv_wait(self.local_flags.data_ptr() + 8 * sem_id, self.expected[sem_id],
-                                        self.wait_max_spins, self.timeout_flag.data_ptr(), self._stream())
+                                        self.wait_max_spins, self.timeout_flag.data_ptr(),
+                                        torch.cuda.current_stream(self.device).cuda_stream)
         _lib.check(st, "kv wait")
 
     # ---- batched extensions ------------------------------------------------------------
     def put_runs(self, sem_id: int, layer_id: int, runs: Sequence[Tuple[int, int]]) -> None:
         """All coalesced runs of one layer (K and V) in one launch."""
         self._check_sem(sem_id)
+        self.flush()
+        self._order_after_current()
         self._put(2 * layer_id, 2, runs)
 
     def put_layers(self, sem_id: int, first_layer: int, num_layers: int, runs: Sequence[Tuple[int, int]]) -> None:
         """The same runs for a range of layers (K and V) in one launch."""
         self._check_sem(sem_id)
+        self.flush()
+        self._order_after_current()
         self._put(2 * first_layer, 2 * num_layers, runs)
 
     def timed_out(self) -> bool:
@@ -217,7 +267,8 @@ class KVCacheCommManager:
     # -- reference surface -------------------------------------------------------------------
     def setup_comm(self, num_layers: int, kv_cache: List[Tuple[torch.Tensor, torch.Tensor]],
                    peer_kv_cache: Optional[List[Tuple[torch.Tensor, torch.Tensor]]] = None,
-                   peer_flags: Optional[torch.Tensor] = None, max_ctas: int = 0) -> None:
+                   peer_flags: Optional[torch.Tensor] = None, max_ctas: int = 0, defer_puts: bool = True,
+                   use_comm_stream: bool = False) -> None:
         device = kv_cache[0][0].device if self.device is None else self.device
         self.device = device
         k0 = kv_cache[0][0]
@@ -254,9 +305,17 @@ class KVCacheCommManager:
             dist.barrier(group=group)
 
         self.kvcache_comm = KVCacheCommunicator(block_size, num_layers, device, src_table, dst_table, remote_flags,
-                                                local_flags, self.rank, self.corr_worker_rank, max_ctas=max_ctas)
+                                                local_flags, self.rank, self.corr_worker_rank, max_ctas=max_ctas,
+                                                defer_puts=defer_puts,
+                                                comm_stream=torch.cuda.Stream(device) if use_comm_stream else None)
+
+    def flush(self) -> None:
+        """Launch any deferred puts now (optional: call after a layer's put loop for the earliest start)."""
+        self.kvcache_comm.flush()
 
     def destroy_comm(self) -> None:
+        if self.kvcache_comm is not None:
+            self.kvcache_comm.flush()
         if self.device is not None and self.device.type == "cuda":
             torch.cuda.synchronize(self.device)
         for base in self._opened:

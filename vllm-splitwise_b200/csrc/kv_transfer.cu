@@ -23,54 +23,68 @@ struct PutTable {
   int len[kMaxRuns];
   int num_runs;
   int num_bufs;
+  int tile_vecs;              // 16-byte vectors per tile (host: divides a block evenly when it can)
   long long block_bytes;
   const long long* src_ptrs;  // device arrays [num_bufs]
   const long long* dst_ptrs;
 };
 static_assert(sizeof(PutTable) <= 4000, "kernel parameter space");
 
-// Work = num_bufs x (sum of run lengths) blocks, cut into 32 KiB tiles.  CTAs take tiles
-// round-robin; a tile is `kTileVecs` 16-byte vectors of one (buffer, run).  Each thread keeps 8
-// independent 16-byte loads from local HBM in flight and then issues 8 stores to the peer mapping.
+// Work = num_bufs x (sum of run lengths) blocks, cut into tiles of `tile_vecs` 16-byte vectors
+// (<= 32 KiB).  CTAs take tiles round-robin; a tile lies inside one (buffer, run).  Each thread keeps up
+// to 8 independent 16-byte loads from local HBM in flight and then issues the stores to the peer mapping.
 __global__ void __launch_bounds__(kPutThreads) kv_put_blocks_kernel(const __grid_constant__ PutTable t) {
-  __shared__ long long run_tile0[kMaxRuns + 1];  // exclusive prefix of tiles per run
-  __shared__ long long tiles_per_buf;
-  if (threadIdx.x == 0) {
-    long long acc = 0;
-    for (int r = 0; r < t.num_runs; ++r) {
-      run_tile0[r] = acc;
-      const long long vecs = (long long)t.len[r] * t.block_bytes / 16;
-      acc += (vecs + kTileVecs - 1) / kTileVecs;
+  __shared__ int run_tile0[kMaxRuns + 1];  // exclusive prefix of tiles per run
+  __shared__ int warp_sum[kPutThreads / 32];
+  const int tv = t.tile_vecs;
+  {
+    // block-wide exclusive scan of tiles per run: thread i owns runs 2i and 2i+1 (kMaxRuns <= 2 * threads)
+    static_assert(kMaxRuns <= 2 * kPutThreads, "two runs per thread");
+    const int r0 = 2 * threadIdx.x, r1 = r0 + 1;
+    const int c0 = r0 < t.num_runs ? (int)(((long long)t.len[r0] * t.block_bytes / 16 + tv - 1) / tv) : 0;
+    const int c1 = r1 < t.num_runs ? (int)(((long long)t.len[r1] * t.block_bytes / 16 + tv - 1) / tv) : 0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int incl = c0 + c1;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int n = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += n;
     }
-    run_tile0[t.num_runs] = acc;
-    tiles_per_buf = acc;
+    if (lane == 31) warp_sum[warp] = incl;
+    __syncthreads();
+    int base = 0;
+    for (int w = 0; w < warp; ++w) base += warp_sum[w];
+    const int excl = base + incl - (c0 + c1);
+    if (r0 < t.num_runs) run_tile0[r0] = excl;
+    if (r1 < t.num_runs) run_tile0[r1] = excl + c0;
+    if (threadIdx.x == kPutThreads - 1) run_tile0[t.num_runs] = base + incl;
+    __syncthreads();
   }
-  __syncthreads();
-  const long long tpb = tiles_per_buf;
+  const long long tpb = run_tile0[t.num_runs];
   const long long total = tpb * t.num_bufs;
   for (long long tile = blockIdx.x; tile < total; tile += gridDim.x) {
     const int buf = (int)(tile / tpb);
-    const long long rt = tile - (long long)buf * tpb;
+    const int rt = (int)(tile - (long long)buf * tpb);
     int lo = 0, hi = t.num_runs - 1;  // last run with run_tile0[r] <= rt
     while (lo < hi) {
       const int mid = (lo + hi + 1) >> 1;
       if (run_tile0[mid] <= rt) lo = mid; else hi = mid - 1;
     }
     const long long run_vecs = (long long)t.len[lo] * t.block_bytes / 16;
-    const long long v0 = (rt - run_tile0[lo]) * kTileVecs;
-    const long long v1 = min(run_vecs, v0 + kTileVecs);
+    const long long v0 = (long long)(rt - run_tile0[lo]) * tv;
+    const long long v1 = min(run_vecs, v0 + tv);
     const long long byte0 = (long long)t.start[lo] * t.block_bytes;
     const uint4* src = reinterpret_cast<const uint4*>(t.src_ptrs[buf] + byte0);
     uint4* dst = reinterpret_cast<uint4*>(t.dst_ptrs[buf] + byte0);
-    long long i = v0 + threadIdx.x;
-    for (; i + 7 * kPutThreads < v1; i += 8 * kPutThreads) {
+    for (long long i = v0 + threadIdx.x; i < v1; i += 8 * kPutThreads) {
       uint4 r[8];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) r[k] = ld_nc_v4(src + i + k * kPutThreads);
+      for (int k = 0; k < 8; ++k)
+        if (i + k * kPutThreads < v1) r[k] = ld_nc_v4(src + i + k * kPutThreads);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) st_na_v4(dst + i + k * kPutThreads, r[k]);
+      for (int k = 0; k < 8; ++k)
+        if (i + k * kPutThreads < v1) st_na_v4(dst + i + k * kPutThreads, r[k]);
     }
-    for (; i < v1; i += kPutThreads) st_na_v4(dst + i, ld_nc_v4(src + i));
   }
 }
 
@@ -168,6 +182,11 @@ B200_API int b200_kv_put_blocks(const int64_t* src_ptrs, const int64_t* dst_ptrs
   if (block_bytes % 16 != 0) return B200_ERR_ALIGN;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (max_ctas <= 0) max_ctas = 2 * num_sms(-1);
+  // Tile = the largest even split of one block that stays <= 32 KiB (a 40 KiB block -> two 20 KiB tiles, not
+  // 32 + 8), so single-block runs of a fragmented block list load the CTAs evenly.
+  const long long block_vecs = block_bytes / 16;
+  const long long pieces = (block_vecs + kTileVecs - 1) / kTileVecs;
+  const int tile_vecs = (int)((block_vecs + pieces - 1) / pieces);
   for (int r0 = 0; r0 < num_runs; r0 += kMaxRuns) {
     PutTable t;
     t.num_runs = std::min(kMaxRuns, num_runs - r0);
@@ -176,8 +195,10 @@ B200_API int b200_kv_put_blocks(const int64_t* src_ptrs, const int64_t* dst_ptrs
       t.start[r] = runs[2 * (r0 + r)];
       t.len[r] = runs[2 * (r0 + r) + 1];
       if (t.start[r] < 0 || t.len[r] < 0) return B200_ERR_ARG;
-      tiles += ((long long)t.len[r] * block_bytes / 16 + kTileVecs - 1) / kTileVecs;
+      tiles += ((long long)t.len[r] * block_vecs + tile_vecs - 1) / tile_vecs;
     }
+    if (tiles * num_bufs > INT32_MAX) return B200_ERR_ARG;
+    t.tile_vecs = tile_vecs;
     t.num_bufs = num_bufs;
     t.block_bytes = block_bytes;
     t.src_ptrs = reinterpret_cast<const long long*>(src_ptrs);
