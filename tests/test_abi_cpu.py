@@ -82,9 +82,35 @@ def test_status_strings_and_validation_without_gpu():
         _lib.check(_lib.ERR_HEAD_SIZE, "paged_attention_v1", 72)
 
 
-def test_ops_refuse_cpu_tensors():
+def _bindings():
+    """(name, ops, cache_ops) for every binding of the C ABI that is built: compiled pybind front, ctypes."""
+    from vllm_splitwise_b200 import _C
+    from vllm_splitwise_b200._C import _ctypes_cache_ops, _ctypes_ops
+    out = [("ctypes", _ctypes_ops, _ctypes_cache_ops)]
+    if _C.BINDING == "torch":
+        out.append(("torch", _C.ops, _C.cache_ops))
+    return out
+
+
+def test_compiled_binding_is_built_and_selected():
+    """build() compiles lib/_b200_torch.so; `_C` must pick it (the ctypes layer is the spare)."""
+    from vllm_splitwise_b200 import _C
+    assert os.path.exists(os.path.join(ROOT, "vllm-splitwise_b200", "lib", "_b200_torch.so"))
+    assert _C.BINDING == "torch"
+    for sub, names in (("ops", ["paged_attention_v1", "paged_attention_v2"]),
+                       ("cache_ops", ["reshape_and_cache", "copy_blocks", "swap_blocks", "convert_fp8_e5m2"]),
+                       ("cuda_utils", ["get_device_attribute", "get_max_shared_memory_per_block_device_attribute"])):
+        for n in names:
+            assert callable(getattr(getattr(_C, sub), n)), (sub, n)
+
+
+@pytest.mark.parametrize("which", ["ctypes", "torch"])
+def test_ops_refuse_cpu_tensors(which):
     import torch
-    from vllm_splitwise_b200._C import cache_ops, ops
+    found = {n: (o, c) for n, o, c in _bindings()}
+    if which not in found:
+        pytest.skip(f"{which} binding not built")
+    ops, cache_ops = found[which]
     q = torch.zeros(1, 2, 64)
     with pytest.raises(RuntimeError, match="no CPU path"):
         ops.paged_attention_v1(q, q, q, q, 2, 1.0, torch.zeros(1, 1, dtype=torch.int32),

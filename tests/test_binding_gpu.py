@@ -1,0 +1,76 @@
+"""Both bindings of the C ABI (compiled pybind front, ctypes) drive the same kernels: identical bits on the
+same inputs, the same RuntimeError text for the reference's error cases (csrc/attention/attention_kernels.cu
+:674-676,706-708), and the compiled one is the binding `_C` exposes."""
+import pytest
+import torch
+
+from _util import bits, make_attention_inputs, run_v1, run_v2
+
+pytestmark = pytest.mark.gpu
+
+
+def _both():
+    from vllm_splitwise_b200 import _C
+    from vllm_splitwise_b200._C import _ctypes_cache_ops, _ctypes_ops
+    if _C.BINDING != "torch":
+        pytest.skip("compiled binding not built")
+    return (_C.ops, _C.cache_ops), (_ctypes_ops, _ctypes_cache_ops)
+
+
+@pytest.mark.parametrize("heads,dtype,kv", [((32, 32), torch.half, "auto"), ((32, 8), torch.bfloat16, "fp8_e5m2")])
+def test_attention_same_bits(heads, dtype, kv):
+    (ops_a, _), (ops_b, _) = _both()
+    a = make_attention_inputs(num_seqs=5, num_heads=heads, head_size=128, block_size=16, dtype=dtype, kv_cache_dtype=kv,
+                              num_blocks=512, context_lens=[1, 100, 777, 1500, 2049], use_alibi=True, seed=2)
+    assert torch.equal(bits(run_v1(ops_a, a)), bits(run_v1(ops_b, a)))
+    for x, y in zip(run_v2(ops_a, a), run_v2(ops_b, a)):
+        assert torch.equal(torch.nan_to_num(x.float()), torch.nan_to_num(y.float()))
+
+
+def test_cache_ops_same_bits():
+    (_, ca), (_, cb) = _both()
+    dev = "cuda"
+    torch.manual_seed(0)
+    N, H, D, bs, NB = 70, 4, 128, 16, 40
+    key = torch.randn(N, H, D, dtype=torch.half, device=dev)
+    val = torch.randn(N, H, D, dtype=torch.half, device=dev)
+    slots = torch.randperm(NB * bs, device=dev)[:N]
+    slots[3] = -1
+    res = []
+    for c in (ca, cb):
+        kc = torch.zeros(NB, H, D // 8, bs, 8, dtype=torch.half, device=dev)
+        vc = torch.zeros(NB, H, D, bs, dtype=torch.half, device=dev)
+        c.reshape_and_cache(key, val, kc, vc, slots, "auto")
+        c.copy_blocks([kc], [vc], {0: [5, 6], 2: [7]})
+        dst = torch.zeros_like(vc)
+        c.swap_blocks(vc, dst, {1: 3, 4: 0})
+        host = torch.zeros(NB, H, D, bs, dtype=torch.half).pin_memory()
+        c.swap_blocks(vc, host, {1: 2, 2: 3, 9: 9})
+        back = torch.zeros_like(vc)
+        c.swap_blocks(host, back, {2: 1, 3: 2})
+        k8 = torch.empty(kc.shape, dtype=torch.uint8, device=dev)
+        c.convert_fp8_e5m2(kc, k8)
+        torch.cuda.synchronize()
+        res.append([bits(kc), bits(vc), bits(dst), bits(host.to(dev)), bits(back), k8])
+    for x, y in zip(*res):
+        assert torch.equal(x, y)
+
+
+def test_same_errors():
+    for ops, cache in _both():
+        q = torch.zeros(2, 4, 72, dtype=torch.half, device="cuda")
+        kc = torch.zeros(4, 4, 9, 16, 8, dtype=torch.half, device="cuda")
+        vc = torch.zeros(4, 4, 72, 16, dtype=torch.half, device="cuda")
+        bt = torch.zeros(2, 1, dtype=torch.int32, device="cuda")
+        cl = torch.ones(2, dtype=torch.int32, device="cuda")
+        with pytest.raises(RuntimeError, match="Unsupported head size: 72"):
+            ops.paged_attention_v1(torch.empty_like(q), q, kc, vc, 4, 1.0, bt, cl, 16, 1, None, "auto")
+        q = torch.zeros(2, 4, 64, dtype=torch.half, device="cuda")
+        kc = torch.zeros(4, 4, 8, 4, 8, dtype=torch.half, device="cuda")
+        vc = torch.zeros(4, 4, 64, 4, dtype=torch.half, device="cuda")
+        with pytest.raises(RuntimeError, match="Unsupported block size: 4"):
+            ops.paged_attention_v1(torch.empty_like(q), q, kc, vc, 4, 1.0, bt, cl, 4, 1, None, "auto")
+        with pytest.raises(RuntimeError, match="Unsupported data type"):
+            ops.paged_attention_v1(torch.empty_like(q), q, kc, vc, 4, 1.0, bt, cl, 16, 1, None, "int8")
+        with pytest.raises(RuntimeError, match="same GPU|Invalid device"):
+            cache.swap_blocks(torch.zeros(2, 4), torch.zeros(2, 4), {0: 1})

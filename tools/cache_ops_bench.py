@@ -59,7 +59,7 @@ def bench_reshape(name, desc, N, Hq, Hkv, D, bs, dtype, kv, iters, ours, ref, co
     ce = 1 if kv == "fp8_e5m2" else es
     x = 16 // ce
     cdt = torch.uint8 if kv == "fp8_e5m2" else dtype
-    NB = (N + bs - 1) // bs + 8
+    NB = ((N + bs - 1) // bs if contiguous_slots else N) + 8
     per_call = N * Hkv * D * 2 * (es + ce) + N * 8
     nbuf = max(2, min(8, int(300e6 // max(per_call, 1)) + 1))
     g = torch.Generator(device="cpu").manual_seed(0)

@@ -1,0 +1,261 @@
+// Thin PyTorch front of libb200kv.so: a pybind11 module with the reference's `vllm._C` shape
+// (csrc/pybind.cpp:6-129): submodules `ops`, `cache_ops`, `cuda_utils`, the same positional signatures.
+// Nothing here computes: each function checks the tensors the way the reference launchers do
+// (dtype / device / density), reads pointers, sizes and strides, and calls the C ABI of
+// include/b200_kv.h on torch's current stream.  Status codes become c10::Error (Python RuntimeError)
+// with the reference's message text.  The ctypes layer in vllm_splitwise_b200/_C/*.py is the same
+// binding written in Python; this compiled one exists because a decode step calls two ops per layer and
+// the interpreter-level marshalling (~10 us per call) is then comparable to the kernels themselves.
+#include <torch/extension.h>
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGraphsC10Utils.h>
+#include <c10/cuda/CUDAGuard.h>
+
+#include <map>
+#include <mutex>
+#include <vector>
+
+#include "../../include/b200_kv.h"
+
+namespace {
+
+int dtype_code(const torch::Tensor& t, const char* what) {
+  switch (t.scalar_type()) {
+    case at::ScalarType::Float: return B200_F32;
+    case at::ScalarType::Half: return B200_F16;
+    case at::ScalarType::BFloat16: return B200_BF16;
+    case at::ScalarType::Byte: return B200_U8_E5M2;
+    default: TORCH_CHECK(false, "Unsupported data type: ", t.scalar_type(), " (", what, ")");
+  }
+  return -1;
+}
+
+void check_status(int st, const char* what, int64_t detail = -1) {
+  if (st == B200_OK) return;
+  std::string msg = b200_kv_strerror(st);
+  if (st == B200_ERR_CUDA) msg += std::string(": ") + b200_kv_last_cuda_error();
+  if (detail >= 0 && (st == B200_ERR_HEAD_SIZE || st == B200_ERR_BLOCK_SIZE)) msg += ": " + std::to_string(detail);
+  TORCH_CHECK(false, what, ": ", msg);
+}
+
+void require_cuda(const torch::Tensor& t, const char* name) {
+  TORCH_CHECK(t.is_cuda(), name, " must be a CUDA tensor (there is no CPU path)");
+}
+
+int cache_dtype_code(const std::string& kv_cache_dtype, const torch::Tensor& query, const torch::Tensor& cache) {
+  if (kv_cache_dtype == "auto") {
+    TORCH_CHECK(cache.scalar_type() == query.scalar_type(), "Unsupported data type: cache ", cache.scalar_type(),
+                " with query ", query.scalar_type());
+    return dtype_code(query, "query");
+  }
+  if (kv_cache_dtype == "fp8_e5m2") {
+    TORCH_CHECK(cache.scalar_type() == at::ScalarType::Byte, "Unsupported data type: fp8_e5m2 cache must be uint8");
+    return B200_U8_E5M2;
+  }
+  TORCH_CHECK(false, "Unsupported data type of kv cache: ", kv_cache_dtype);
+  return -1;
+}
+
+b200_paged_attn_args_t fill_args(torch::Tensor& out, torch::Tensor& query, torch::Tensor& key_cache,
+                                 torch::Tensor& value_cache, int num_kv_heads, float scale,
+                                 torch::Tensor& block_tables, torch::Tensor& context_lens, int block_size,
+                                 int max_context_len, const c10::optional<torch::Tensor>& alibi_slopes,
+                                 const std::string& kv_cache_dtype) {
+  require_cuda(out, "out"); require_cuda(query, "query"); require_cuda(key_cache, "key_cache");
+  require_cuda(value_cache, "value_cache"); require_cuda(block_tables, "block_tables");
+  require_cuda(context_lens, "context_lens");
+  TORCH_CHECK(block_tables.scalar_type() == at::ScalarType::Int && context_lens.scalar_type() == at::ScalarType::Int,
+              "block_tables and context_lens must be int32");
+  TORCH_CHECK(query.dim() == 3 && query.stride(2) == 1 && query.stride(1) == query.size(2) && out.is_contiguous(),
+              "query must be dense in its last two dims and out contiguous");
+  b200_paged_attn_args_t a{};
+  a.out = out.data_ptr();
+  a.query = query.data_ptr();
+  a.key_cache = key_cache.data_ptr();
+  a.value_cache = value_cache.data_ptr();
+  a.block_tables = block_tables.data_ptr<int32_t>();
+  a.context_lens = context_lens.data_ptr<int32_t>();
+  if (alibi_slopes.has_value() && alibi_slopes->defined()) {
+    TORCH_CHECK(alibi_slopes->scalar_type() == at::ScalarType::Float, "alibi_slopes must be float32");
+    a.alibi_slopes = alibi_slopes->data_ptr<float>();
+  }
+  a.scale = scale;
+  a.num_seqs = (int32_t)query.size(0);
+  a.num_heads = (int32_t)query.size(1);
+  a.head_size = (int32_t)query.size(2);
+  a.num_kv_heads = num_kv_heads;
+  a.block_size = block_size;
+  a.max_context_len = max_context_len;
+  a.max_num_blocks_per_seq = (int32_t)block_tables.size(1);
+  a.q_stride = query.stride(0);
+  a.kv_block_stride = key_cache.stride(0);
+  a.kv_head_stride = key_cache.stride(1);
+  a.query_dtype = dtype_code(query, "query");
+  a.cache_dtype = cache_dtype_code(kv_cache_dtype, query, key_cache);
+  a.device = query.get_device();
+  return a;
+}
+
+// Scratch for the internal split of v1 calls: one zero-initialised buffer per device, grown on demand
+// (never inside a CUDA-graph capture).  The head of it holds reduce tickets the kernel leaves at zero.
+constexpr int64_t kWorkspaceCap = 256ll << 20;
+std::mutex g_ws_mutex;
+std::map<int, torch::Tensor> g_workspaces;
+
+torch::Tensor* workspace_for(const b200_paged_attn_args_t& a, const torch::Tensor& like) {
+  const int64_t need = std::min<int64_t>(b200_paged_attention_workspace_bytes(&a), kWorkspaceCap);
+  std::lock_guard<std::mutex> lock(g_ws_mutex);
+  auto it = g_workspaces.find(a.device);
+  if (it == g_workspaces.end() || it->second.numel() < need) {
+    if (c10::cuda::currentStreamCaptureStatusMayInitCtx() != c10::cuda::CaptureStatus::None)
+      return it == g_workspaces.end() ? nullptr : &it->second;
+    g_workspaces[a.device] = torch::zeros({need}, like.options().dtype(torch::kUInt8));
+    it = g_workspaces.find(a.device);
+  }
+  return &it->second;
+}
+
+void paged_attention_v1(torch::Tensor& out, torch::Tensor& query, torch::Tensor& key_cache, torch::Tensor& value_cache,
+                        int num_kv_heads, float scale, torch::Tensor& block_tables, torch::Tensor& context_lens,
+                        int block_size, int max_context_len, const c10::optional<torch::Tensor>& alibi_slopes,
+                        const std::string& kv_cache_dtype) {
+  b200_paged_attn_args_t a = fill_args(out, query, key_cache, value_cache, num_kv_heads, scale, block_tables,
+                                       context_lens, block_size, max_context_len, alibi_slopes, kv_cache_dtype);
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  if (a.max_context_len >= 256) {
+    if (torch::Tensor* ws = workspace_for(a, query)) {
+      a.workspace = ws->data_ptr();
+      a.workspace_bytes = ws->numel();
+    }
+  }
+  const int st = b200_paged_attention_v1(&a, at::cuda::getCurrentCUDAStream().stream());
+  check_status(st, "paged_attention_v1", st == B200_ERR_HEAD_SIZE ? a.head_size : a.block_size);
+}
+
+void paged_attention_v2(torch::Tensor& out, torch::Tensor& exp_sums, torch::Tensor& max_logits, torch::Tensor& tmp_out,
+                        torch::Tensor& query, torch::Tensor& key_cache, torch::Tensor& value_cache, int num_kv_heads,
+                        float scale, torch::Tensor& block_tables, torch::Tensor& context_lens, int block_size,
+                        int max_context_len, const c10::optional<torch::Tensor>& alibi_slopes,
+                        const std::string& kv_cache_dtype) {
+  b200_paged_attn_args_t a = fill_args(out, query, key_cache, value_cache, num_kv_heads, scale, block_tables,
+                                       context_lens, block_size, max_context_len, alibi_slopes, kv_cache_dtype);
+  TORCH_CHECK(exp_sums.scalar_type() == at::ScalarType::Float && max_logits.scalar_type() == at::ScalarType::Float,
+              "exp_sums and max_logits must be float32");
+  TORCH_CHECK(tmp_out.scalar_type() == query.scalar_type(), "tmp_out must have the query dtype");
+  TORCH_CHECK(exp_sums.is_contiguous() && max_logits.is_contiguous() && tmp_out.is_contiguous(),
+              "v2 scratch tensors must be contiguous");
+  a.exp_sums = exp_sums.data_ptr<float>();
+  a.max_logits = max_logits.data_ptr<float>();
+  a.tmp_out = tmp_out.data_ptr();
+  a.max_num_partitions = (int32_t)exp_sums.size(2);
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  const int st = b200_paged_attention_v2(&a, at::cuda::getCurrentCUDAStream().stream());
+  check_status(st, "paged_attention_v2", st == B200_ERR_HEAD_SIZE ? a.head_size : a.block_size);
+}
+
+void check_kv_source(const torch::Tensor& t, const char* name) {
+  require_cuda(t, name);
+  TORCH_CHECK(t.dim() == 3 && t.stride(2) == 1 && t.stride(1) == t.size(2), "key/value must be dense in their last two dims");
+}
+
+void reshape_and_cache(torch::Tensor& key, torch::Tensor& value, torch::Tensor& key_cache, torch::Tensor& value_cache,
+                       torch::Tensor& slot_mapping, const std::string& kv_cache_dtype) {
+  check_kv_source(key, "key"); check_kv_source(value, "value");
+  require_cuda(key_cache, "key_cache"); require_cuda(value_cache, "value_cache"); require_cuda(slot_mapping, "slot_mapping");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Long && slot_mapping.is_contiguous(),
+              "slot_mapping must be a contiguous int64 tensor");
+  const int cache_code = cache_dtype_code(kv_cache_dtype, key, key_cache);
+  TORCH_CHECK(key_cache.is_contiguous() && value_cache.is_contiguous(), "key_cache/value_cache must be contiguous");
+  const at::cuda::OptionalCUDAGuard guard(device_of(key));
+  const int st = b200_reshape_and_cache(
+      key.data_ptr(), value.data_ptr(), key_cache.data_ptr(), value_cache.data_ptr(), slot_mapping.data_ptr<int64_t>(),
+      (int32_t)key.size(0), (int32_t)key.size(1), (int32_t)key.size(2), (int32_t)key_cache.size(3),
+      (int32_t)key_cache.size(4), key.stride(0), value.stride(0), key_cache.size(0), dtype_code(key, "key"), cache_code,
+      at::cuda::getCurrentCUDAStream().stream());
+  check_status(st, "reshape_and_cache");
+}
+
+void copy_blocks(std::vector<torch::Tensor>& key_caches, std::vector<torch::Tensor>& value_caches,
+                 const std::map<int64_t, std::vector<int64_t>>& block_mapping) {
+  const int num_layers = (int)key_caches.size();
+  TORCH_CHECK(num_layers == (int)value_caches.size(), "key_caches and value_caches must have the same length");
+  if (num_layers == 0) return;
+  require_cuda(key_caches[0], "key_caches[0]");
+  std::vector<int64_t> kp(num_layers), vp(num_layers), pairs;
+  for (int l = 0; l < num_layers; ++l) {
+    kp[l] = reinterpret_cast<int64_t>(key_caches[l].data_ptr());
+    vp[l] = reinterpret_cast<int64_t>(value_caches[l].data_ptr());
+  }
+  for (const auto& kv : block_mapping)  // std::map: ascending source block (reference cache_kernels.cu:119-126)
+    for (int64_t dst : kv.second) {
+      pairs.push_back(kv.first);
+      pairs.push_back(dst);
+    }
+  if (pairs.empty()) return;
+  const int64_t block_bytes = key_caches[0][0].numel() * key_caches[0].element_size();
+  const at::cuda::OptionalCUDAGuard guard(device_of(key_caches[0]));
+  const int st = b200_copy_blocks(kp.data(), vp.data(), num_layers, pairs.data(), (int32_t)(pairs.size() / 2), block_bytes,
+                                  at::cuda::getCurrentCUDAStream().stream());
+  check_status(st, "copy_blocks");
+}
+
+void swap_blocks(torch::Tensor& src, torch::Tensor& dst, const std::map<int64_t, int64_t>& block_mapping) {
+  int kind;
+  torch::Device dev = src.device();
+  if (src.is_cuda() && dst.is_cuda()) {
+    TORCH_CHECK(src.get_device() == dst.get_device(), "src and dst must be on the same GPU");
+    kind = B200_SWAP_D2D;
+  } else if (src.is_cuda() && dst.is_cpu()) {
+    kind = B200_SWAP_D2H;
+  } else if (src.is_cpu() && dst.is_cuda()) {
+    kind = B200_SWAP_H2D;
+    dev = dst.device();
+  } else {
+    TORCH_CHECK(false, "Invalid device combination");
+  }
+  std::vector<int64_t> pairs;
+  pairs.reserve(2 * block_mapping.size());
+  for (const auto& kv : block_mapping) {
+    pairs.push_back(kv.first);
+    pairs.push_back(kv.second);
+  }
+  if (pairs.empty()) return;
+  const int64_t block_bytes = src.element_size() * src[0].numel();
+  const at::cuda::CUDAGuard guard(dev);
+  const int st = b200_swap_blocks(src.data_ptr(), dst.data_ptr(), block_bytes, pairs.data(), (int32_t)(pairs.size() / 2),
+                                  kind, src.is_cuda() ? src.get_device() : -1, dst.is_cuda() ? dst.get_device() : -1,
+                                  at::cuda::getCurrentCUDAStream().stream());
+  check_status(st, "swap_blocks");
+}
+
+void convert_fp8_e5m2(torch::Tensor& src_cache, torch::Tensor& dst_cache) {
+  require_cuda(src_cache, "src_cache"); require_cuda(dst_cache, "dst_cache");
+  TORCH_CHECK(src_cache.numel() == dst_cache.numel(), "src_cache and dst_cache must have the same number of elements");
+  TORCH_CHECK(src_cache.is_contiguous() && dst_cache.is_contiguous(), "convert_fp8_e5m2 needs contiguous tensors");
+  const at::cuda::OptionalCUDAGuard guard(device_of(src_cache));
+  const int st = b200_convert_fp8_e5m2(src_cache.data_ptr(), dst_cache.data_ptr(), src_cache.numel(),
+                                       dtype_code(src_cache, "src_cache"), dtype_code(dst_cache, "dst_cache"),
+                                       at::cuda::getCurrentCUDAStream().stream());
+  check_status(st, "convert_fp8_e5m2");
+}
+
+}  // namespace
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  pybind11::module ops = m.def_submodule("ops", "paged attention (reference csrc/ops.h:5-34)");
+  ops.def("paged_attention_v1", &paged_attention_v1,
+          "Compute the attention between an input query and the cached keys/values using PagedAttention.");
+  ops.def("paged_attention_v2", &paged_attention_v2, "PagedAttention V2.");
+  pybind11::module cache_ops = m.def_submodule("cache_ops", "cache writes and block moves (reference csrc/cache.h:8-29)");
+  cache_ops.def("swap_blocks", &swap_blocks, "Swap in (out) the cache blocks from src to dst");
+  cache_ops.def("copy_blocks", &copy_blocks, "Copy the cache blocks from src to dst");
+  cache_ops.def("reshape_and_cache", &reshape_and_cache, "Reshape the key and value tensors and cache them");
+  cache_ops.def("convert_fp8_e5m2", &convert_fp8_e5m2, "Convert the key and value cache to fp8_e5m2 data type");
+  pybind11::module cuda_utils = m.def_submodule("cuda_utils", "device attributes (reference csrc/pybind.cpp:101-111)");
+  cuda_utils.def("get_device_attribute",
+                 [](int attribute, int device_id) { return b200_get_device_attribute(attribute, device_id); },
+                 "Gets the specified device attribute.");
+  cuda_utils.def("get_max_shared_memory_per_block_device_attribute",
+                 [](int device_id) { return b200_get_max_shared_memory_per_block_device_attribute(device_id); },
+                 "Gets the maximum shared memory per block device attribute.");
+}
