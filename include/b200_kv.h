@@ -165,6 +165,34 @@ B200_API int b200_swap_blocks(const void* src, void* dst, int64_t block_bytes, c
 B200_API int b200_convert_fp8_e5m2(const void* src, void* dst, int64_t numel, int32_t src_dtype,
                           int32_t dst_dtype, b200_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Rotary position embedding, alone and fused with the cache write (the op the model runs right
+ * before reshape_and_cache: vllm/model_executor/models/llama.py:156-158).
+ * ------------------------------------------------------------------------------------------ */
+
+/* Replaces rotary_embedding (csrc/ops.h:48-54, csrc/pos_encoding_kernels.cu:77-95,126-165) and, with
+ * cos_sin_cache_offsets != NULL, batched_rotary_embedding (csrc/ops.h:56-63, :97-123,167-209).
+ * In place on query [num_tokens, num_heads, head_size] (row stride query_stride) and key
+ * [num_tokens, num_kv_heads, head_size] (row stride key_stride); positions int64 [num_tokens];
+ * cos_sin_cache [max_position, rot_dim] of the query dtype: rot_dim/2 cosines then rot_dim/2 sines.
+ * is_neox: pairs (i, i + rot_dim/2); otherwise GPT-J pairs (2i, 2i+1).  dtype F32/F16/BF16.
+ * Every product and sum is rounded to the element type, as the reference's scalar_t arithmetic. */
+B200_API int b200_rotary_embedding(const int64_t* positions, void* query, void* key, const void* cos_sin_cache,
+                          const int64_t* cos_sin_cache_offsets, int64_t num_tokens, int32_t num_heads,
+                          int32_t num_kv_heads, int32_t head_size, int32_t rot_dim, int64_t query_stride,
+                          int64_t key_stride, int32_t is_neox, int32_t dtype, b200_stream_t stream);
+
+/* rotary_embedding(positions, query, key) followed by reshape_and_cache(key, value, ...) with the same
+ * results bit for bit: query and key are rotated in place, the rotated key and the value go to the
+ * paged cache (negative slots skip the cache write only).  Decode-sized calls are ONE launch (the K
+ * row is read once); prefill-sized calls run the two kernels back to back.  Arguments as the two ops. */
+B200_API int b200_rotary_embedding_reshape_and_cache(
+    const int64_t* positions, void* query, void* key, const void* value, const void* cos_sin_cache,
+    int64_t num_tokens, int32_t num_heads, int32_t num_kv_heads, int32_t head_size, int32_t rot_dim,
+    int64_t query_stride, int64_t key_stride, int64_t value_stride, int32_t is_neox, void* key_cache,
+    void* value_cache, const int64_t* slot_mapping, int32_t block_size, int32_t x, int64_t num_blocks,
+    int32_t src_dtype, int32_t cache_dtype, b200_stream_t stream);
+
 /* Replaces cuda_utils (csrc/cuda_utils_kernels.cu:5-35). */
 B200_API int b200_get_device_attribute(int32_t attribute, int32_t device_id);
 B200_API int b200_get_max_shared_memory_per_block_device_attribute(int32_t device_id);

@@ -98,6 +98,45 @@ def test_reshape_and_cache_prefill_sized(cache_ops, kv_cache_factory, dtype, kv_
         assert _same(kc, kc_r) and _same(vc, vc_r)
 
 
+@pytest.mark.parametrize("kv_cache_dtype", ["auto", "fp8_e5m2"])
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("block_size", BLOCK_SIZES)
+@pytest.mark.parametrize("max_prompt_len", [64, 77])
+def test_reshape_and_cache_prompt_batches(cache_ops, kv_cache_factory, max_prompt_len, block_size, dtype, kv_cache_dtype):
+    """The prefill slot_mapping the model runner builds (model_runner.py:126-272): [B, max_prompt_len] flattened,
+    token i of a prompt at block_table[i // bs] * bs + i % bs, padding -1.  max_prompt_len 64 keeps every tile
+    aligned to a block (vector row stores); 77 makes tiles straddle prompts, blocks and padding (element path).
+    Also a source whose rows are not 16-byte aligned.  Bit-exact against the oracle and the reference kernel."""
+    from oracle import paged_kv_oracle as O
+    _seed(3)
+    B, H, D, NB = 5, 4, 128, 256
+    lens = [max_prompt_len, 1, max_prompt_len - 3, 17, max_prompt_len // 2]
+    free = list(range(NB))
+    random.shuffle(free)
+    slots = []
+    for n in lens:
+        table = [free.pop() for _ in range((n + block_size - 1) // block_size)]
+        row = [table[i // block_size] * block_size + i % block_size for i in range(n)]
+        slots += row + [-1] * (max_prompt_len - n)
+    slot_mapping = torch.tensor(slots, dtype=torch.long, device="cuda")
+    N = B * max_prompt_len
+    ref = load_ref_cuda()
+    for misalign in (0, 1):
+        buf = torch.randn(N * 3 * H * D + 8, dtype=dtype, device="cuda")
+        qkv = buf[misalign:misalign + N * 3 * H * D].view(N, 3, H, D)
+        _, key, value = qkv.unbind(dim=1)
+        kcs, vcs = kv_cache_factory(NB, block_size, 1, H, D, kv_cache_dtype, dtype, 0, "cuda")
+        kc, vc = kcs[0], vcs[0]
+        kc_o, vc_o = kc.cpu().clone(), vc.cpu().clone()
+        kc_r, vc_r = kc.clone(), vc.clone()
+        cache_ops.reshape_and_cache(key, value, kc, vc, slot_mapping, kv_cache_dtype)
+        O.reshape_and_cache(key.cpu(), value.cpu(), kc_o, vc_o, slot_mapping.cpu(), kv_cache_dtype)
+        assert _same(kc, kc_o) and _same(vc, vc_o)
+        if ref is not None:
+            ref.cache_ops.reshape_and_cache(key, value, kc_r, vc_r, slot_mapping, kv_cache_dtype)
+            assert _same(kc, kc_r) and _same(vc, vc_r)
+
+
 def test_reshape_and_cache_fp8_special_values(cache_ops):
     """Saturation, signed zeros, subnormals, Inf, NaN through the fused fp8 write (quant_utils.cuh:164-192)."""
     from oracle import paged_kv_oracle as O

@@ -42,7 +42,32 @@ def timeit(fn, iters, nbuf):
     return beg.elapsed_time(end) / iters
 
 
-def emit(name, desc, nbytes, ms, ref_ms, exact, note="", bound="hbm"):
+def timeit_graph(fn, nbuf, calls=24, replays=20):
+    """GPU time per call with the CPU out of the way: `calls` calls captured into one CUDA graph (the decode
+    path is graph-captured in the reference, model_runner.py:826-834), replayed `replays` times."""
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for i in range(3):
+            fn(i % nbuf)
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for i in range(calls):
+            fn(i % nbuf)
+    g.replay()
+    torch.cuda.synchronize()
+    beg, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    beg.record()
+    for _ in range(replays):
+        g.replay()
+    end.record()
+    torch.cuda.synchronize()
+    return beg.elapsed_time(end) / (replays * calls)
+
+
+def emit(name, desc, nbytes, ms, ref_ms, exact, note="", bound="hbm", graph_ms=None, ref_graph_ms=None):
     pk = peak()
     line = {"case": name, "workload": desc, "algorithmic_bytes": nbytes, "ms": round(ms, 5),
             "GBps": round(nbytes / ms / 1e6, 1), "bound": bound,
@@ -50,6 +75,14 @@ def emit(name, desc, nbytes, ms, ref_ms, exact, note="", bound="hbm"):
             "reference_cuda_ms": round(ref_ms, 5) if ref_ms else None,
             "speedup_vs_reference_cuda": round(ref_ms / ms, 2) if ref_ms else None,
             "bit_exact_vs_reference_cuda": exact, "note": note}
+    if graph_ms is not None:
+        line["graph_replay_ms"] = round(graph_ms, 5)
+        line["graph_replay_GBps"] = round(nbytes / graph_ms / 1e6, 1)
+        if bound == "hbm":
+            line["graph_replay_frac_of_measured_hbm"] = round(nbytes / graph_ms / 1e6 / pk, 4)
+        if ref_graph_ms:
+            line["reference_cuda_graph_replay_ms"] = round(ref_graph_ms, 5)
+            line["graph_replay_speedup_vs_reference_cuda"] = round(ref_graph_ms / graph_ms, 2)
     print(json.dumps(line), flush=True)
 
 
@@ -82,16 +115,24 @@ def bench_reshape(name, desc, N, Hq, Hkv, D, bs, dtype, kv, iters, ours, ref, co
         v = qkvs[i][:, Hq + Hkv:]
         mod.reshape_and_cache(k, v, kcs[i], vcs[i], slots, kv)
 
+    views = [(q[:, Hq:Hq + Hkv], q[:, Hq + Hkv:]) for q in qkvs]   # made once: view construction is not the op
+
+    def call(mod, i):  # noqa: F811
+        mod.reshape_and_cache(views[i][0], views[i][1], kcs[i], vcs[i], slots, kv)
+
     ms = timeit(lambda i: call(ours, i), iters, nbuf)
+    gms = timeit_graph(lambda i: call(ours, i), nbuf)
     mine = (kcs[0].clone(), vcs[0].clone())
-    ref_ms, exact = None, None
+    ref_ms, exact, rgms = None, None, None
     if ref is not None:
         kcs[0].zero_(); vcs[0].zero_()
         ref_ms = timeit(lambda i: call(ref.cache_ops, i), iters, nbuf)
+        rgms = timeit_graph(lambda i: call(ref.cache_ops, i), nbuf)
         exact = bool(torch.equal(mine[0].view(torch.uint8), kcs[0].view(torch.uint8)) and
                      torch.equal(mine[1].view(torch.uint8), vcs[0].view(torch.uint8)))
-    emit(name, desc, per_call, ms, ref_ms, exact,
-         note=f"{nbuf} buffer sets rotated; K/V are strided views of a [N, Hq+2Hkv, D] qkv buffer")
+    emit(name, desc, per_call, ms, ref_ms, exact, graph_ms=gms, ref_graph_ms=rgms,
+         note=f"{nbuf} buffer sets rotated; K/V are strided views of a [N, Hq+2Hkv, D] qkv buffer; ms = eager calls "
+              f"(CPU launch rate included), graph_replay_ms = the same calls replayed from a CUDA graph")
 
 
 def bench_copy_blocks(iters, ours, ref):
@@ -133,6 +174,7 @@ def bench_swap(iters, ours, ref):
         for kind, a, b, bound in (("d2d", src, dst, "hbm"), ("d2h", src, host, "pcie"), ("h2d", host, dst, "pcie")):
             nbytes = n * bb * (2 if kind == "d2d" else 1)
             it = iters if kind == "d2d" else max(5, iters // 5)
+            b.zero_()
             ms = timeit(lambda i: ours.swap_blocks(a, b, mapping), it, 1)
             mine = b.clone() if kind != "d2h" else b.clone()
             ref_ms, exact = None, None

@@ -71,6 +71,12 @@ SIGNATURES = {
     "b200_swap_blocks": (c_int32, [c_void_p, c_void_p, c_int64, POINTER(c_int64), c_int32, c_int32,
                                    c_int32, c_int32, c_void_p]),
     "b200_convert_fp8_e5m2": (c_int32, [c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p]),
+    "b200_rotary_embedding": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32,
+                                        c_int32, c_int32, c_int64, c_int64, c_int32, c_int32, c_void_p]),
+    "b200_rotary_embedding_reshape_and_cache": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
+                                                          c_int32, c_int32, c_int32, c_int32, c_int64, c_int64,
+                                                          c_int64, c_int32, c_void_p, c_void_p, c_void_p, c_int32,
+                                                          c_int32, c_int64, c_int32, c_int32, c_void_p]),
     "b200_get_device_attribute": (c_int32, [c_int32, c_int32]),
     "b200_get_max_shared_memory_per_block_device_attribute": (c_int32, [c_int32]),
     "b200_kv_ipc_export": (c_int32, [c_void_p, POINTER(c_ubyte), POINTER(c_int64),

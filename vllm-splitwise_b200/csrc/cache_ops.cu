@@ -6,6 +6,7 @@
 // All four are HBM-bound byte movers: the design rules are coalesced 16-byte accesses,
 // tables carried as kernel parameters (no H2D copy, no sync) and grids sized from the work.
 #include <algorithm>
+#include <stdlib.h>
 #include <atomic>
 #include <cstring>
 #include <mutex>
@@ -47,11 +48,32 @@ int num_sms(int device) {
 // ------------------------------------------------------------------------------------------
 // reshape_and_cache
 // ------------------------------------------------------------------------------------------
-// Token-major kernel: one CTA per token.  K: every (head, d/x chunk) is x contiguous source
-// elements and x contiguous destination elements (16 bytes in the cache), so it moves as one
-// vector.  V: element (h, d) lands at [blk, h, d, off] -- a scatter with stride block_size; the
-// tile kernel below handles the prefill case where consecutive tokens fill consecutive offsets.
-template <typename T, typename CT, bool FP8, int X>
+// N source elements starting at p: 16-byte vector loads when the host proved alignment (VEC), else scalar.
+template <typename T, int N, bool VEC>
+__device__ __forceinline__ void load_elems(const T* __restrict__ p, T* out /* 16-byte aligned */) {
+  if constexpr (VEC) {
+    constexpr int PER = 16 / (int)sizeof(T);
+    static_assert(N % PER == 0, "whole vectors");
+#pragma unroll
+    for (int i = 0; i < N / PER; ++i)
+      *reinterpret_cast<uint4*>(out + i * PER) = ld_nc_v4(reinterpret_cast<const uint4*>(p) + i);
+  } else {
+#pragma unroll
+    for (int i = 0; i < N; ++i) out[i] = p[i];
+  }
+}
+
+template <typename T, typename CT, bool FP8>
+__device__ __forceinline__ CT cache_cvt(T v) {
+  if constexpr (FP8) return to_e5m2<T>(v);
+  else return v;
+}
+
+// Token-major kernel (decode-sized calls): one CTA per token.  K: every (head, d/x chunk) is x contiguous
+// source elements and x contiguous destination elements (16 bytes in the cache), so it moves as one
+// vector.  V: element (h, d) lands at [blk, h, d, off] -- a scatter with stride block_size that one token
+// cannot avoid; the source side is read in 16-byte vectors.
+template <typename T, typename CT, bool FP8, int X, bool VEC>
 __global__ void __launch_bounds__(256) reshape_and_cache_token_kernel(
     const T* __restrict__ key, const T* __restrict__ value, CT* __restrict__ key_cache,
     CT* __restrict__ value_cache, const int64_t* __restrict__ slot_mapping, int64_t key_stride,
@@ -70,91 +92,146 @@ __global__ void __launch_bounds__(256) reshape_and_cache_token_kernel(
   CT* vdst = value_cache + blk * (int64_t)num_heads * head_size * block_size;
 
   for (int v = threadIdx.x; v < n_vec; v += blockDim.x) {
-    const int h = v / chunks, c = v - h * chunks;
-    const T* s = ksrc + h * head_size + c * X;
-    CT* d = kdst + ((int64_t)(h * chunks + c) * block_size + off) * X;
+    // (h * chunks + c) * X == v * X: heads are dense in the source row and in the cache block
+    alignas(16) T src[X];
+    load_elems<T, X, VEC>(ksrc + (int64_t)v * X, src);
     alignas(16) CT tmp[X];
 #pragma unroll
-    for (int e = 0; e < X; ++e) {
-      if constexpr (FP8) tmp[e] = to_e5m2<T>(s[e]);
-      else tmp[e] = s[e];
-    }
-    *reinterpret_cast<uint4*>(d) = *reinterpret_cast<const uint4*>(tmp);
+    for (int e = 0; e < X; ++e) tmp[e] = cache_cvt<T, CT, FP8>(src[e]);
+    *reinterpret_cast<uint4*>(kdst + ((int64_t)v * block_size + off) * X) = *reinterpret_cast<const uint4*>(tmp);
   }
+  constexpr int PER = 16 / (int)sizeof(T);
   const int n = num_heads * head_size;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
-    CT o;
-    if constexpr (FP8) o = to_e5m2<T>(vsrc[i]);
-    else o = vsrc[i];
-    vdst[(int64_t)i * block_size + off] = o;
+  for (int i0 = threadIdx.x * PER; i0 < n; i0 += blockDim.x * PER) {
+    alignas(16) T src[PER];
+    load_elems<T, PER, VEC>(vsrc + i0, src);
+#pragma unroll
+    for (int e = 0; e < PER; ++e) vdst[(int64_t)(i0 + e) * block_size + off] = cache_cvt<T, CT, FP8>(src[e]);
   }
 }
 
-// Tile kernel (prefill): one CTA per (group of TOK consecutive tokens, head).  K moves as one
-// 16-byte vector per (token, d/x chunk).  V is read coalesced along d, transposed through shared
-// memory and written token-fastest, so when consecutive tokens occupy consecutive slots (the
-// normal prefill layout) every row d of the [D, block_size] tile receives one contiguous run
-// instead of `n` isolated 1-2 byte stores block_size elements apart (the reference's pattern,
-// cache_kernels.cu:188-191,204).  Slots are looked up per token, so any mapping is correct.
-template <typename T, typename CT, bool FP8, int X, int TOK>
+// Tile kernel (prefill-sized calls): one CTA per (16 consecutive tokens, head).
+// K needs no staging: thread (chunk c, token t), token-fastest, reads its x source elements (16-64 bytes of
+// one row; the lanes of a warp cover whole 32-byte sectors between them) and writes one 16-byte cache vector;
+// consecutive slots give 256 contiguous bytes per chunk.  Every thread looks its own slot up, so the K path
+// has no barrier and all of its global loads are in flight from the first instruction.
+// V is the transposing side: the [16, D] source tile is read with 16-byte vectors into shared memory (rows
+// padded by 16 bytes); cache row d of a block holds that block's tokens contiguously, so when a group of
+// G = min(block_size, 16) tile tokens occupies an aligned run of G slots of one block (the normal prefill
+// layout) each thread gathers its row's G values from the shared tile and stores them as 8-byte words --
+// a warp writes 32 adjacent rows, i.e. one contiguous span -- instead of the reference's isolated 1-2 byte
+// stores block_size elements apart (cache_kernels.cu:188-191,204).  Any other mapping (padding, shuffled or
+// unaligned slots) takes the element-wise path of the same kernel.
+constexpr int kTileTok = 16;
+
+template <typename T, typename CT, bool FP8, int X, bool VEC>
 __global__ void __launch_bounds__(256) reshape_and_cache_tile_kernel(
     const T* __restrict__ key, const T* __restrict__ value, CT* __restrict__ key_cache,
     CT* __restrict__ value_cache, const int64_t* __restrict__ slot_mapping, int64_t key_stride,
     int64_t value_stride, int num_tokens, int num_heads, int head_size, int block_size,
     int64_t num_blocks) {
+  constexpr int TOK = kTileTok;
+  constexpr int PER = 16 / (int)sizeof(T);
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  CT* vt = reinterpret_cast<CT*>(smem_raw);  // [head_size][TOK + PAD]
-  constexpr int PAD = 16 / sizeof(CT);
-  constexpr int LD = TOK + PAD;
+  const int pitch = head_size + PER;  // elements; rows stay 16-byte aligned
+  T* vt = reinterpret_cast<T*>(smem_raw);
   __shared__ int64_t s_base[TOK];  // element offset of (blk, h, 0, 0) or -1 = skip
   __shared__ int s_off[TOK];
+  __shared__ int s_fast;
 
   const int t0 = blockIdx.x * TOK;
   const int h = blockIdx.y;
   const int nt = min(TOK, num_tokens - t0);
-  if (threadIdx.x < TOK) {
+  const int G = min(block_size, TOK);
+  const int64_t head_elems = (int64_t)head_size * block_size;
+
+  // ---- V source tile -> shared memory (issued first: the longest dependency chain) ----
+  const T* vsrc = value + (int64_t)t0 * value_stride + h * head_size;
+  if constexpr (VEC) {
+    const int vpr = head_size / PER;  // 16-byte vectors per row
+    for (int v = threadIdx.x; v < nt * vpr; v += blockDim.x) {
+      const int t = v / vpr, c = v - t * vpr;
+      *reinterpret_cast<uint4*>(vt + t * pitch + c * PER) =
+          ld_nc_v4(reinterpret_cast<const uint4*>(vsrc + (int64_t)t * value_stride) + c);
+    }
+  } else {
+    for (int i = threadIdx.x; i < nt * head_size; i += blockDim.x) {
+      const int t = i / head_size, d = i - t * head_size;
+      vt[t * pitch + d] = vsrc[(int64_t)t * value_stride + d];
+    }
+  }
+
+  // ---- slots of the tile (first warp) ----
+  if (threadIdx.x < 32) {
+    const int t = threadIdx.x;
     int64_t base = -1;
     int off = 0;
-    if (threadIdx.x < nt) {
-      const int64_t slot = slot_mapping[t0 + threadIdx.x];
+    if (t < nt) {
+      const int64_t slot = slot_mapping[t0 + t];
       if (slot >= 0) {
         const int64_t blk = slot / block_size;
         off = static_cast<int>(slot - blk * block_size);
-        if (blk < num_blocks) base = (blk * num_heads + h) * (int64_t)head_size * block_size;
+        if (blk < num_blocks) base = (blk * num_heads + h) * head_elems;
       }
     }
-    s_base[threadIdx.x] = base;
-    s_off[threadIdx.x] = off;
+    if (t < TOK) {
+      s_base[t] = base;
+      s_off[t] = off;
+    }
+    // group leader = first token of this token's aligned group of G
+    const int lead = t - (t % G);
+    const int64_t lbase = __shfl_sync(0xffffffffu, base, lead & 31);
+    const int loff = __shfl_sync(0xffffffffu, off, lead & 31);
+    const bool ok = t >= TOK || (nt == TOK && base >= 0 && base == lbase && off == loff + (t - lead) && (loff % G) == 0);
+    const bool all_ok = __all_sync(0xffffffffu, ok);
+    if (t == 0) s_fast = VEC && all_ok;
   }
-  __syncthreads();
-  const int chunks = head_size / X;
 
+  // ---- K: global -> registers -> one 16-byte cache vector per (token, chunk), token-fastest ----
+  const int chunks = head_size / X;
+  const T* ksrc = key + (int64_t)t0 * key_stride + h * head_size;
   for (int v = threadIdx.x; v < nt * chunks; v += blockDim.x) {
-    const int c = v / nt, t = v - c * nt;  // t fastest: neighbouring threads hit neighbouring slots
-    if (s_base[t] < 0) continue;
-    const T* s = key + (int64_t)(t0 + t) * key_stride + h * head_size + c * X;
+    const int c = v / nt, t = v - c * nt;
+    const int64_t slot = slot_mapping[t0 + t];
+    alignas(16) T src[X];
+    load_elems<T, X, VEC>(ksrc + (int64_t)t * key_stride + c * X, src);
+    if (slot < 0) continue;
+    const int64_t blk = slot / block_size;
+    if (blk >= num_blocks) continue;
+    const int off = static_cast<int>(slot - blk * block_size);
     alignas(16) CT tmp[X];
 #pragma unroll
-    for (int e = 0; e < X; ++e) {
-      if constexpr (FP8) tmp[e] = to_e5m2<T>(s[e]);
-      else tmp[e] = s[e];
-    }
-    *reinterpret_cast<uint4*>(key_cache + s_base[t] + ((int64_t)c * block_size + s_off[t]) * X) =
+    for (int e = 0; e < X; ++e) tmp[e] = cache_cvt<T, CT, FP8>(src[e]);
+    *reinterpret_cast<uint4*>(key_cache + (blk * num_heads + h) * head_elems + ((int64_t)c * block_size + off) * X) =
         *reinterpret_cast<const uint4*>(tmp);
   }
-  for (int i = threadIdx.x; i < nt * head_size; i += blockDim.x) {
-    const int t = i / head_size, d = i - t * head_size;
-    const T sv = value[(int64_t)(t0 + t) * value_stride + h * head_size + d];
-    CT o;
-    if constexpr (FP8) o = to_e5m2<T>(sv);
-    else o = sv;
-    vt[d * LD + t] = o;
-  }
   __syncthreads();
-  for (int i = threadIdx.x; i < nt * head_size; i += blockDim.x) {
-    const int d = i / nt, t = i - d * nt;
-    if (s_base[t] < 0) continue;
-    value_cache[s_base[t] + (int64_t)d * block_size + s_off[t]] = vt[d * LD + t];
+
+  // ---- V ----
+  if (s_fast) {
+    const int ngroups = TOK / G;
+    constexpr int WPE = 8 / (int)sizeof(CT);  // cache elements per 8-byte word
+    for (int i = threadIdx.x; i < head_size * ngroups; i += blockDim.x) {
+      const int g = i / head_size, d = i - g * head_size;
+      const int tl = g * G;
+      CT* row = value_cache + s_base[tl] + (int64_t)d * block_size + s_off[tl];
+      const T* col = vt + tl * pitch + d;
+#pragma unroll
+      for (int w = 0; w < TOK / WPE; ++w) {
+        if (w * WPE < G) {
+          alignas(8) CT tmp[WPE];
+#pragma unroll
+          for (int e = 0; e < WPE; ++e) tmp[e] = cache_cvt<T, CT, FP8>(col[(w * WPE + e) * pitch]);
+          *reinterpret_cast<uint2*>(row + w * WPE) = *reinterpret_cast<const uint2*>(tmp);
+        }
+      }
+    }
+  } else {
+    for (int i = threadIdx.x; i < nt * head_size; i += blockDim.x) {
+      const int d = i / nt, t = i - d * nt;
+      if (s_base[t] < 0) continue;
+      value_cache[s_base[t] + (int64_t)d * block_size + s_off[t]] = cache_cvt<T, CT, FP8>(vt[t * pitch + d]);
+    }
   }
 }
 
@@ -164,22 +241,33 @@ static int launch_reshape_and_cache(const void* key, const void* value, void* ke
                                     int num_heads, int head_size, int block_size, int64_t key_stride,
                                     int64_t value_stride, int64_t num_blocks, cudaStream_t stream) {
   constexpr int X = 16 / sizeof(CT);
+  constexpr int PER = 16 / (int)sizeof(T);
   if (head_size % X != 0) return B200_ERR_HEAD_SIZE;
-  constexpr int TOK = 16;
+  // 16-byte vector path: every source row and the caches are 16-byte aligned and rows are whole vectors
+  const bool vec = (reinterpret_cast<uintptr_t>(key) % 16 == 0) && (reinterpret_cast<uintptr_t>(value) % 16 == 0) &&
+                   ((key_stride * (int64_t)sizeof(T)) % 16 == 0) && ((value_stride * (int64_t)sizeof(T)) % 16 == 0) &&
+                   (head_size % PER == 0) && (reinterpret_cast<uintptr_t>(value_cache) % 16 == 0) && (block_size % 8 == 0);
+#define B200_RC_LAUNCH(KERNEL, GRID, THREADS, SMEM, ...)                                                  \
+  do {                                                                                                    \
+    if (vec) KERNEL<T, CT, FP8, X, true><<<GRID, THREADS, SMEM, stream>>>(__VA_ARGS__);                    \
+    else KERNEL<T, CT, FP8, X, false><<<GRID, THREADS, SMEM, stream>>>(__VA_ARGS__);                       \
+  } while (0)
   // Prefill-sized calls take the tile kernel; decode-sized calls (one token per sequence, every
   // token in a different block) take the token kernel.
-  if (num_tokens >= 4 * TOK) {
-    dim3 grid((num_tokens + TOK - 1) / TOK, num_heads);
-    size_t smem = (size_t)head_size * (TOK + 16 / sizeof(CT)) * sizeof(CT);
-    reshape_and_cache_tile_kernel<T, CT, FP8, X, TOK><<<grid, 256, smem, stream>>>(
-        (const T*)key, (const T*)value, (CT*)key_cache, (CT*)value_cache, slot_mapping, key_stride,
-        value_stride, num_tokens, num_heads, head_size, block_size, num_blocks);
+  if (num_tokens >= 4 * kTileTok) {
+    dim3 grid((num_tokens + kTileTok - 1) / kTileTok, num_heads);
+    const size_t smem = (size_t)kTileTok * (head_size + PER) * sizeof(T);
+    B200_RC_LAUNCH(reshape_and_cache_tile_kernel, grid, 256, smem, (const T*)key, (const T*)value, (CT*)key_cache,
+                   (CT*)value_cache, slot_mapping, key_stride, value_stride, num_tokens, num_heads, head_size,
+                   block_size, num_blocks);
   } else {
-    int threads = std::min(256, std::max(32, (num_heads * head_size + 31) / 32 * 32));
-    reshape_and_cache_token_kernel<T, CT, FP8, X><<<num_tokens, threads, 0, stream>>>(
-        (const T*)key, (const T*)value, (CT*)key_cache, (CT*)value_cache, slot_mapping, key_stride,
-        value_stride, num_heads, head_size, block_size, num_blocks);
+    const int work = num_heads * head_size / PER;  // 16-byte source vectors per token
+    const int threads = std::min(256, std::max(32, (work + 31) / 32 * 32));
+    B200_RC_LAUNCH(reshape_and_cache_token_kernel, num_tokens, threads, 0, (const T*)key, (const T*)value,
+                   (CT*)key_cache, (CT*)value_cache, slot_mapping, key_stride, value_stride, num_heads, head_size,
+                   block_size, num_blocks);
   }
+#undef B200_RC_LAUNCH
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -257,15 +345,58 @@ static int launch_copy(const int64_t* src_bases, const int64_t* dst_bases, int n
 // ------------------------------------------------------------------------------------------
 // convert_fp8_e5m2
 // ------------------------------------------------------------------------------------------
-template <typename T>
+// 16 elements per thread per step: 16-byte vectors on both sides when the host proved alignment; the
+// tail (numel % 16) and unaligned tensors take the scalar loop of the same kernel.
+template <typename T, bool VEC>
 __global__ void __launch_bounds__(256) to_fp8_kernel(const T* __restrict__ src, uint8_t* __restrict__ dst, int64_t n) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = to_e5m2<T>(src[i]);
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t done = 0;
+  if constexpr (VEC) {
+    const int64_t groups = n / 16;
+    for (int64_t g = tid; g < groups; g += stride) {
+      alignas(16) T in[16];
+      load_elems<T, 16, true>(src + g * 16, in);
+      alignas(16) uint8_t out[16];
+#pragma unroll
+      for (int e = 0; e < 16; ++e) out[e] = to_e5m2<T>(in[e]);
+      st_na_v4(dst + g * 16, *reinterpret_cast<const uint4*>(out));
+    }
+    done = groups * 16;
+  }
+  for (int64_t i = done + tid; i < n; i += stride) dst[i] = to_e5m2<T>(src[i]);
 }
-template <typename T>
+template <typename T, bool VEC>
 __global__ void __launch_bounds__(256) from_fp8_kernel(const uint8_t* __restrict__ src, T* __restrict__ dst, int64_t n) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = from_e5m2<T>(src[i]);
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t done = 0;
+  if constexpr (VEC) {
+    constexpr int PER = 16 / (int)sizeof(T);
+    const int64_t groups = n / 16;
+    for (int64_t g = tid; g < groups; g += stride) {
+      const uint4 raw = ld_nc_v4(src + g * 16);
+      const uint8_t* in = reinterpret_cast<const uint8_t*>(&raw);
+      alignas(16) T out[16];
+#pragma unroll
+      for (int e = 0; e < 16; ++e) out[e] = from_e5m2<T>(in[e]);
+#pragma unroll
+      for (int v = 0; v < 16 / PER; ++v) st_na_v4(dst + g * 16 + v * PER, *reinterpret_cast<const uint4*>(out + v * PER));
+    }
+    done = groups * 16;
+  }
+  for (int64_t i = done + tid; i < n; i += stride) dst[i] = from_e5m2<T>(src[i]);
+}
+
+template <typename T>
+static void launch_to_fp8(const void* src, void* dst, int64_t n, int blocks, bool vec, cudaStream_t stream) {
+  if (vec) to_fp8_kernel<T, true><<<blocks, 256, 0, stream>>>((const T*)src, (uint8_t*)dst, n);
+  else to_fp8_kernel<T, false><<<blocks, 256, 0, stream>>>((const T*)src, (uint8_t*)dst, n);
+}
+template <typename T>
+static void launch_from_fp8(const void* src, void* dst, int64_t n, int blocks, bool vec, cudaStream_t stream) {
+  if (vec) from_fp8_kernel<T, true><<<blocks, 256, 0, stream>>>((const uint8_t*)src, (T*)dst, n);
+  else from_fp8_kernel<T, false><<<blocks, 256, 0, stream>>>((const uint8_t*)src, (T*)dst, n);
 }
 
 }  // namespace b200
@@ -360,7 +491,29 @@ B200_API int b200_swap_blocks(const void* src, void* dst, int64_t block_bytes, c
   const cudaMemcpyKind mk = kind == B200_SWAP_D2H ? cudaMemcpyDeviceToHost : cudaMemcpyHostToDevice;
   const char* s = static_cast<const char*>(src);
   char* d = static_cast<char*>(dst);
-  // merge runs where src and dst both advance by one block: one copy per run
+  // runs where src and dst both advance by one block
+  int runs = 0;
+  for (int i = 0; i < num_pairs; ++i)
+    if (i == 0 || block_pairs[2 * i] != block_pairs[2 * (i - 1)] + 1 ||
+        block_pairs[2 * i + 1] != block_pairs[2 * (i - 1) + 1] + 1)
+      ++runs;
+  // Fragmented block lists (the usual case: a swapped sequence's blocks are scattered on both sides) against
+  // PINNED host memory: one gather kernel that reads / writes the host side through its device mapping, so
+  // the PCIe link sees one stream of 16-byte accesses instead of one DMA descriptor per 128 KiB block
+  // (the reference issues one cudaMemcpyAsync per block, cache_kernels.cu:47-58).  Pageable host memory and
+  // lists that merge into a few long runs keep the copy engine.
+  static const bool no_zero_copy = getenv("B200_SWAP_NO_ZERO_COPY") != nullptr;  // A/B knob
+  if (runs > 2 && !no_zero_copy) {
+    const void* host = kind == B200_SWAP_D2H ? (const void*)dst : src;
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, host) == cudaSuccess && attr.type == cudaMemoryTypeHost &&
+        attr.devicePointer != nullptr) {
+      int64_t sp = kind == B200_SWAP_D2H ? reinterpret_cast<int64_t>(src) : reinterpret_cast<int64_t>(attr.devicePointer);
+      int64_t dp = kind == B200_SWAP_D2H ? reinterpret_cast<int64_t>(attr.devicePointer) : reinterpret_cast<int64_t>(dst);
+      return launch_copy(&sp, &dp, 1, block_pairs, num_pairs, block_bytes, stream);
+    }
+    (void)cudaGetLastError();
+  }
   int i = 0;
   while (i < num_pairs) {
     int j = i + 1;
@@ -380,16 +533,18 @@ B200_API int b200_convert_fp8_e5m2(const void* src, void* dst, int64_t numel, in
   if (numel == 0) return B200_OK;
   if (!src || !dst || numel < 0) return B200_ERR_ARG;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  const int blocks = (int)std::min<int64_t>((numel + 255) / 256, (int64_t)num_sms(-1) * 16);
+  const bool vec = (reinterpret_cast<uintptr_t>(src) % 16 == 0) && (reinterpret_cast<uintptr_t>(dst) % 16 == 0);
+  const int64_t work = vec ? (numel + 15) / 16 : numel;
+  const int blocks = (int)std::min<int64_t>((work + 255) / 256, (int64_t)num_sms(-1) * 16);
   if (dst_dtype == B200_U8_E5M2) {
-    if (src_dtype == B200_F32) to_fp8_kernel<float><<<blocks, 256, 0, stream>>>((const float*)src, (uint8_t*)dst, numel);
-    else if (src_dtype == B200_F16) to_fp8_kernel<__half><<<blocks, 256, 0, stream>>>((const __half*)src, (uint8_t*)dst, numel);
-    else if (src_dtype == B200_BF16) to_fp8_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>((const __nv_bfloat16*)src, (uint8_t*)dst, numel);
+    if (src_dtype == B200_F32) launch_to_fp8<float>(src, dst, numel, blocks, vec, stream);
+    else if (src_dtype == B200_F16) launch_to_fp8<__half>(src, dst, numel, blocks, vec, stream);
+    else if (src_dtype == B200_BF16) launch_to_fp8<__nv_bfloat16>(src, dst, numel, blocks, vec, stream);
     else return B200_ERR_DTYPE;
   } else if (src_dtype == B200_U8_E5M2) {
-    if (dst_dtype == B200_F32) from_fp8_kernel<float><<<blocks, 256, 0, stream>>>((const uint8_t*)src, (float*)dst, numel);
-    else if (dst_dtype == B200_F16) from_fp8_kernel<__half><<<blocks, 256, 0, stream>>>((const uint8_t*)src, (__half*)dst, numel);
-    else if (dst_dtype == B200_BF16) from_fp8_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>((const uint8_t*)src, (__nv_bfloat16*)dst, numel);
+    if (dst_dtype == B200_F32) launch_from_fp8<float>(src, dst, numel, blocks, vec, stream);
+    else if (dst_dtype == B200_F16) launch_from_fp8<__half>(src, dst, numel, blocks, vec, stream);
+    else if (dst_dtype == B200_BF16) launch_from_fp8<__nv_bfloat16>(src, dst, numel, blocks, vec, stream);
     else return B200_ERR_DTYPE;
   } else {
     return B200_ERR_DTYPE;
