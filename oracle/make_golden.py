@@ -6,6 +6,8 @@ copying any source into this repository,
     (tests/kernels/test_attention.py:43-111; the module itself cannot be imported: it needs
     xformers and the reference's compiled vllm._C), and
   * coalesce_blocks (vllm/utils.py:403-420),
+  * RotaryEmbedding (+ _rotate_neox / _rotate_gptj) of vllm/model_executor/layers/rotary_embedding.py:31-137,
+    whose _forward is the torch check the reference's own rotary test uses (tests/kernels/test_pos_encoding.py),
 executes them on seeded inputs and stores inputs + the reference's outputs.  The committed
 fixtures are what tests/test_oracle_golden.py checks the oracle against on every CPU run, and
 what the GPU parity tests check the CUDA kernels against on the GPU box (where /root/reference
@@ -30,9 +32,12 @@ OUT = os.path.join(os.path.dirname(HERE), "tests", "golden")
 
 def extract(path: str, names: List[str]) -> dict:
     tree = ast.parse(open(path).read())
-    ns = {"torch": torch, "Optional": Optional, "List": List, "Tuple": Tuple, "Dict": Dict}
+    import math
+    from typing import Any, Union
+    ns = {"torch": torch, "nn": torch.nn, "math": math, "Optional": Optional, "List": List, "Tuple": Tuple,
+          "Dict": Dict, "Any": Any, "Union": Union}
     for node in tree.body:
-        if isinstance(node, ast.FunctionDef) and node.name in names:
+        if isinstance(node, (ast.FunctionDef, ast.ClassDef)) and node.name in names:
             exec(compile(ast.Module([node], []), path, "exec"), ns)
     missing = [n for n in names if n not in ns]
     if missing:
@@ -109,6 +114,47 @@ def make_coalesce(ref) -> None:
     print("coalesce cases:", len(out))
 
 
+# (name, dtype, is_neox, head_size, rotary_dim, num_heads, num_kv_heads, batch, seq_len, max_position, base)
+ROPE_CASES = [
+    ("neox_f16_d128", "float16", True, 128, 128, 8, 2, 2, 9, 512, 10000),
+    ("neox_bf16_d128", "bfloat16", True, 128, 128, 8, 8, 3, 5, 4096, 10000),
+    ("neox_f32_d64", "float32", True, 64, 64, 4, 4, 1, 11, 256, 10000),
+    ("gptj_f16_d256_rot64", "float16", False, 256, 64, 4, 4, 2, 7, 512, 10000),
+    ("gptj_bf16_d80_rot32", "bfloat16", False, 80, 32, 6, 3, 2, 6, 300, 1000000),
+    ("neox_f16_d96_rot48", "float16", True, 96, 48, 5, 5, 1, 13, 128, 10000),
+]
+
+
+def make_rope(ref) -> None:
+    store, meta = {}, []
+    # _forward moves the cache with .to(positions.get_device()); on CPU tensors get_device() is -1
+    orig_get_device = torch.Tensor.get_device
+    torch.Tensor.get_device = lambda self: "cpu"
+    try:
+        for ci, (name, dt, neox, d, rot, hq, hkv, b, sl, maxpos, base) in enumerate(ROPE_CASES):
+            torch.manual_seed(100 + ci)
+            dtype = DT[dt]
+            torch.set_default_dtype(dtype)         # as tests/kernels/test_pos_encoding.py does
+            rope = ref["RotaryEmbedding"](d, rot, maxpos, base, neox)
+            torch.set_default_dtype(torch.float32)
+            positions = torch.randint(0, maxpos, (b, sl))
+            q = torch.randn(b, sl, hq * d, dtype=dtype)
+            k = torch.randn(b, sl, hkv * d, dtype=dtype)
+            oq, ok = rope._forward(positions, q.clone(), k.clone())
+            store[f"{name}.pos"] = positions.numpy()
+            store[f"{name}.q"], store[f"{name}.k"] = raw(q), raw(k)
+            store[f"{name}.oq"], store[f"{name}.ok"] = raw(oq), raw(ok)
+            store[f"{name}.cache"] = raw(rope.cos_sin_cache)
+            meta.append(dict(name=name, dtype=dt, is_neox=neox, head_size=d, rotary_dim=rot, num_heads=hq,
+                             num_kv_heads=hkv, batch=b, seq_len=sl, max_position=maxpos, base=base))
+    finally:
+        torch.Tensor.get_device = orig_get_device
+        torch.set_default_dtype(torch.float32)
+    np.savez_compressed(os.path.join(OUT, "rope_ref.npz"), **store)
+    json.dump(meta, open(os.path.join(OUT, "rope_ref.json"), "w"), indent=1)
+    print("rope cases:", len(meta))
+
+
 def main() -> None:
     if not os.path.isdir(REF):
         sys.exit(f"{REF} not present: golden fixtures can only be regenerated in the build container")
@@ -118,6 +164,8 @@ def main() -> None:
                    ["ref_masked_attention", "ref_single_query_cached_kv_attention"])
     make_attention(attn)
     make_coalesce(extract(os.path.join(REF, "vllm/utils.py"), ["coalesce_blocks"]))
+    make_rope(extract(os.path.join(REF, "vllm/model_executor/layers/rotary_embedding.py"),
+                      ["_rotate_neox", "_rotate_gptj", "RotaryEmbedding"]))
 
 
 if __name__ == "__main__":

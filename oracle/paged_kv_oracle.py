@@ -254,6 +254,57 @@ def reshape_and_cache(key: torch.Tensor, value: torch.Tensor, key_cache: torch.T
         value_cache[blk, :, :, off] = v[i]
 
 
+def compute_cos_sin_cache(rotary_dim: int, max_position: int, base: float, dtype: torch.dtype) -> torch.Tensor:
+    """[max_position, rotary_dim]: cos then sin of position * base^(-2i/rotary_dim)
+    (reference vllm/model_executor/layers/rotary_embedding.py:67-93, cast as in :63-65)."""
+    inv_freq = 1.0 / (base ** (torch.arange(0, rotary_dim, 2, dtype=torch.float) / rotary_dim))
+    t = torch.arange(max_position, dtype=torch.float)
+    freqs = torch.einsum("i,j -> ij", t, inv_freq)
+    return torch.cat((freqs.cos(), freqs.sin()), dim=-1).to(dtype)
+
+
+def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor, head_size: int,
+                     cos_sin_cache: torch.Tensor, is_neox: bool,
+                     cos_sin_cache_offsets: Optional[torch.Tensor] = None) -> None:
+    """In place on query/key [..., heads * head_size], restating the reference kernel
+    (csrc/pos_encoding_kernels.cu:9-95): for pair (x, y) of every head, x' = x*cos - y*sin, y' = y*cos + x*sin,
+    NeoX pairs (i, i + rot_dim/2), GPT-J pairs (2i, 2i+1); the rotation covers the first rot_dim elements of a
+    head.  Each product and sum is a torch op in the tensor dtype -- float arithmetic rounded to the element type
+    per operation, which is what the kernel's scalar_t arithmetic does (and what the reference's own torch
+    check, RotaryEmbedding._forward, rotary_embedding.py:95-137, computes)."""
+    rot_dim = cos_sin_cache.shape[1]
+    embed = rot_dim // 2
+    pos = positions.reshape(-1)
+    if cos_sin_cache_offsets is not None:
+        pos = pos + cos_sin_cache_offsets.reshape(-1)
+    cs = cos_sin_cache[pos]                       # [N, rot_dim]
+    cos, sin = cs[:, None, :embed], cs[:, None, embed:]
+    for t in (query, key):
+        n = t.numel() // t.shape[-1]
+        v = t.reshape(n, -1, head_size)           # a view for the dense / row-strided layouts the ops accept
+        rot = v[..., :rot_dim]
+        if is_neox:
+            x, y = rot[..., :embed].clone(), rot[..., embed:].clone()
+            rot[..., :embed] = x * cos - y * sin
+            rot[..., embed:] = y * cos + x * sin
+        else:
+            x, y = rot[..., 0::2].clone(), rot[..., 1::2].clone()
+            rot[..., 0::2] = x * cos - y * sin
+            rot[..., 1::2] = y * cos + x * sin
+        if v.data_ptr() != t.data_ptr():          # reshape had to copy (non-viewable strides): write back
+            t.copy_(v.reshape(t.shape))
+
+
+def rotary_embedding_reshape_and_cache(positions, query, key, value, head_size, cos_sin_cache, is_neox, key_cache,
+                                       value_cache, slot_mapping, kv_cache_dtype) -> None:
+    """The fused op is DEFINED as the two reference ops in sequence (models/llama.py:156-158 then
+    attention backends -> reshape_and_cache)."""
+    rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox)
+    n = key.numel() // key.shape[-1]
+    reshape_and_cache(key.reshape(n, -1, head_size), value.reshape(n, -1, head_size), key_cache, value_cache,
+                      slot_mapping.reshape(-1), kv_cache_dtype)
+
+
 def copy_blocks(key_caches: List[torch.Tensor], value_caches: List[torch.Tensor],
                 block_mapping: Dict[int, List[int]]) -> None:
     """For every layer: cache[dst] = cache[src] for K and V (csrc/cache_kernels.cu:65-91;

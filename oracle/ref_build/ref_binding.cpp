@@ -3,7 +3,8 @@
 // Minimal pybind11 front for the *unmodified* reference CUDA kernels so that the GPU parity
 // tests and bench.py can run the reference's own paged_attention / cache ops next to ours on
 // identical inputs.  The kernels themselves are compiled straight from
-// /root/reference/csrc/{attention/attention_kernels.cu,cache_kernels.cu,cuda_utils_kernels.cu}
+// /root/reference/csrc/{attention/attention_kernels.cu,cache_kernels.cu,cuda_utils_kernels.cu,
+// pos_encoding_kernels.cu}
 // by oracle/build_ref.sh; nothing from the reference is copied into this repository.  The
 // prototypes below restate csrc/ops.h:5-34, csrc/cache.h:8-29 and csrc/cuda_utils.h.
 #include <torch/extension.h>
@@ -34,6 +35,13 @@ void reshape_and_cache(torch::Tensor& key, torch::Tensor& value, torch::Tensor& 
                        const std::string& kv_cache_dtype);
 void convert_fp8_e5m2(torch::Tensor& src_cache, torch::Tensor& dst_cache);
 
+// csrc/ops.h:48-63 (compiled from csrc/pos_encoding_kernels.cu)
+void rotary_embedding(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key, int head_size,
+                      torch::Tensor& cos_sin_cache, bool is_neox);
+void batched_rotary_embedding(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key, int head_size,
+                              torch::Tensor& cos_sin_cache, bool is_neox, int rot_dim,
+                              torch::Tensor& cos_sin_cache_offsets);
+
 int get_device_attribute(int attribute, int device_id);
 int get_max_shared_memory_per_block_device_attribute(int device_id);
 
@@ -41,6 +49,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   pybind11::module ops = m.def_submodule("ops");
   ops.def("paged_attention_v1", &paged_attention_v1);
   ops.def("paged_attention_v2", &paged_attention_v2);
+  ops.def("rotary_embedding", &rotary_embedding);
+  ops.def("batched_rotary_embedding", &batched_rotary_embedding);
   pybind11::module cache_ops = m.def_submodule("cache_ops");
   cache_ops.def("swap_blocks", &swap_blocks);
   cache_ops.def("copy_blocks", &copy_blocks);

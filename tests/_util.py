@@ -129,3 +129,16 @@ def oracle_attention(a):
     O.single_query_cached_kv_attention(ref, a["q"], a["hq"] // a["hkv"], kc, vc, a["bt"], a["cl"], a["scale"],
                                        a["alibi"])
     return ref
+
+
+def load_rope_golden():
+    """RotaryEmbedding._forward outputs of the reference (oracle/make_golden.py): list of dicts with CPU tensors
+    pos [B, S], q/k inputs, oq/ok outputs ([B, S, heads*D]) and the reference's cos_sin_cache."""
+    meta = json.load(open(os.path.join(GOLDEN, "rope_ref.json")))
+    z = np.load(os.path.join(GOLDEN, "rope_ref.npz"))
+    out = []
+    for m in meta:
+        dt, n = DT[m["dtype"]], m["name"]
+        out.append(dict(meta=m, pos=torch.from_numpy(z[f"{n}.pos"].copy()),
+                        **{k: _from_raw(z[f"{n}.{k}"], dt) for k in ("q", "k", "oq", "ok", "cache")}))
+    return out

@@ -149,3 +149,45 @@ def test_copy_blocks_python_vs_c():
     pairs = [(s, d) for s in sorted(mapping) for d in mapping[s]]
     c_oracle.copy_blocks(kc, pairs)
     assert torch.equal(bits(kc), bits(ref))
+
+
+# ---------------------------------------------------------------------------------------------
+# rotary embedding: the oracle against the reference's RotaryEmbedding._forward
+# ---------------------------------------------------------------------------------------------
+from _util import load_rope_golden  # noqa: E402
+
+ROPE = load_rope_golden()
+
+
+@pytest.mark.parametrize("case", ROPE, ids=[c["meta"]["name"] for c in ROPE])
+def test_rotary_oracle_matches_reference_forward(case):
+    m = case["meta"]
+    cache = O.compute_cos_sin_cache(m["rotary_dim"], m["max_position"], m["base"], case["q"].dtype)
+    assert torch.equal(bits(cache), bits(case["cache"]))
+    q, k = case["q"].clone(), case["k"].clone()
+    O.rotary_embedding(case["pos"], q, k, m["head_size"], case["cache"], m["is_neox"])
+    # per-operation rounding in the element type on both sides -> bit-identical
+    assert torch.equal(bits(q), bits(case["oq"])) and torch.equal(bits(k), bits(case["ok"]))
+
+
+def test_rotary_oracle_strided_views_and_offsets():
+    """In place on the strided q/k views of a fused qkv buffer (how llama.py:155-158 holds them); offsets shift
+    the position (batched_rotary_embedding, pos_encoding_kernels.cu:97-123)."""
+    torch.manual_seed(0)
+    n, hq, hkv, d = 6, 4, 2, 64
+    cache = O.compute_cos_sin_cache(d, 64, 10000, torch.float16)
+    qkv = torch.randn(n, (hq + 2 * hkv) * d).half()
+    dense_q, dense_k = qkv[:, :hq * d].clone(), qkv[:, hq * d:(hq + hkv) * d].clone()
+    v_before = qkv[:, (hq + hkv) * d:].clone()
+    pos = torch.tensor([0, 5, 17, 3, 9, 30])
+    O.rotary_embedding(pos, qkv[:, :hq * d], qkv[:, hq * d:(hq + hkv) * d], d, cache, True)
+    O.rotary_embedding(pos, dense_q, dense_k, d, cache, True)
+    assert torch.equal(qkv[:, :hq * d], dense_q) and torch.equal(qkv[:, hq * d:(hq + hkv) * d], dense_k)
+    assert torch.equal(qkv[:, (hq + hkv) * d:], v_before)
+    a, b = dense_q.clone(), dense_k.clone()
+    q2, k2 = torch.randn(n, hq * d).half(), torch.randn(n, hkv * d).half()
+    q3, k3 = q2.clone(), k2.clone()
+    off = torch.tensor([1, 0, 2, 20, 0, 7])
+    O.rotary_embedding(pos, q2, k2, d, cache, False, off)
+    O.rotary_embedding(pos + off, q3, k3, d, cache, False)
+    assert torch.equal(q2, q3) and torch.equal(k2, k3)

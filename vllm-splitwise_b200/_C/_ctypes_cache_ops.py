@@ -109,3 +109,42 @@ def convert_fp8_e5m2(src_cache: torch.Tensor, dst_cache: torch.Tensor) -> None:
             dtype_code(src_cache, "src_cache"), dtype_code(dst_cache, "dst_cache"),
             stream_ptr(src_cache.device))
     _lib.check(st, "convert_fp8_e5m2")
+
+
+def rotary_embedding_reshape_and_cache(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
+                                       value: torch.Tensor, head_size: int, cos_sin_cache: torch.Tensor,
+                                       is_neox: bool, key_cache: torch.Tensor, value_cache: torch.Tensor,
+                                       slot_mapping: torch.Tensor, kv_cache_dtype: str) -> None:
+    """ops.rotary_embedding(positions, query, key, ...) followed by reshape_and_cache(key, value, ...) in one
+    call; query/key/value are [..., heads * head_size]."""
+    from ._ctypes_ops import _rotary_shape
+    n, hq, hkv, rot, qs, ks = _rotary_shape(positions, query, key, head_size, cos_sin_cache)
+    for name, t in (("value", value), ("key_cache", key_cache), ("value_cache", value_cache),
+                    ("slot_mapping", slot_mapping)):
+        require_cuda(t, name)
+    if (value.dim() != key.dim() or value.size(-1) != key.size(-1) or value.stride(-1) != 1
+            or value.dtype != key.dtype or value.numel() != key.numel()):
+        raise RuntimeError("value must have the shape and dtype of key")
+    if slot_mapping.dtype != torch.int64 or not slot_mapping.is_contiguous() or slot_mapping.numel() != n:
+        raise RuntimeError("slot_mapping must be a contiguous int64 tensor with one entry per token")
+    if not (key_cache.is_contiguous() and value_cache.is_contiguous()):
+        raise RuntimeError("key_cache/value_cache must be contiguous")
+    if key_cache.dim() != 5 or key_cache.size(1) != hkv:
+        raise RuntimeError("key_cache must be [blocks, kv_heads, D/x, bs, x]")
+    if kv_cache_dtype == "auto":
+        cache_code = dtype_code(key, "key")
+        if key_cache.dtype != key.dtype:
+            raise RuntimeError("Unsupported data type: cache dtype must equal key dtype for 'auto'")
+    elif kv_cache_dtype == "fp8_e5m2":
+        cache_code = _lib.U8_E5M2
+        if key_cache.dtype != torch.uint8:
+            raise RuntimeError("Unsupported data type: fp8_e5m2 cache must be uint8")
+    else:
+        raise RuntimeError(f"Unsupported data type of kv cache: {kv_cache_dtype}")
+    with device_ctx(query.device):
+        st = _lib.load().b200_rotary_embedding_reshape_and_cache(
+            positions.data_ptr(), query.data_ptr(), key.data_ptr(), value.data_ptr(), cos_sin_cache.data_ptr(), n, hq,
+            hkv, head_size, rot, qs, ks, value.stride(-2), int(bool(is_neox)), key_cache.data_ptr(),
+            value_cache.data_ptr(), slot_mapping.data_ptr(), key_cache.size(3), key_cache.size(4), key_cache.size(0),
+            dtype_code(key, "key"), cache_code, stream_ptr(query.device))
+    _lib.check(st, "rotary_embedding_reshape_and_cache")

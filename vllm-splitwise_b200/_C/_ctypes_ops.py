@@ -122,3 +122,52 @@ def paged_attention_v2(out: torch.Tensor, exp_sums: torch.Tensor, max_logits: to
     a.max_num_partitions = exp_sums.size(2)
     st = _lib.load().b200_paged_attention_v2(ctypes.byref(a), stream_ptr(query.device))
     _lib.check(st, "paged_attention_v2", _detail(a, st))
+
+
+def _rotary_shape(positions, query, key, head_size, cos_sin_cache):
+    for name, t in (("positions", positions), ("query", query), ("key", key), ("cos_sin_cache", cos_sin_cache)):
+        require_cuda(t, name)
+    if positions.dtype != torch.int64 or not positions.is_contiguous():
+        raise RuntimeError("positions must be a contiguous int64 tensor")
+    if (query.dim() < 2 or key.dim() < 2 or head_size <= 0 or query.size(-1) % head_size or key.size(-1) % head_size
+            or query.stride(-1) != 1 or key.stride(-1) != 1):
+        raise RuntimeError("query/key must be [..., num_heads * head_size] with a dense last dim")
+    if key.dtype != query.dtype or cos_sin_cache.dtype != query.dtype:
+        raise RuntimeError("query, key and cos_sin_cache must have the same dtype")
+    if cos_sin_cache.dim() != 2 or not cos_sin_cache.is_contiguous():
+        raise RuntimeError("cos_sin_cache must be [max_position, rot_dim]")
+    num_tokens = query.numel() // query.size(-1)
+    if positions.numel() != num_tokens or key.numel() // key.size(-1) != num_tokens:
+        raise RuntimeError("positions, query and key must describe the same number of tokens")
+    return (num_tokens, query.size(-1) // head_size, key.size(-1) // head_size, cos_sin_cache.size(1),
+            query.stride(-2), key.stride(-2))
+
+
+def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor, head_size: int,
+                     cos_sin_cache: torch.Tensor, is_neox: bool) -> None:
+    """reference csrc/ops.h:48-54"""
+    n, hq, hkv, rot, qs, ks = _rotary_shape(positions, query, key, head_size, cos_sin_cache)
+    with device_ctx(query.device):
+        st = _lib.load().b200_rotary_embedding(positions.data_ptr(), query.data_ptr(), key.data_ptr(),
+                                               cos_sin_cache.data_ptr(), None, n, hq, hkv, head_size, rot, qs, ks,
+                                               int(bool(is_neox)), dtype_code(query, "query"), stream_ptr(query.device))
+    _lib.check(st, "rotary_embedding")
+
+
+def batched_rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor, head_size: int,
+                             cos_sin_cache: torch.Tensor, is_neox: bool, rot_dim: int,
+                             cos_sin_cache_offsets: torch.Tensor) -> None:
+    """reference csrc/ops.h:56-63"""
+    n, hq, hkv, rot, qs, ks = _rotary_shape(positions, query, key, head_size, cos_sin_cache)
+    require_cuda(cos_sin_cache_offsets, "cos_sin_cache_offsets")
+    if (cos_sin_cache_offsets.dtype != torch.int64 or not cos_sin_cache_offsets.is_contiguous()
+            or cos_sin_cache_offsets.numel() != n):
+        raise RuntimeError("cos_sin_cache_offsets must be a contiguous int64 tensor with one entry per token")
+    if rot_dim != rot:
+        raise RuntimeError("rot_dim must equal cos_sin_cache.size(1)")
+    with device_ctx(query.device):
+        st = _lib.load().b200_rotary_embedding(positions.data_ptr(), query.data_ptr(), key.data_ptr(),
+                                               cos_sin_cache.data_ptr(), cos_sin_cache_offsets.data_ptr(), n, hq, hkv,
+                                               head_size, rot, qs, ks, int(bool(is_neox)), dtype_code(query, "query"),
+                                               stream_ptr(query.device))
+    _lib.check(st, "batched_rotary_embedding")

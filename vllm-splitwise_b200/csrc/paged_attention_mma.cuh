@@ -196,6 +196,9 @@ struct MmaImpl {
       CT* vt = reinterpret_cast<CT*>(vs);
       for (int i = lane; i < D * BS; i += 32)
         if ((i % BS) >= rem) vt[i] = CT(0);
+      // These are generic-proxy writes into a stage the producer will refill through the async proxy (TMA):
+      // order them before that refill (the empty-barrier arrive that follows releases the stage).
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncwarp();
     }
     const uint32_t ks_u = smem_u32(ks), vs_u = smem_u32(vs);

@@ -239,6 +239,94 @@ void convert_fp8_e5m2(torch::Tensor& src_cache, torch::Tensor& dst_cache) {
   check_status(st, "convert_fp8_e5m2");
 }
 
+// ---- rotary embedding (reference csrc/ops.h:48-63) and its fusion with the cache write ----
+struct RotaryShape {
+  int64_t num_tokens, query_stride, key_stride;
+  int num_heads, num_kv_heads, rot_dim;
+};
+
+RotaryShape rotary_shape(const torch::Tensor& positions, const torch::Tensor& query, const torch::Tensor& key,
+                         int head_size, const torch::Tensor& cos_sin_cache) {
+  require_cuda(positions, "positions"); require_cuda(query, "query"); require_cuda(key, "key");
+  require_cuda(cos_sin_cache, "cos_sin_cache");
+  TORCH_CHECK(positions.scalar_type() == at::ScalarType::Long && positions.is_contiguous(),
+              "positions must be a contiguous int64 tensor");
+  TORCH_CHECK(query.dim() >= 2 && key.dim() >= 2 && head_size > 0 && query.size(-1) % head_size == 0 &&
+                  key.size(-1) % head_size == 0 && query.stride(-1) == 1 && key.stride(-1) == 1,
+              "query/key must be [..., num_heads * head_size] with a dense last dim");
+  TORCH_CHECK(key.scalar_type() == query.scalar_type() && cos_sin_cache.scalar_type() == query.scalar_type(),
+              "query, key and cos_sin_cache must have the same dtype");
+  TORCH_CHECK(cos_sin_cache.dim() == 2 && cos_sin_cache.is_contiguous(), "cos_sin_cache must be [max_position, rot_dim]");
+  RotaryShape r;
+  r.num_tokens = query.numel() / query.size(-1);  // reference pos_encoding_kernels.cu:133
+  r.num_heads = (int)(query.size(-1) / head_size);
+  r.num_kv_heads = (int)(key.size(-1) / head_size);
+  r.rot_dim = (int)cos_sin_cache.size(1);
+  r.query_stride = query.stride(-2);
+  r.key_stride = key.stride(-2);
+  TORCH_CHECK(positions.numel() == r.num_tokens && key.numel() / key.size(-1) == r.num_tokens,
+              "positions, query and key must describe the same number of tokens");
+  return r;
+}
+
+void rotary_embedding(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key, int head_size,
+                      torch::Tensor& cos_sin_cache, bool is_neox) {
+  const RotaryShape r = rotary_shape(positions, query, key, head_size, cos_sin_cache);
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  const int st = b200_rotary_embedding(positions.data_ptr<int64_t>(), query.data_ptr(), key.data_ptr(),
+                                       cos_sin_cache.data_ptr(), nullptr, r.num_tokens, r.num_heads, r.num_kv_heads,
+                                       head_size, r.rot_dim, r.query_stride, r.key_stride, is_neox ? 1 : 0,
+                                       dtype_code(query, "query"), at::cuda::getCurrentCUDAStream().stream());
+  check_status(st, "rotary_embedding");
+}
+
+void batched_rotary_embedding(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key, int head_size,
+                              torch::Tensor& cos_sin_cache, bool is_neox, int rot_dim,
+                              torch::Tensor& cos_sin_cache_offsets) {
+  const RotaryShape r = rotary_shape(positions, query, key, head_size, cos_sin_cache);
+  require_cuda(cos_sin_cache_offsets, "cos_sin_cache_offsets");
+  TORCH_CHECK(cos_sin_cache_offsets.scalar_type() == at::ScalarType::Long && cos_sin_cache_offsets.is_contiguous() &&
+                  cos_sin_cache_offsets.numel() == r.num_tokens,
+              "cos_sin_cache_offsets must be a contiguous int64 tensor with one entry per token");
+  TORCH_CHECK(rot_dim == r.rot_dim, "rot_dim must equal cos_sin_cache.size(1)");
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  const int st = b200_rotary_embedding(positions.data_ptr<int64_t>(), query.data_ptr(), key.data_ptr(),
+                                       cos_sin_cache.data_ptr(), cos_sin_cache_offsets.data_ptr<int64_t>(), r.num_tokens,
+                                       r.num_heads, r.num_kv_heads, head_size, r.rot_dim, r.query_stride, r.key_stride,
+                                       is_neox ? 1 : 0, dtype_code(query, "query"),
+                                       at::cuda::getCurrentCUDAStream().stream());
+  check_status(st, "batched_rotary_embedding");
+}
+
+// rotary_embedding(positions, query, key, ...) then reshape_and_cache(key, value, ...) in one call (one launch for
+// decode-sized batches).  query/key/value are [..., heads * head_size] as the model holds them after qkv.split
+// (vllm/model_executor/models/llama.py:155-158).
+void rotary_embedding_reshape_and_cache(torch::Tensor& positions, torch::Tensor& query, torch::Tensor& key,
+                                        torch::Tensor& value, int head_size, torch::Tensor& cos_sin_cache, bool is_neox,
+                                        torch::Tensor& key_cache, torch::Tensor& value_cache, torch::Tensor& slot_mapping,
+                                        const std::string& kv_cache_dtype) {
+  const RotaryShape r = rotary_shape(positions, query, key, head_size, cos_sin_cache);
+  require_cuda(value, "value"); require_cuda(key_cache, "key_cache"); require_cuda(value_cache, "value_cache");
+  require_cuda(slot_mapping, "slot_mapping");
+  TORCH_CHECK(value.dim() == key.dim() && value.size(-1) == key.size(-1) && value.stride(-1) == 1 &&
+                  value.scalar_type() == key.scalar_type() && value.numel() == key.numel(),
+              "value must have the shape and dtype of key");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Long && slot_mapping.is_contiguous() &&
+                  slot_mapping.numel() == r.num_tokens,
+              "slot_mapping must be a contiguous int64 tensor with one entry per token");
+  TORCH_CHECK(key_cache.is_contiguous() && value_cache.is_contiguous(), "key_cache/value_cache must be contiguous");
+  TORCH_CHECK(key_cache.dim() == 5 && key_cache.size(1) == r.num_kv_heads, "key_cache must be [blocks, kv_heads, D/x, bs, x]");
+  const int cache_code = cache_dtype_code(kv_cache_dtype, key, key_cache);
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  const int st = b200_rotary_embedding_reshape_and_cache(
+      positions.data_ptr<int64_t>(), query.data_ptr(), key.data_ptr(), value.data_ptr(), cos_sin_cache.data_ptr(),
+      r.num_tokens, r.num_heads, r.num_kv_heads, head_size, r.rot_dim, r.query_stride, r.key_stride, value.stride(-2),
+      is_neox ? 1 : 0, key_cache.data_ptr(), value_cache.data_ptr(), slot_mapping.data_ptr<int64_t>(),
+      (int32_t)key_cache.size(3), (int32_t)key_cache.size(4), key_cache.size(0), dtype_code(key, "key"), cache_code,
+      at::cuda::getCurrentCUDAStream().stream());
+  check_status(st, "rotary_embedding_reshape_and_cache");
+}
+
 }  // namespace
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
@@ -246,11 +334,16 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   ops.def("paged_attention_v1", &paged_attention_v1,
           "Compute the attention between an input query and the cached keys/values using PagedAttention.");
   ops.def("paged_attention_v2", &paged_attention_v2, "PagedAttention V2.");
+  ops.def("rotary_embedding", &rotary_embedding, "Apply GPT-NeoX or GPT-J style rotary embedding to query and key");
+  ops.def("batched_rotary_embedding", &batched_rotary_embedding,
+          "Apply GPT-NeoX or GPT-J style rotary embedding to query and key (supports multiple loras)");
   pybind11::module cache_ops = m.def_submodule("cache_ops", "cache writes and block moves (reference csrc/cache.h:8-29)");
   cache_ops.def("swap_blocks", &swap_blocks, "Swap in (out) the cache blocks from src to dst");
   cache_ops.def("copy_blocks", &copy_blocks, "Copy the cache blocks from src to dst");
   cache_ops.def("reshape_and_cache", &reshape_and_cache, "Reshape the key and value tensors and cache them");
   cache_ops.def("convert_fp8_e5m2", &convert_fp8_e5m2, "Convert the key and value cache to fp8_e5m2 data type");
+  cache_ops.def("rotary_embedding_reshape_and_cache", &rotary_embedding_reshape_and_cache,
+                "rotary_embedding followed by reshape_and_cache in one call (one launch for decode batches)");
   pybind11::module cuda_utils = m.def_submodule("cuda_utils", "device attributes (reference csrc/pybind.cpp:101-111)");
   cuda_utils.def("get_device_attribute",
                  [](int attribute, int device_id) { return b200_get_device_attribute(attribute, device_id); },
