@@ -97,13 +97,13 @@ def test_batched_rotary_offsets(dtype):
 @pytest.mark.parametrize("is_neox", [True, False])
 @pytest.mark.parametrize("dtype", DTYPES)
 @pytest.mark.parametrize("block_size", [8, 16, 32])
-@pytest.mark.parametrize("num_tokens", [1, 40, 200])
+@pytest.mark.parametrize("num_tokens", [1, 40, 200, 600])
 def test_fused_equals_the_two_ops(kv_cache_factory, num_tokens, block_size, dtype, is_neox, kv_cache_dtype):
     """The fused op IS rotary_embedding followed by reshape_and_cache: same q, k (in place) and caches, bit for
     bit, for decode-sized (single launch) and prefill-sized calls, with padding slots; and the sequence of the
     two reference CUDA kernels gives the same bits when oracle/_ref is built."""
     from oracle import paged_kv_oracle as O
-    hq, hkv, d, nb = 8, 2, 128, 64
+    hq, hkv, d, nb = 8, 2, 128, 96
     cache = O.compute_cos_sin_cache(d, 4096, 10000, dtype).cuda()
     gen = torch.Generator(device="cuda").manual_seed(3)
     pos = torch.randint(0, 4096, (num_tokens,), device="cuda", generator=gen)
@@ -124,7 +124,7 @@ def test_fused_equals_the_two_ops(kv_cache_factory, num_tokens, block_size, dtyp
         ops.rotary_embedding(pos, qs, ks, d, cache, is_neox)
         cache_ops.reshape_and_cache(ks.view(num_tokens, hkv, d), vs.view(num_tokens, hkv, d), kc_s, vc_s, slots,
                                     kv_cache_dtype)
-        assert fused_launches == (1 if num_tokens < 64 else 2), (name, fused_launches)
+        assert fused_launches == (1 if num_tokens < 512 else 2), (name, fused_launches)
         assert torch.equal(bits(qkv_f), bits(qkv_s)), name
         assert torch.equal(bits(kc_f), bits(kc_s)) and torch.equal(bits(vc_f), bits(vc_s)), name
         if ref is not None:

@@ -207,6 +207,51 @@ def bench_convert(iters, ours, ref):
     emit("convert_fp8_to_fp16", "256 Mi elements", n * 3, ms, ref_ms, exact)
 
 
+def bench_rope(name, desc, N, Hq, Hkv, D, bs, dtype, kv, ours_ops, ours_cache, ref):
+    """The decode step's rotary_embedding + reshape_and_cache pair (llama.py:156-158 -> attention backend):
+    ours fused (one launch), ours as two ops, the reference's two kernels; CUDA-graph replay times."""
+    sys.path.insert(0, ROOT)
+    from oracle import paged_kv_oracle as O   # cos/sin table recipe only (a checker-side helper, not timed)
+    dev = "cuda"
+    ce = 1 if kv == "fp8_e5m2" else 2
+    x = 16 // ce
+    cdt = torch.uint8 if kv == "fp8_e5m2" else dtype
+    NB = N + 8
+    nbuf = 4
+    g = torch.Generator().manual_seed(0)
+    cache = O.compute_cos_sin_cache(D, 8192, 10000, dtype).to(dev)
+    pos = torch.randint(0, 8192, (N,), generator=g).to(dev)
+    slots = (torch.randperm(NB, generator=g)[:N] * bs + torch.randint(0, bs, (N,), generator=g)).to(dev)
+    qkvs = [torch.randn(N, (Hq + 2 * Hkv) * D, dtype=dtype, device=dev) for _ in range(nbuf)]
+    views = [(q[:, :Hq * D], q[:, Hq * D:(Hq + Hkv) * D], q[:, (Hq + Hkv) * D:]) for q in qkvs]
+    kvs3 = [(k.view(N, Hkv, D), v.view(N, Hkv, D)) for _, k, v in views]
+    kcs = [torch.zeros(NB, Hkv, D // x, bs, x, dtype=cdt, device=dev) for _ in range(nbuf)]
+    vcs = [torch.zeros(NB, Hkv, D, bs, dtype=cdt, device=dev) for _ in range(nbuf)]
+
+    def fused(i):
+        ours_cache.rotary_embedding_reshape_and_cache(pos, views[i][0], views[i][1], views[i][2], D, cache, True,
+                                                      kcs[i], vcs[i], slots, kv)
+
+    def two(ops_mod, cache_mod):
+        def f(i):
+            ops_mod.rotary_embedding(pos, views[i][0], views[i][1], D, cache, True)
+            cache_mod.reshape_and_cache(kvs3[i][0], kvs3[i][1], kcs[i], vcs[i], slots, kv)
+        return f
+
+    t_f = timeit_graph(fused, nbuf)
+    t_2 = timeit_graph(two(ours_ops, ours_cache), nbuf)
+    t_r = timeit_graph(two(ref.ops, ref.cache_ops), nbuf) if ref is not None else None
+    es = 2
+    nbytes = N * (2 * (Hq + Hkv) * D * es + Hkv * D * es + 2 * Hkv * D * ce) + N * 16
+    line = {"case": name, "workload": desc, "algorithmic_bytes": nbytes, "fused_graph_replay_ms": round(t_f, 5),
+            "two_ops_graph_replay_ms": round(t_2, 5),
+            "reference_cuda_two_kernels_graph_replay_ms": round(t_r, 5) if t_r else None,
+            "fused_speedup_vs_reference_cuda": round(t_r / t_f, 2) if t_r else None,
+            "note": "latency case: per-call GPU time of 24 calls captured in one CUDA graph; bit-exactness of the "
+                    "fused op against both sequences is asserted in tests/test_rope_gpu.py"}
+    print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=50)
@@ -234,6 +279,14 @@ def main():
                       64, 32, 32, 128, 16, torch.float16, "auto", args.iters * 4, ours, ref, False)
         bench_reshape("reshape_and_cache_c3_decode", "C3 tp=8 decode: N=256 tokens, 1 kv head, head 128, bf16 (latency case)",
                       256, 8, 1, 128, 16, torch.bfloat16, "auto", args.iters * 4, ours, ref, False)
+    if want("rope"):
+        from vllm_splitwise_b200._C import ops as ours_ops
+        bench_rope("rope_reshape_and_cache_c4_decode", "C4 decode step: N=128 tokens, 32 q / 8 kv heads, head 128, bf16 -> fp8_e5m2",
+                   128, 32, 8, 128, 16, torch.bfloat16, "fp8_e5m2", ours_ops, ours, ref)
+        bench_rope("rope_reshape_and_cache_c2_decode", "C2 decode step: N=64 tokens, 32 q / 32 kv heads, head 128, fp16",
+                   64, 32, 32, 128, 16, torch.float16, "auto", ours_ops, ours, ref)
+        bench_rope("rope_reshape_and_cache_c3_decode", "C3 tp=8 decode step: N=256 tokens, 8 q / 1 kv head, head 128, bf16",
+                   256, 8, 1, 128, 16, torch.bfloat16, "auto", ours_ops, ours, ref)
     if want("copy"):
         bench_copy_blocks(args.iters, ours, ref)
     if want("swap"):

@@ -74,39 +74,45 @@ __device__ __forceinline__ CT cache_cvt(T v) {
 // vector.  V: element (h, d) lands at [blk, h, d, off] -- a scatter with stride block_size that one token
 // cannot avoid; the source side is read in 16-byte vectors.
 template <typename T, typename CT, bool FP8, int X, bool VEC>
-__global__ void __launch_bounds__(256) reshape_and_cache_token_kernel(
+__global__ void __launch_bounds__(512) reshape_and_cache_token_kernel(
     const T* __restrict__ key, const T* __restrict__ value, CT* __restrict__ key_cache,
     CT* __restrict__ value_cache, const int64_t* __restrict__ slot_mapping, int64_t key_stride,
     int64_t value_stride, int num_heads, int head_size, int block_size, int64_t num_blocks) {
+  constexpr int PER = 16 / (int)sizeof(T);
   const int64_t token = blockIdx.x;
-  const int64_t slot = slot_mapping[token];
-  if (slot < 0) return;  // padding (reference cache_kernels.cu:169-172)
-  const int64_t blk = slot / block_size;
-  const int off = static_cast<int>(slot % block_size);
-  if (blk >= num_blocks) return;  // out-of-range slot: never write outside the cache
-  const int chunks = head_size / X;
-  const int n_vec = num_heads * chunks;
+  const int n = num_heads * head_size;
+  const int n_kvec = n / X;    // 16-byte cache vectors of the K row
+  const int n_vvec = n / PER;  // 16-byte source vectors of the V row
   const T* ksrc = key + token * key_stride;
   const T* vsrc = value + token * value_stride;
-  CT* kdst = key_cache + blk * (int64_t)num_heads * head_size * block_size;
-  CT* vdst = value_cache + blk * (int64_t)num_heads * head_size * block_size;
-
-  for (int v = threadIdx.x; v < n_vec; v += blockDim.x) {
-    // (h * chunks + c) * X == v * X: heads are dense in the source row and in the cache block
-    alignas(16) T src[X];
-    load_elems<T, X, VEC>(ksrc + (int64_t)v * X, src);
-    alignas(16) CT tmp[X];
+  // The slot and the source vectors are independent loads: all of them are issued before anything is
+  // consumed, so a decode-sized call costs one global-memory round trip, not three in a row.
+  const int64_t slot = slot_mapping[token];
+  for (int base = 0; base < n_vvec; base += blockDim.x) {  // n_vvec >= n_kvec (PER <= X)
+    const int i = base + threadIdx.x;
+    alignas(16) T ks[X];
+    alignas(16) T vs[PER];
+    const bool has_k = i < n_kvec, has_v = i < n_vvec;
+    // (h * chunks + c) * X == i * X: heads are dense in the source row and in the cache block
+    if (has_k) load_elems<T, X, VEC>(ksrc + (int64_t)i * X, ks);
+    if (has_v) load_elems<T, PER, VEC>(vsrc + (int64_t)i * PER, vs);
+    if (slot < 0) continue;  // padding (reference cache_kernels.cu:169-172)
+    const int64_t blk = slot / block_size;
+    const int off = static_cast<int>(slot - blk * block_size);
+    if (blk >= num_blocks) continue;  // out-of-range slot: never write outside the cache
+    CT* kdst = key_cache + blk * (int64_t)n * block_size;
+    CT* vdst = value_cache + blk * (int64_t)n * block_size;
+    if (has_k) {
+      alignas(16) CT tmp[X];
 #pragma unroll
-    for (int e = 0; e < X; ++e) tmp[e] = cache_cvt<T, CT, FP8>(src[e]);
-    *reinterpret_cast<uint4*>(kdst + ((int64_t)v * block_size + off) * X) = *reinterpret_cast<const uint4*>(tmp);
-  }
-  constexpr int PER = 16 / (int)sizeof(T);
-  const int n = num_heads * head_size;
-  for (int i0 = threadIdx.x * PER; i0 < n; i0 += blockDim.x * PER) {
-    alignas(16) T src[PER];
-    load_elems<T, PER, VEC>(vsrc + i0, src);
+      for (int e = 0; e < X; ++e) tmp[e] = cache_cvt<T, CT, FP8>(ks[e]);
+      *reinterpret_cast<uint4*>(kdst + ((int64_t)i * block_size + off) * X) = *reinterpret_cast<const uint4*>(tmp);
+    }
+    if (has_v) {
 #pragma unroll
-    for (int e = 0; e < PER; ++e) vdst[(int64_t)(i0 + e) * block_size + off] = cache_cvt<T, CT, FP8>(src[e]);
+      for (int e = 0; e < PER; ++e)
+        vdst[(int64_t)(i * PER + e) * block_size + off] = cache_cvt<T, CT, FP8>(vs[e]);
+    }
   }
 }
 
@@ -122,42 +128,50 @@ __global__ void __launch_bounds__(256) reshape_and_cache_token_kernel(
 // a warp writes 32 adjacent rows, i.e. one contiguous span -- instead of the reference's isolated 1-2 byte
 // stores block_size elements apart (cache_kernels.cu:188-191,204).  Any other mapping (padding, shuffled or
 // unaligned slots) takes the element-wise path of the same kernel.
-constexpr int kTileTok = 16;
 
-template <typename T, typename CT, bool FP8, int X, bool VEC>
+template <typename T, typename CT, bool FP8, int X, bool VEC, bool KSMEM, int TOK>
 __global__ void __launch_bounds__(256) reshape_and_cache_tile_kernel(
     const T* __restrict__ key, const T* __restrict__ value, CT* __restrict__ key_cache,
     CT* __restrict__ value_cache, const int64_t* __restrict__ slot_mapping, int64_t key_stride,
     int64_t value_stride, int num_tokens, int num_heads, int head_size, int block_size,
-    int64_t num_blocks) {
-  constexpr int TOK = kTileTok;
+    int64_t num_blocks, int head_major) {
+  static_assert(TOK == 16 || TOK == 32, "the slot decode runs on one warp");
   constexpr int PER = 16 / (int)sizeof(T);
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int pitch = head_size + PER;  // elements; rows stay 16-byte aligned
   T* vt = reinterpret_cast<T*>(smem_raw);
+  T* kt = vt + TOK * pitch;  // KSMEM only
   __shared__ int64_t s_base[TOK];  // element offset of (blk, h, 0, 0) or -1 = skip
   __shared__ int s_off[TOK];
   __shared__ int s_fast;
 
-  const int t0 = blockIdx.x * TOK;
-  const int h = blockIdx.y;
+  // head_major: consecutive CTAs take the heads of one token tile, so CTAs that run together read one
+  // contiguous span of each source row (all heads) instead of 256-byte pieces a whole row apart.
+  const int tile = head_major ? blockIdx.y : blockIdx.x;
+  const int h = head_major ? blockIdx.x : blockIdx.y;
+  const int t0 = tile * TOK;
   const int nt = min(TOK, num_tokens - t0);
   const int G = min(block_size, TOK);
   const int64_t head_elems = (int64_t)head_size * block_size;
 
-  // ---- V source tile -> shared memory (issued first: the longest dependency chain) ----
+  // ---- source tiles -> shared memory (issued first: the longest dependency chain) ----
   const T* vsrc = value + (int64_t)t0 * value_stride + h * head_size;
+  const T* ksrc = key + (int64_t)t0 * key_stride + h * head_size;
   if constexpr (VEC) {
     const int vpr = head_size / PER;  // 16-byte vectors per row
     for (int v = threadIdx.x; v < nt * vpr; v += blockDim.x) {
       const int t = v / vpr, c = v - t * vpr;
+      uint4 kv;
+      if constexpr (KSMEM) kv = ld_nc_v4(reinterpret_cast<const uint4*>(ksrc + (int64_t)t * key_stride) + c);
       *reinterpret_cast<uint4*>(vt + t * pitch + c * PER) =
           ld_nc_v4(reinterpret_cast<const uint4*>(vsrc + (int64_t)t * value_stride) + c);
+      if constexpr (KSMEM) *reinterpret_cast<uint4*>(kt + t * pitch + c * PER) = kv;
     }
   } else {
     for (int i = threadIdx.x; i < nt * head_size; i += blockDim.x) {
       const int t = i / head_size, d = i - t * head_size;
       vt[t * pitch + d] = vsrc[(int64_t)t * value_stride + d];
+      if constexpr (KSMEM) kt[t * pitch + d] = ksrc[(int64_t)t * key_stride + d];
     }
   }
 
@@ -187,14 +201,20 @@ __global__ void __launch_bounds__(256) reshape_and_cache_tile_kernel(
     if (t == 0) s_fast = VEC && all_ok;
   }
 
-  // ---- K: global -> registers -> one 16-byte cache vector per (token, chunk), token-fastest ----
+  // ---- K: one 16-byte cache vector per (token, chunk), token-fastest ----
   const int chunks = head_size / X;
-  const T* ksrc = key + (int64_t)t0 * key_stride + h * head_size;
+  if constexpr (KSMEM) __syncthreads();
   for (int v = threadIdx.x; v < nt * chunks; v += blockDim.x) {
     const int c = v / nt, t = v - c * nt;
     const int64_t slot = slot_mapping[t0 + t];
     alignas(16) T src[X];
-    load_elems<T, X, VEC>(ksrc + (int64_t)t * key_stride + c * X, src);
+    if constexpr (KSMEM) {
+#pragma unroll
+      for (int i = 0; i < X / PER; ++i)
+        *reinterpret_cast<uint4*>(src + i * PER) = *reinterpret_cast<const uint4*>(kt + t * pitch + c * X + i * PER);
+    } else {
+      load_elems<T, X, VEC>(ksrc + (int64_t)t * key_stride + c * X, src);
+    }
     if (slot < 0) continue;
     const int64_t blk = slot / block_size;
     if (blk >= num_blocks) continue;
@@ -205,7 +225,7 @@ __global__ void __launch_bounds__(256) reshape_and_cache_tile_kernel(
     *reinterpret_cast<uint4*>(key_cache + (blk * num_heads + h) * head_elems + ((int64_t)c * block_size + off) * X) =
         *reinterpret_cast<const uint4*>(tmp);
   }
-  __syncthreads();
+  if constexpr (!KSMEM) __syncthreads();
 
   // ---- V ----
   if (s_fast) {
@@ -252,22 +272,44 @@ static int launch_reshape_and_cache(const void* key, const void* value, void* ke
     if (vec) KERNEL<T, CT, FP8, X, true><<<GRID, THREADS, SMEM, stream>>>(__VA_ARGS__);                    \
     else KERNEL<T, CT, FP8, X, false><<<GRID, THREADS, SMEM, stream>>>(__VA_ARGS__);                       \
   } while (0)
-  // Prefill-sized calls take the tile kernel; decode-sized calls (one token per sequence, every
-  // token in a different block) take the token kernel.
-  if (num_tokens >= 4 * kTileTok) {
-    dim3 grid((num_tokens + kTileTok - 1) / kTileTok, num_heads);
-    const size_t smem = (size_t)kTileTok * (head_size + PER) * sizeof(T);
-    B200_RC_LAUNCH(reshape_and_cache_tile_kernel, grid, 256, smem, (const T*)key, (const T*)value, (CT*)key_cache,
-                   (CT*)value_cache, slot_mapping, key_stride, value_stride, num_tokens, num_heads, head_size,
-                   block_size, num_blocks);
+#define B200_RC_LAUNCH_TILE(KS, TK, GRID, SMEM, ...)                                                      \
+  do {                                                                                                    \
+    if (vec) reshape_and_cache_tile_kernel<T, CT, FP8, X, true, KS, TK><<<GRID, 256, SMEM, stream>>>(__VA_ARGS__);   \
+    else reshape_and_cache_tile_kernel<T, CT, FP8, X, false, KS, TK><<<GRID, 256, SMEM, stream>>>(__VA_ARGS__);      \
+  } while (0)
+  // Prefill-sized calls take the tile kernel; decode-sized calls (one token per sequence, every token in a
+  // different block: up to a few hundred tokens) take the token kernel.  The slots cannot be inspected on
+  // the host, so the split is by size: measured (profiles/), a 128-token decode batch costs 2x more through
+  // the tile kernel (32 CTAs, element-wise path) than through the token kernel.
+  if (num_tokens >= 512) {
+    static const int variant = getenv("B200_RC_VARIANT") ? atoi(getenv("B200_RC_VARIANT")) : 1;  // tuning knobs
+    static const int tok_env = getenv("B200_RC_TOK") ? atoi(getenv("B200_RC_TOK")) : 32;
+    const bool ksmem = variant & 1;
+    // 32-token tiles while they still fit the default 48 KiB of dynamic shared memory, else 16
+    const size_t row = (size_t)(head_size + PER) * sizeof(T);
+    // and while 32-token tiles still give every SM a few waves of CTAs (measured: C4 prefill +20 %, C5 -6 %)
+    const bool many = (long long)((num_tokens + 31) / 32) * num_heads >= 4ll * 8 * num_sms(-1);
+    const int tok = (tok_env == 32 && many && (ksmem ? 2 : 1) * 32 * row <= 48 * 1024) ? 32 : 16;
+    const int tiles = (num_tokens + tok - 1) / tok;
+    const int head_major = (variant & 2) && tiles <= 65535;
+    dim3 grid = head_major ? dim3(num_heads, tiles) : dim3(tiles, num_heads);
+    const size_t smem = (size_t)(ksmem ? 2 : 1) * tok * row;
+#define B200_RC_TILE_ARGS (const T*)key, (const T*)value, (CT*)key_cache, (CT*)value_cache, slot_mapping, key_stride, \
+                          value_stride, num_tokens, num_heads, head_size, block_size, num_blocks, head_major
+    if (ksmem && tok == 32) B200_RC_LAUNCH_TILE(true, 32, grid, smem, B200_RC_TILE_ARGS);
+    else if (ksmem) B200_RC_LAUNCH_TILE(true, 16, grid, smem, B200_RC_TILE_ARGS);
+    else if (tok == 32) B200_RC_LAUNCH_TILE(false, 32, grid, smem, B200_RC_TILE_ARGS);
+    else B200_RC_LAUNCH_TILE(false, 16, grid, smem, B200_RC_TILE_ARGS);
+#undef B200_RC_TILE_ARGS
   } else {
     const int work = num_heads * head_size / PER;  // 16-byte source vectors per token
-    const int threads = std::min(256, std::max(32, (work + 31) / 32 * 32));
+    const int threads = std::min(512, std::max(32, (work + 31) / 32 * 32));
     B200_RC_LAUNCH(reshape_and_cache_token_kernel, num_tokens, threads, 0, (const T*)key, (const T*)value,
                    (CT*)key_cache, (CT*)value_cache, slot_mapping, key_stride, value_stride, num_heads, head_size,
                    block_size, num_blocks);
   }
 #undef B200_RC_LAUNCH
+#undef B200_RC_LAUNCH_TILE
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -503,7 +545,8 @@ B200_API int b200_swap_blocks(const void* src, void* dst, int64_t block_bytes, c
   // (the reference issues one cudaMemcpyAsync per block, cache_kernels.cu:47-58).  Pageable host memory and
   // lists that merge into a few long runs keep the copy engine.
   static const bool no_zero_copy = getenv("B200_SWAP_NO_ZERO_COPY") != nullptr;  // A/B knob
-  if (runs > 2 && !no_zero_copy) {
+  // (measured, profiles/: H2D through the mapping beats the copy engine even for one long run: 50 vs 38-45 GB/s)
+  if ((runs > 2 || kind == B200_SWAP_H2D) && !no_zero_copy) {
     const void* host = kind == B200_SWAP_D2H ? (const void*)dst : src;
     cudaPointerAttributes attr;
     if (cudaPointerGetAttributes(&attr, host) == cudaSuccess && attr.type == cudaMemoryTypeHost &&

@@ -230,7 +230,7 @@ B200_API int b200_rotary_embedding_reshape_and_cache(
   // Prefill-sized calls: rotate in place, then the tiled cache write (two large launches; the K rows the second
   // one reads are still in L2).  Decode-sized calls: the single fused launch.
   const size_t smem = (size_t)num_kv_heads * head_size * dtype_size(src_dtype);
-  if (num_tokens >= 64 || num_tokens > INT32_MAX || smem > 48 * 1024) {
+  if (num_tokens >= 512 || smem > 48 * 1024) {
     st = b200_rotary_embedding(positions, query, key, cos_sin_cache, nullptr, num_tokens, num_heads, num_kv_heads,
                                head_size, rot_dim, query_stride, key_stride, is_neox, src_dtype, stream_);
     if (st != B200_OK) return st;
