@@ -98,13 +98,16 @@ def test_batched_rotary_offsets(dtype):
 @pytest.mark.parametrize("dtype", DTYPES)
 @pytest.mark.parametrize("block_size", [8, 16, 32])
 @pytest.mark.parametrize("num_tokens", [1, 40, 200, 600])
-def test_fused_equals_the_two_ops(kv_cache_factory, num_tokens, block_size, dtype, is_neox, kv_cache_dtype):
+@pytest.mark.parametrize("d,rot", [(128, 128), (80, 80), (256, 64)])
+def test_fused_equals_the_two_ops(kv_cache_factory, d, rot, num_tokens, block_size, dtype, is_neox, kv_cache_dtype):
     """The fused op IS rotary_embedding followed by reshape_and_cache: same q, k (in place) and caches, bit for
     bit, for decode-sized (single launch) and prefill-sized calls, with padding slots; and the sequence of the
     two reference CUDA kernels gives the same bits when oracle/_ref is built."""
     from oracle import paged_kv_oracle as O
-    hq, hkv, d, nb = 8, 2, 128, 96
-    cache = O.compute_cos_sin_cache(d, 4096, 10000, dtype).cuda()
+    # (128,128): vector kernel; (80,80) NeoX with an fp8 cache: 40 pairs do not fill 16-element chunks -> scalar
+    # kernel; (256,64): pass-through chunks past rot_dim
+    hq, hkv, nb = 8, 2, 96
+    cache = O.compute_cos_sin_cache(rot, 4096, 10000, dtype).cuda()
     gen = torch.Generator(device="cuda").manual_seed(3)
     pos = torch.randint(0, 4096, (num_tokens,), device="cuda", generator=gen)
     slots = torch.randperm(nb * block_size, device="cuda", generator=gen)[:num_tokens]
@@ -146,6 +149,37 @@ def test_fused_equals_the_two_ops(kv_cache_factory, num_tokens, block_size, dtyp
             assert torch.equal(bits(kc_f.cpu()), bits(kc_o)) and torch.equal(bits(vc_f.cpu()), bits(vc_o)), name
         else:
             assert torch.allclose(qkv_f.cpu(), qkv_o, rtol=1e-6, atol=1e-7), name
+
+
+@pytest.mark.parametrize("dtype", [torch.half, torch.float])
+@pytest.mark.parametrize("is_neox", [True, False])
+def test_unaligned_rows_take_the_scalar_kernels(dtype, is_neox):
+    """q/k/v rows that are not 16-byte aligned (a view one element into a buffer): same results."""
+    from oracle import paged_kv_oracle as O
+    from vllm_splitwise_b200._C import cache_ops, ops
+    n, hq, hkv, d, bs, nb = 9, 4, 2, 64, 16, 16
+    cache = O.compute_cos_sin_cache(d, 256, 10000, dtype).cuda()
+    pos = torch.arange(n, device="cuda") * 7
+    slots = torch.randperm(nb * bs, device="cuda")[:n]
+    width = (hq + 2 * hkv) * d
+    buf = torch.randn(n * width + 8, dtype=dtype, device="cuda")
+    res = []
+    for shift in (0, 1):
+        qkv = buf[shift:shift + n * width].view(n, width).clone() if shift == 0 else None
+        if shift == 1:
+            holder = torch.empty(n * width + 8, dtype=dtype, device="cuda")
+            qkv = holder[1:1 + n * width].view(n, width)
+            qkv.copy_(buf[0:n * width].view(n, width))
+        q, k, v = qkv[:, :hq * d], qkv[:, hq * d:(hq + hkv) * d], qkv[:, (hq + hkv) * d:]
+        x = 16 // qkv.element_size()
+        kc = torch.zeros(nb, hkv, d // x, bs, x, dtype=dtype, device="cuda")
+        vc = torch.zeros(nb, hkv, d, bs, dtype=dtype, device="cuda")
+        cache_ops.rotary_embedding_reshape_and_cache(pos, q, k, v, d, cache, is_neox, kc, vc, slots, "auto")
+        q2 = q.clone()
+        ops.rotary_embedding(pos, q2, k.clone(), d, cache, is_neox)   # rotates once more: only exercises the path
+        res.append((qkv.clone(), kc, vc, q2))
+    for a, b in zip(*res):
+        assert torch.equal(bits(a), bits(b))
 
 
 def _launches():

@@ -11,6 +11,7 @@
 // product and the sum rounded to the element type (the reference computes in scalar_t, c10::Half / BFloat16
 // operators: float op, round), so f16/bf16 results are bit-identical to rotary_embedding + reshape_and_cache.
 #include <algorithm>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -144,10 +145,199 @@ __global__ void __launch_bounds__(256) rope_reshape_and_cache_token_kernel(
     vdst[(int64_t)i * block_size + off] = cache_cvt<T, CT, FP8>(vrow[i]);
 }
 
+// ---- vectorised path ---------------------------------------------------------------------------
+// The scalar kernels above walk (head, pair) items with 2-byte loads in a loop whose iterations the compiler
+// must keep in order (in-place updates may alias); with many heads that is several dependent global round
+// trips per token.  Here one work item is a 16-byte vector (q) or one x-element cache chunk (k) and a token's
+// items are spread over up to 512 threads, so every global load of the token is in flight at once:
+//   q item  NeoX: vectors j and j + embed of a head (PER pairs);   GPT-J: one vector (PER/2 adjacent pairs)
+//   k item  NeoX: chunks c and c + embed/X of a head (X pairs);    GPT-J: one chunk (X/2 pairs);
+//           rotated in registers, stored in place AND (CACHE) as 16-byte vectors of the paged K cache;
+//           chunks past rot_dim are pass-through (cache write only)
+//   v item  (CACHE) one 16-byte source vector scattered to the paged V cache.
+template <typename T, int N>
+__device__ __forceinline__ void ld_row(const T* p, T* out) {  // N * sizeof(T) is 8 or a multiple of 16
+  constexpr int BYTES = N * (int)sizeof(T);
+  if constexpr (BYTES % 16 == 0) {
+#pragma unroll
+    for (int i = 0; i < BYTES / 16; ++i) reinterpret_cast<uint4*>(out)[i] = reinterpret_cast<const uint4*>(p)[i];
+  } else {
+    static_assert(BYTES == 8, "8-byte tail only");
+    *reinterpret_cast<uint2*>(out) = *reinterpret_cast<const uint2*>(p);
+  }
+}
+template <typename T, int N>
+__device__ __forceinline__ void st_row(T* p, const T* in) {
+  constexpr int BYTES = N * (int)sizeof(T);
+  static_assert(BYTES % 16 == 0, "whole vectors");
+#pragma unroll
+  for (int i = 0; i < BYTES / 16; ++i) reinterpret_cast<uint4*>(p)[i] = reinterpret_cast<const uint4*>(in)[i];
+}
+
+template <typename T>
+__device__ __forceinline__ void rotate_xy(T& x, T& y, T c, T s) {
+  const T x0 = x, y0 = y;
+  if constexpr (sizeof(T) == 4) {
+    x = x0 * c - y0 * s;
+    y = y0 * c + x0 * s;
+  } else {
+    x = rnd_sub<T>(rnd_mul<T>(x0, c), rnd_mul<T>(y0, s));
+    y = rnd_add<T>(rnd_mul<T>(y0, c), rnd_mul<T>(x0, s));
+  }
+}
+
+// N elements at xp (and, NeoX, N more at xp + embed) rotated in registers; results left in xs / ys.
+template <typename T, int N, bool NEOX>
+__device__ __forceinline__ void rotate_item(const T* xp, int embed, const T* __restrict__ cos_p,
+                                            const T* __restrict__ sin_p, T* xs, T* ys) {
+  if constexpr (NEOX) {
+    alignas(16) T cs[N], sn[N];
+    ld_row<T, N>(xp, xs);
+    ld_row<T, N>(xp + embed, ys);
+    ld_row<T, N>(cos_p, cs);
+    ld_row<T, N>(sin_p, sn);
+#pragma unroll
+    for (int e = 0; e < N; ++e) rotate_xy<T>(xs[e], ys[e], cs[e], sn[e]);
+  } else {
+    alignas(16) T cs[N / 2], sn[N / 2];
+    ld_row<T, N>(xp, xs);
+    ld_row<T, N / 2>(cos_p, cs);
+    ld_row<T, N / 2>(sin_p, sn);
+#pragma unroll
+    for (int e = 0; e < N / 2; ++e) rotate_xy<T>(xs[2 * e], xs[2 * e + 1], cs[e], sn[e]);
+  }
+}
+
+template <typename T, typename CT, bool FP8, int X, bool NEOX, bool CACHE>
+__global__ void __launch_bounds__(512) rope_vec_kernel(
+    const int64_t* __restrict__ positions, const int64_t* __restrict__ cache_offsets, T* query, T* key,
+    const T* __restrict__ value, const T* __restrict__ cos_sin_cache, int rot_dim, int64_t query_stride,
+    int64_t key_stride, int64_t value_stride, int num_heads, int num_kv_heads, int head_size,
+    CT* __restrict__ key_cache, CT* __restrict__ value_cache, const int64_t* __restrict__ slot_mapping, int block_size,
+    int64_t num_blocks) {
+  constexpr int PER = 16 / (int)sizeof(T);
+  const int64_t token = blockIdx.x;
+  int64_t pos = positions[token];
+  if (cache_offsets != nullptr) pos += cache_offsets[token];
+  const int embed = rot_dim / 2;
+  const T* cos_ptr = cos_sin_cache + pos * rot_dim;
+  const T* sin_ptr = cos_ptr + embed;
+  T* qrow = query + token * query_stride;
+  T* krow = key + token * key_stride;
+
+  // cache destination of this token (CACHE only); a negative slot is padding: rotate, skip the cache
+  bool cache_ok = false;
+  int off = 0;
+  CT* kdst = nullptr;
+  CT* vdst = nullptr;
+  const int nkv = num_kv_heads * head_size;
+  if constexpr (CACHE) {
+    const int64_t slot = slot_mapping[token];
+    if (slot >= 0) {
+      const int64_t blk = slot / block_size;
+      off = static_cast<int>(slot - blk * block_size);
+      cache_ok = blk < num_blocks;
+      kdst = key_cache + blk * (int64_t)nkv * block_size;
+      vdst = value_cache + blk * (int64_t)nkv * block_size;
+    }
+  }
+
+  const int q_per_head = (NEOX ? embed : rot_dim) / PER;
+  const int nq = num_heads * q_per_head;
+  const int chunks = head_size / X;                         // cache chunks per head
+  const int k_rot = (NEOX ? embed : rot_dim) / X;           // rotating k items per head
+  const int k_pass = CACHE ? (head_size - rot_dim) / X : 0; // pass-through chunks per head
+  const int k_per_head = k_rot + k_pass;
+  const int nk = num_kv_heads * k_per_head;
+  const int nv = CACHE ? nkv / PER : 0;
+  const int total = nq + nk + nv;
+
+  for (int it = threadIdx.x; it < total; it += blockDim.x) {
+    if (it < nq) {
+      const int h = it / q_per_head, j = it - h * q_per_head;
+      T* xp = qrow + (int64_t)h * head_size + j * PER;
+      alignas(16) T xs[PER], ys[PER];
+      rotate_item<T, PER, NEOX>(xp, embed, cos_ptr + (NEOX ? j * PER : j * PER / 2), sin_ptr + (NEOX ? j * PER : j * PER / 2),
+                                xs, ys);
+      st_row<T, PER>(xp, xs);
+      if constexpr (NEOX) st_row<T, PER>(xp + embed, ys);
+    } else if (it < nq + nk) {
+      const int i = it - nq;
+      const int h = i / k_per_head, c = i - h * k_per_head;
+      T* hrow = krow + (int64_t)h * head_size;
+      alignas(16) T xs[X], ys[X];
+      alignas(16) CT tmp[X];
+      if (c < k_rot) {
+        T* xp = hrow + c * X;
+        rotate_item<T, X, NEOX>(xp, embed, cos_ptr + (NEOX ? c * X : c * X / 2), sin_ptr + (NEOX ? c * X : c * X / 2), xs, ys);
+        st_row<T, X>(xp, xs);
+        if constexpr (NEOX) st_row<T, X>(xp + embed, ys);
+        if (CACHE && cache_ok) {
+#pragma unroll
+          for (int e = 0; e < X; ++e) tmp[e] = cache_cvt<T, CT, FP8>(xs[e]);
+          *reinterpret_cast<uint4*>(kdst + ((int64_t)(h * chunks + c) * block_size + off) * X) =
+              *reinterpret_cast<const uint4*>(tmp);
+          if constexpr (NEOX) {
+#pragma unroll
+            for (int e = 0; e < X; ++e) tmp[e] = cache_cvt<T, CT, FP8>(ys[e]);
+            *reinterpret_cast<uint4*>(kdst + ((int64_t)(h * chunks + c + embed / X) * block_size + off) * X) =
+                *reinterpret_cast<const uint4*>(tmp);
+          }
+        }
+      } else if (CACHE && cache_ok) {  // pass-through chunk: d in [rot_dim, head_size)
+        const int cc = rot_dim / X + (c - k_rot);
+        ld_row<T, X>(hrow + cc * X, xs);
+#pragma unroll
+        for (int e = 0; e < X; ++e) tmp[e] = cache_cvt<T, CT, FP8>(xs[e]);
+        *reinterpret_cast<uint4*>(kdst + ((int64_t)(h * chunks + cc) * block_size + off) * X) =
+            *reinterpret_cast<const uint4*>(tmp);
+      }
+    } else if (CACHE) {
+      const int i = it - nq - nk;
+      alignas(16) T vs[PER];
+      *reinterpret_cast<uint4*>(vs) = ld_nc_v4(value + token * value_stride + (int64_t)i * PER);
+      if (cache_ok) {
+#pragma unroll
+        for (int e = 0; e < PER; ++e)
+          vdst[(int64_t)(i * PER + e) * block_size + off] = cache_cvt<T, CT, FP8>(vs[e]);
+      }
+    }
+  }
+}
+
+// Host-side proof that the vectorised kernel's 16-byte (and 8-byte) accesses are aligned.
+inline bool rope_vec_ok(const void* query, const void* key, const void* value, const void* cos_sin_cache, int elt,
+                        int head_size, int rot_dim, int64_t qs, int64_t ks, int64_t vs, bool neox, int x) {
+  const int embed = rot_dim / 2;
+  auto a16 = [](const void* p) { return reinterpret_cast<uintptr_t>(p) % 16 == 0; };
+  if (!a16(query) || !a16(key) || (value && !a16(value)) || !a16(cos_sin_cache)) return false;
+  if ((qs * elt) % 16 || (ks * elt) % 16 || (vs * elt) % 16 || (head_size * elt) % 16) return false;
+  if ((rot_dim * elt) % 16 || (embed * elt) % 16) return false;
+  if (head_size % x || rot_dim % x) return false;
+  return neox ? embed % x == 0 : true;
+}
+
 template <typename T>
 int launch_rotary(const int64_t* positions, void* query, void* key, const void* cos_sin_cache, const int64_t* offsets,
                   int64_t num_tokens, int num_heads, int num_kv_heads, int head_size, int rot_dim, int64_t query_stride,
                   int64_t key_stride, bool neox, cudaStream_t stream) {
+  constexpr int PER = 16 / (int)sizeof(T);
+  static const bool no_vec = getenv("B200_ROPE_NO_VEC") != nullptr;  // A/B knob
+  if (!no_vec && rope_vec_ok(query, key, nullptr, cos_sin_cache, (int)sizeof(T), head_size, rot_dim, query_stride,
+                             key_stride, 0, neox, PER)) {
+    const int items = (num_heads + num_kv_heads) * (neox ? rot_dim / 2 : rot_dim) / PER;
+    const int threads = std::max(32, std::min((items + 31) / 32 * 32, 512));
+    if (neox)
+      rope_vec_kernel<T, T, false, PER, true, false><<<(unsigned)num_tokens, threads, 0, stream>>>(
+          positions, offsets, (T*)query, (T*)key, nullptr, (const T*)cos_sin_cache, rot_dim, query_stride, key_stride, 0,
+          num_heads, num_kv_heads, head_size, nullptr, nullptr, nullptr, 0, 0);
+    else
+      rope_vec_kernel<T, T, false, PER, false, false><<<(unsigned)num_tokens, threads, 0, stream>>>(
+          positions, offsets, (T*)query, (T*)key, nullptr, (const T*)cos_sin_cache, rot_dim, query_stride, key_stride, 0,
+          num_heads, num_kv_heads, head_size, nullptr, nullptr, nullptr, 0, 0);
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+  }
   const int threads = std::max(32, std::min(num_heads * rot_dim / 2, 512));  // reference :139-140
   if (neox)
     rotary_embedding_kernel<T, true><<<(unsigned)num_tokens, threads, 0, stream>>>(
@@ -167,7 +357,25 @@ int launch_fused_token(const int64_t* positions, void* query, void* key, const v
                        int64_t ks, int64_t vs, bool neox, void* key_cache, void* value_cache, const int64_t* slots,
                        int block_size, int64_t num_blocks, cudaStream_t stream) {
   constexpr int X = 16 / (int)sizeof(CT);
+  constexpr int PER = 16 / (int)sizeof(T);
   if (head_size % X != 0) return B200_ERR_HEAD_SIZE;
+  static const bool no_vec = getenv("B200_ROPE_NO_VEC") != nullptr;  // A/B knob
+  if (!no_vec &&
+      rope_vec_ok(query, key, value, cos_sin_cache, (int)sizeof(T), head_size, rot_dim, qs, ks, vs, neox, X)) {
+    const int half = neox ? rot_dim / 2 : rot_dim;
+    const int items = num_heads * half / PER + num_kv_heads * (half / X + (head_size - rot_dim) / X) +
+                      num_kv_heads * head_size / PER;
+    const int threads = std::max(32, std::min((items + 31) / 32 * 32, 512));
+#define B200_FUSED_VEC(NEOX)                                                                                      \
+  rope_vec_kernel<T, CT, FP8, X, NEOX, true><<<(unsigned)num_tokens, threads, 0, stream>>>(                       \
+      positions, nullptr, (T*)query, (T*)key, (const T*)value, (const T*)cos_sin_cache, rot_dim, qs, ks, vs,      \
+      num_heads, num_kv_heads, head_size, (CT*)key_cache, (CT*)value_cache, slots, block_size, num_blocks)
+    if (neox) B200_FUSED_VEC(true);
+    else B200_FUSED_VEC(false);
+#undef B200_FUSED_VEC
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+  }
   const size_t smem = (size_t)num_kv_heads * head_size * sizeof(T);
   if (smem > 48 * 1024) return B200_ERR_ARG;
 #define B200_FUSED(NEOX)                                                                                          \
