@@ -222,6 +222,17 @@ B200_API int b200_kv_put_blocks(const int64_t* src_ptrs, const int64_t* dst_ptrs
                        const int32_t* runs, int32_t num_runs, int64_t block_bytes,
                        int32_t max_ctas, b200_stream_t stream);
 
+/* Run lists longer than one launch's parameter table (several hundred runs: many fragmented prompts put in
+ * one go).  b200_kv_put_table_build (host only, no CUDA call) turns runs [num_runs][2] into a table of
+ * 3*num_runs+1 int32 -- starts, lengths, exclusive tile prefix -- that the caller copies to the device ONCE
+ * and reuses for every layer (the backends put the same block list 2 x num_layers times,
+ * flash_attn.py:81-86); b200_kv_put_blocks_table then moves all of it in one launch. */
+B200_API int b200_kv_put_table_build(const int32_t* runs, int32_t num_runs, int64_t block_bytes, int32_t* table,
+                            int32_t* tile_vecs_out, int64_t* tiles_per_buf_out);
+B200_API int b200_kv_put_blocks_table(const int64_t* src_ptrs, const int64_t* dst_ptrs, int32_t num_bufs,
+                             const int32_t* dev_table, int32_t num_runs, int32_t tile_vecs, int64_t tiles_per_buf,
+                             int64_t block_bytes, int32_t max_ctas, b200_stream_t stream);
+
 /* After all prior work on `stream`: system-scope release store of `value` to *remote_flag (a
  * peer-mapped uint64).  Replaces nw_cache_out_signal_kernel (kv_comm_kernels.cu:22-29). */
 B200_API int b200_kv_signal(uint64_t* remote_flag, uint64_t value, b200_stream_t stream);

@@ -109,6 +109,7 @@ class KVCacheCommunicator:
         self.defer_puts = defer_puts
         self._pending_layer = -1
         self._pending_runs: List[Tuple[int, int]] = []
+        self._tables: dict = {}
         # optional side stream: transfers then overlap the prefill compute that follows on the main stream
         # (the reference's host proxy copies asynchronously too); signal rides the same side stream.
         self.comm_stream = comm_stream
@@ -137,21 +138,62 @@ class KVCacheCommunicator:
         if not 0 <= sem_id < MAX_SLOT_IDS:
             raise ValueError(f"sem_id {sem_id} out of range [0, {MAX_SLOT_IDS})")
 
+    PARAM_TABLE_RUNS = 440  # runs one launch carries in its kernel parameters (csrc/kv_transfer.cu kMaxRuns)
+
+    def _device_table(self, key):
+        """(device int32 table, num_runs, tile_vecs, tiles_per_buf) for a long run list, uploaded once and kept:
+        the same list is put for every layer of the batch."""
+        hit = self._tables.get(key)
+        if hit is not None:
+            return hit
+        arr, n = _runs_array(key)
+        host = torch.empty(3 * n + 1, dtype=torch.int32).pin_memory()
+        tv, tpb = ctypes.c_int32(), ctypes.c_int64()
+        _lib.check(self._lib.b200_kv_put_table_build(arr, n, self.block_size, host.data_ptr(), ctypes.byref(tv),
+                                                     ctypes.byref(tpb)), "kv put table")
+        with torch.cuda.device(self.device):
+            stream = self.comm_stream if self.comm_stream is not None else torch.cuda.current_stream(self.device)
+            with torch.cuda.stream(stream):
+                dev = host.to(self.device, non_blocking=True)
+        if len(self._tables) >= 16:
+            self._tables.pop(next(iter(self._tables)))
+        out = (dev, n, tv.value, tpb.value, host)   # host kept alive until the async copy is long done
+        self._tables[key] = out
+        return out
+
     def _put(self, first_buf: int, num_bufs: int, runs: Sequence[Tuple[int, int]]) -> None:
         if self.src_table is None or self.dst_table is None:
             raise RuntimeError("put() called on a rank that has no outgoing KV connection")
-        arr, n = _runs_array(runs)
-        if n == 0:
+        key = runs if isinstance(runs, tuple) else tuple(map(tuple, runs))
+        if len(key) == 0:
             return
         with torch.cuda.device(self.device):
-            st = self._lib.b200_kv_put_blocks(self.src_table.data_ptr() + 8 * first_buf,
-                                              self.dst_table.data_ptr() + 8 * first_buf, num_bufs, arr, n,
-                                              self.block_size, self.max_ctas, self._stream())
+            if len(key) > self.PARAM_TABLE_RUNS:
+                dev, n, tv, tpb, _ = self._device_table(key)
+                st = self._lib.b200_kv_put_blocks_table(self.src_table.data_ptr() + 8 * first_buf,
+                                                        self.dst_table.data_ptr() + 8 * first_buf, num_bufs,
+                                                        dev.data_ptr(), n, tv, tpb, self.block_size, self.max_ctas,
+                                                        self._stream())
+            else:
+                arr, n = _runs_array(key)
+                st = self._lib.b200_kv_put_blocks(self.src_table.data_ptr() + 8 * first_buf,
+                                                  self.dst_table.data_ptr() + 8 * first_buf, num_bufs, arr, n,
+                                                  self.block_size, self.max_ctas, self._stream())
         _lib.check(st, "kv put")
 
     # ---- reference surface -------------------------------------------------------------
     def put(self, sem_id: int, layer_id: int, block_start: int, num_blocks: int) -> None:
-        """K and V blocks [block_start, block_start+num_blocks) of one layer (comm_utils.py:132-147)."""
+        """K and V blocks [block_start, block_start+num_blocks) of one layer (comm_utils.py:132-147).
+        Called once per coalesced run per semaphore per layer by the backends, i.e. tens of thousands of times
+        per prefill batch: the deferred path is an append; everything else happens once per layer in flush()."""
+        if layer_id != self._pending_layer or not self.defer_puts:
+            self._put_slow(sem_id, layer_id, block_start, num_blocks)
+        elif num_blocks > 0 and 0 <= sem_id < MAX_SLOT_IDS:
+            self._pending_runs.append((block_start, num_blocks))
+        else:
+            self._check_sem(sem_id)
+
+    def _put_slow(self, sem_id: int, layer_id: int, block_start: int, num_blocks: int) -> None:
         self._check_sem(sem_id)
         if not 0 <= layer_id < self.num_layers:
             raise ValueError(f"layer_id {layer_id} out of range [0, {self.num_layers})")
@@ -161,12 +203,11 @@ class KVCacheCommunicator:
             return
         if not self.defer_puts:
             self._order_after_current()
-            self._put(2 * layer_id, 2, [(block_start, num_blocks)])
+            self._put(2 * layer_id, 2, ((int(block_start), int(num_blocks)),))
             return
-        if layer_id != self._pending_layer:
-            self.flush()
-            self._pending_layer = layer_id
-        self._pending_runs.append((int(block_start), int(num_blocks)))
+        self.flush()
+        self._pending_layer = layer_id
+        self._pending_runs.append((block_start, num_blocks))
 
     def signal_and_flush(self, sem_id: int) -> None:
         self._check_sem(sem_id)
@@ -308,6 +349,7 @@ class KVCacheCommManager:
                                                 local_flags, self.rank, self.corr_worker_rank, max_ctas=max_ctas,
                                                 defer_puts=defer_puts,
                                                 comm_stream=torch.cuda.Stream(device) if use_comm_stream else None)
+        self.put = self.kvcache_comm.put  # the hot call of the prefill loop: one Python frame, not two
 
     def flush(self) -> None:
         """Launch any deferred puts now (optional: call after a layer's put loop for the earliest start)."""
@@ -323,6 +365,7 @@ class KVCacheCommManager:
         self._opened = []
         self._keepalive = []
         self.kvcache_comm = None
+        self.__dict__.pop("put", None)
 
     def wait(self, sem_id: int) -> None:
         self.kvcache_comm.wait(sem_id)
@@ -331,7 +374,7 @@ class KVCacheCommManager:
         self.kvcache_comm.signal_and_flush(sem_id)
 
     def put(self, sem_id: int, layer_id: int, block_start: int, num_blocks: int) -> None:
-        self.kvcache_comm.put(sem_id, layer_id, block_start, num_blocks)
+        self.kvcache_comm.put(sem_id, layer_id, block_start, num_blocks)  # setup_comm rebinds self.put to skip this frame
 
     def put_runs(self, sem_id: int, layer_id: int, runs: Sequence[Tuple[int, int]]) -> None:
         self.kvcache_comm.put_runs(sem_id, layer_id, runs)

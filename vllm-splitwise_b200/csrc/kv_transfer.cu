@@ -30,6 +30,39 @@ struct PutTable {
 };
 static_assert(sizeof(PutTable) <= 4000, "kernel parameter space");
 
+// CTAs take tiles round-robin; a tile lies inside one (buffer, run).  Each thread keeps up to 8 independent
+// 16-byte loads from local HBM in flight and then issues the stores to the peer mapping.
+__device__ __forceinline__ void put_tiles(const int* start, const int* len, const int* run_tile0, int num_runs,
+                                          int num_bufs, int tv, long long block_bytes, const long long* src_ptrs,
+                                          const long long* dst_ptrs) {
+  const long long tpb = run_tile0[num_runs];
+  const long long total = tpb * num_bufs;
+  for (long long tile = blockIdx.x; tile < total; tile += gridDim.x) {
+    const int buf = (int)(tile / tpb);
+    const int rt = (int)(tile - (long long)buf * tpb);
+    int lo = 0, hi = num_runs - 1;  // last run with run_tile0[r] <= rt
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (run_tile0[mid] <= rt) lo = mid; else hi = mid - 1;
+    }
+    const long long run_vecs = (long long)len[lo] * block_bytes / 16;
+    const long long v0 = (long long)(rt - run_tile0[lo]) * tv;
+    const long long v1 = min(run_vecs, v0 + tv);
+    const long long byte0 = (long long)start[lo] * block_bytes;
+    const uint4* src = reinterpret_cast<const uint4*>(src_ptrs[buf] + byte0);
+    uint4* dst = reinterpret_cast<uint4*>(dst_ptrs[buf] + byte0);
+    for (long long i = v0 + threadIdx.x; i < v1; i += 8 * kPutThreads) {
+      uint4 r[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (i + k * kPutThreads < v1) r[k] = ld_nc_v4(src + i + k * kPutThreads);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (i + k * kPutThreads < v1) st_na_v4(dst + i + k * kPutThreads, r[k]);
+    }
+  }
+}
+
 // Work = num_bufs x (sum of run lengths) blocks, cut into tiles of `tile_vecs` 16-byte vectors
 // (<= 32 KiB).  CTAs take tiles round-robin; a tile lies inside one (buffer, run).  Each thread keeps up
 // to 8 independent 16-byte loads from local HBM in flight and then issues the stores to the peer mapping.
@@ -60,32 +93,20 @@ __global__ void __launch_bounds__(kPutThreads) kv_put_blocks_kernel(const __grid
     if (threadIdx.x == kPutThreads - 1) run_tile0[t.num_runs] = base + incl;
     __syncthreads();
   }
-  const long long tpb = run_tile0[t.num_runs];
-  const long long total = tpb * t.num_bufs;
-  for (long long tile = blockIdx.x; tile < total; tile += gridDim.x) {
-    const int buf = (int)(tile / tpb);
-    const int rt = (int)(tile - (long long)buf * tpb);
-    int lo = 0, hi = t.num_runs - 1;  // last run with run_tile0[r] <= rt
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (run_tile0[mid] <= rt) lo = mid; else hi = mid - 1;
-    }
-    const long long run_vecs = (long long)t.len[lo] * t.block_bytes / 16;
-    const long long v0 = (long long)(rt - run_tile0[lo]) * tv;
-    const long long v1 = min(run_vecs, v0 + tv);
-    const long long byte0 = (long long)t.start[lo] * t.block_bytes;
-    const uint4* src = reinterpret_cast<const uint4*>(t.src_ptrs[buf] + byte0);
-    uint4* dst = reinterpret_cast<uint4*>(t.dst_ptrs[buf] + byte0);
-    for (long long i = v0 + threadIdx.x; i < v1; i += 8 * kPutThreads) {
-      uint4 r[8];
-#pragma unroll
-      for (int k = 0; k < 8; ++k)
-        if (i + k * kPutThreads < v1) r[k] = ld_nc_v4(src + i + k * kPutThreads);
-#pragma unroll
-      for (int k = 0; k < 8; ++k)
-        if (i + k * kPutThreads < v1) st_na_v4(dst + i + k * kPutThreads, r[k]);
-    }
-  }
+  put_tiles(t.start, t.len, run_tile0, t.num_runs, t.num_bufs, tv, t.block_bytes, t.src_ptrs, t.dst_ptrs);
+}
+
+// Same copy for run lists that do not fit the kernel-parameter table: starts, lengths and the exclusive tile
+// prefix live in DEVICE memory (built once per run list by b200_kv_put_table_build and reused for every
+// layer -- the backends put the same block list 2 x num_layers times); each CTA stages them in shared memory.
+// tab = [start[n] | len[n] | tile0[n + 1]] int32.
+__global__ void __launch_bounds__(kPutThreads) kv_put_blocks_table_kernel(
+    const int* __restrict__ tab, int num_runs, int num_bufs, int tile_vecs, long long block_bytes,
+    const long long* __restrict__ src_ptrs, const long long* __restrict__ dst_ptrs) {
+  extern __shared__ int s_tab[];
+  for (int i = threadIdx.x; i < 3 * num_runs + 1; i += blockDim.x) s_tab[i] = tab[i];
+  __syncthreads();
+  put_tiles(s_tab, s_tab + num_runs, s_tab + 2 * num_runs, num_runs, num_bufs, tile_vecs, block_bytes, src_ptrs, dst_ptrs);
 }
 
 __global__ void kv_signal_kernel(unsigned long long* flag, unsigned long long value) {
@@ -117,6 +138,14 @@ __global__ void kv_wait_kernel(const unsigned long long* flag, unsigned long lon
 }  // namespace b200
 
 using namespace b200;
+
+// Tile = the largest even split of one block that stays <= 32 KiB (a 40 KiB block -> two 20 KiB tiles, not
+// 32 + 8), so single-block runs of a fragmented block list load the CTAs evenly.
+static int put_tile_vecs(int64_t block_bytes) {
+  const long long block_vecs = block_bytes / 16;
+  const long long pieces = (block_vecs + kTileVecs - 1) / kTileVecs;
+  return (int)((block_vecs + pieces - 1) / pieces);
+}
 
 extern "C" {
 
@@ -185,8 +214,7 @@ B200_API int b200_kv_put_blocks(const int64_t* src_ptrs, const int64_t* dst_ptrs
   // Tile = the largest even split of one block that stays <= 32 KiB (a 40 KiB block -> two 20 KiB tiles, not
   // 32 + 8), so single-block runs of a fragmented block list load the CTAs evenly.
   const long long block_vecs = block_bytes / 16;
-  const long long pieces = (block_vecs + kTileVecs - 1) / kTileVecs;
-  const int tile_vecs = (int)((block_vecs + pieces - 1) / pieces);
+  const int tile_vecs = put_tile_vecs(block_bytes);
   for (int r0 = 0; r0 < num_runs; r0 += kMaxRuns) {
     PutTable t;
     t.num_runs = std::min(kMaxRuns, num_runs - r0);
@@ -209,6 +237,56 @@ B200_API int b200_kv_put_blocks(const int64_t* src_ptrs, const int64_t* dst_ptrs
     kv_put_blocks_kernel<<<grid, kPutThreads, 0, stream>>>(t);
     B200_LAUNCH_CHECK();
   }
+  return B200_OK;
+}
+
+B200_API int b200_kv_put_table_build(const int32_t* runs, int32_t num_runs, int64_t block_bytes, int32_t* table,
+                            int32_t* tile_vecs_out, int64_t* tiles_per_buf_out) {
+  if (!runs || !table || !tile_vecs_out || !tiles_per_buf_out || num_runs <= 0 || block_bytes <= 0) return B200_ERR_ARG;
+  if (block_bytes % 16 != 0) return B200_ERR_ALIGN;
+  const int tv = put_tile_vecs(block_bytes);
+  long long acc = 0;
+  for (int r = 0; r < num_runs; ++r) {
+    const int start = runs[2 * r], len = runs[2 * r + 1];
+    if (start < 0 || len < 0) return B200_ERR_ARG;
+    table[r] = start;
+    table[num_runs + r] = len;
+    table[2 * num_runs + r] = (int32_t)acc;
+    acc += ((long long)len * (block_bytes / 16) + tv - 1) / tv;
+    if (acc > INT32_MAX) return B200_ERR_ARG;
+  }
+  table[3 * num_runs] = (int32_t)acc;
+  *tile_vecs_out = tv;
+  *tiles_per_buf_out = acc;
+  return B200_OK;
+}
+
+B200_API int b200_kv_put_blocks_table(const int64_t* src_ptrs, const int64_t* dst_ptrs, int32_t num_bufs,
+                             const int32_t* dev_table, int32_t num_runs, int32_t tile_vecs, int64_t tiles_per_buf,
+                             int64_t block_bytes, int32_t max_ctas, b200_stream_t stream_) {
+  if (num_bufs == 0 || num_runs == 0 || tiles_per_buf == 0) return B200_OK;
+  if (!src_ptrs || !dst_ptrs || !dev_table || num_bufs < 0 || num_runs < 0 || tile_vecs <= 0 || tiles_per_buf < 0 ||
+      block_bytes <= 0)
+    return B200_ERR_ARG;
+  if (block_bytes % 16 != 0) return B200_ERR_ALIGN;
+  if (tiles_per_buf * num_bufs > INT32_MAX) return B200_ERR_ARG;
+  const size_t smem = ((size_t)3 * num_runs + 1) * sizeof(int);
+  if (smem > 200 * 1024) return B200_ERR_ARG;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (max_ctas <= 0) max_ctas = 2 * num_sms(-1);
+  static size_t attr_set[64] = {0};
+  int dev = 0;
+  B200_CUDA_TRY(cudaGetDevice(&dev));
+  dev &= 63;
+  if (smem > 48 * 1024 && attr_set[dev] < smem) {
+    B200_CUDA_TRY(cudaFuncSetAttribute(kv_put_blocks_table_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr_set[dev] = 200 * 1024;
+  }
+  const int grid = (int)std::min<long long>(tiles_per_buf * num_bufs, max_ctas);
+  kv_put_blocks_table_kernel<<<grid, kPutThreads, smem, stream>>>(
+      dev_table, num_runs, num_bufs, tile_vecs, block_bytes, reinterpret_cast<const long long*>(src_ptrs),
+      reinterpret_cast<const long long*>(dst_ptrs));
+  B200_LAUNCH_CHECK();
   return B200_OK;
 }
 
