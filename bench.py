@@ -87,9 +87,10 @@ def reshape_and_cache_bytes(w) -> int:
     return w["S"] * w["Hkv"] * w["D"] * 2 * (elt_bytes(w["dtype"]) + cache_elt) + w["S"] * 8
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per attention launch from the committed ncu --set full capture
-# of the same command (profiles/r02_c2_attn_ncu_full.txt); null for workloads without a capture.
-NCU_TRAFFIC = {"c2": 4_295_611_000 + 4_237_824}
+# dram__bytes_read.sum + dram__bytes_write.sum per attention launch from the committed ncu --set full captures
+# of the same commands (profiles/r03_{c2,c4,c3tp8}_attn_ncu_full.txt, mean of the two captured launches); null
+# for workloads without a capture.
+NCU_TRAFFIC = {"c2": 4_295_847_500 + 4_181_760, "c4": 2_148_911_000 + 4_078_976, "c3tp8": 537_709_952 + 3_330_560}
 
 
 def kernel_name(w) -> str:
