@@ -193,6 +193,57 @@ B200_API int b200_rotary_embedding_reshape_and_cache(
     void* value_cache, const int64_t* slot_mapping, int32_t block_size, int32_t x, int64_t num_blocks,
     int32_t src_dtype, int32_t cache_dtype, b200_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Prefix ("context") prefill attention over the paged cache.
+ * Replaces context_attention_fwd, the Triton kernels _fwd_kernel / _fwd_kernel_alibi
+ * (vllm/model_executor/layers/attention/ops/prefix_prefill.py:621-745, :10-199, :392-618); caller
+ * PagedAttentionImpl.forward_prefix (.../ops/paged_attn.py:113-138).
+ *
+ *   for sequence b with ctx = ctx_lens[b] cached tokens and L = seq_lens[b] - ctx new tokens at rows
+ *   start_loc[b] .. start_loc[b]+L-1 of query/key/value/out, and m < L:
+ *     out[m,h,:] = softmax_n( scale*q[m,h].k[n] + alibi[h]*(pos_n - (ctx+m)) ) . v[n]
+ *   over the cached tokens n < ctx (read through block_tables from key_cache / value_cache) and the new
+ *   tokens n <= m (read from key / value); kv head = h / (num_heads / num_kv_heads).
+ *
+ * query/out [num_tokens, num_heads, head_size], key/value [num_tokens, num_kv_heads, head_size] with
+ * token / head strides in elements (last dim dense); caches in the paged layouts of paged_attention
+ * (x = 8: 2-byte elements only, as the reference hard-codes, prefix_prefill.py:719); block_tables int32
+ * [batch, block_table_stride]; start_loc, seq_lens, ctx_lens int32 [batch]; dtype F16 / BF16;
+ * head_size 16/32/64/128 (prefix_prefill.py:639), block_size 8/16/32.  Rows m >= max_input_len are not
+ * computed (the reference's grid, :645).  Never allocates, never synchronises.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  void* out;
+  const void* query;
+  const void* key;
+  const void* value;
+  const void* key_cache;
+  const void* value_cache;
+  const int32_t* block_tables;
+  const int32_t* start_loc;
+  const int32_t* seq_lens;
+  const int32_t* ctx_lens;
+  const float* alibi_slopes; /* [num_heads] f32 or NULL */
+  float scale;
+  int32_t batch;
+  int32_t num_heads;
+  int32_t num_kv_heads;
+  int32_t head_size;
+  int32_t block_size;
+  int32_t max_input_len;
+  int32_t block_table_stride;
+  int64_t q_stride_t, q_stride_h;
+  int64_t k_stride_t, k_stride_h;
+  int64_t v_stride_t, v_stride_h;
+  int64_t o_stride_t, o_stride_h;
+  int64_t kc_block_stride, kc_head_stride;
+  int64_t vc_block_stride, vc_head_stride;
+  int32_t dtype;  /* b200_dtype_t: F16 / BF16 */
+  int32_t device; /* CUDA device ordinal, or -1 = current device */
+} b200_context_attn_args_t;
+
+B200_API int b200_context_attention_fwd(const b200_context_attn_args_t* args, b200_stream_t stream);
+
 /* Replaces cuda_utils (csrc/cuda_utils_kernels.cu:5-35). */
 B200_API int b200_get_device_attribute(int32_t attribute, int32_t device_id);
 B200_API int b200_get_max_shared_memory_per_block_device_attribute(int32_t device_id);

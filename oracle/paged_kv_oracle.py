@@ -345,3 +345,51 @@ def kv_put(src_caches: Sequence[torch.Tensor], dst_caches: Sequence[torch.Tensor
     for s, d in zip(src_caches, dst_caches):
         for start, n in runs:
             d[start:start + n].copy_(s[start:start + n])
+
+
+# --------------------------------------------------------------------------------------------
+# prefix ("context") prefill attention  
+# --------------------------------------------------------------------------------------------
+def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: torch.Tensor,
+                          k_cache: torch.Tensor, v_cache: torch.Tensor, b_loc: torch.Tensor,
+                          b_start_loc: torch.Tensor, b_seq_len: torch.Tensor, b_ctx_len: torch.Tensor,
+                          max_input_len: int, alibi_slopes: Optional[torch.Tensor] = None,
+                          compute_dtype: torch.dtype = torch.float32) -> None:
+    """Restates the reference Triton kernels _fwd_kernel / _fwd_kernel_alibi
+    (vllm/model_executor/layers/attention/ops/prefix_prefill.py:10-199, 392-618) as dense per-sequence
+    attention in `compute_dtype`: new token m of sequence b attends the ctx cached tokens (gathered through
+    b_loc from the paged layouts, :87-107) and the new tokens n <= m (:145-149); sm_scale = D**-0.5 (:641);
+    ALiBi bias slope*(key position - query position) (:503-508, 572-577).  The grid has ceil(max_input_len/BLOCK)
+    row blocks of BLOCK = 128 rows (:635,645): rows past the last started block are left untouched.
+    Pinned by tests/golden/prefix_prefill_ref.npz: outputs of the reference kernels themselves, executed in
+    the build container with Triton's interpreter (oracle/make_golden_prefix.py)."""
+    num_heads, D = q.shape[1], q.shape[2]
+    num_kv_heads = k.shape[1]
+    G = num_heads // num_kv_heads
+    bs = v_cache.shape[3]
+    scale = 1.0 / (D ** 0.5)
+    for b in range(b_seq_len.shape[0]):
+        ctx = int(b_ctx_len[b])
+        L = min(int(b_seq_len[b]) - ctx, (int(max_input_len) + 127) // 128 * 128)
+        if L <= 0:
+            continue
+        s0 = int(b_start_loc[b])
+        nblk = (ctx + bs - 1) // bs
+        blocks = b_loc[b, :nblk].long()
+        # K cache [NB, Hkv, D/x, bs, x] -> [ctx, Hkv, D];  V cache [NB, Hkv, D, bs] -> [ctx, Hkv, D]
+        kc = k_cache[blocks].permute(0, 3, 1, 2, 4).reshape(nblk * bs, num_kv_heads, D)[:ctx]
+        vc = v_cache[blocks].permute(0, 3, 1, 2).reshape(nblk * bs, num_kv_heads, D)[:ctx]
+        keys = torch.cat([kc, k[s0:s0 + L]], 0).to(compute_dtype)      # [ctx+L, Hkv, D]
+        vals = torch.cat([vc, v[s0:s0 + L]], 0).to(compute_dtype)
+        qq = q[s0:s0 + L].to(compute_dtype)                           # [L, H, D]
+        keys = keys.repeat_interleave(G, dim=1)
+        vals = vals.repeat_interleave(G, dim=1)
+        logits = torch.einsum("mhd,nhd->hmn", qq, keys) * scale       # [H, L, ctx+L]
+        qpos = ctx + torch.arange(L)
+        kpos = torch.arange(ctx + L)
+        if alibi_slopes is not None:
+            bias = (kpos[None, :] - qpos[:, None]).to(compute_dtype)
+            logits = logits + alibi_slopes.to(compute_dtype)[:, None, None] * bias[None]
+        logits = logits.masked_fill((kpos[None, :] > qpos[:, None])[None], float("-inf"))
+        probs = torch.softmax(logits, dim=-1)
+        o[s0:s0 + L] = torch.einsum("hmn,nhd->mhd", probs, vals).to(o.dtype)

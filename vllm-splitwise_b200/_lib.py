@@ -54,6 +54,19 @@ class PagedAttnArgs(Structure):
     ]
 
 
+class ContextAttnArgs(Structure):
+    """Mirror of b200_context_attn_args_t (field order and types must match the header)."""
+    _fields_ = ([(n, c_void_p) for n in ("out", "query", "key", "value", "key_cache", "value_cache", "block_tables",
+                                         "start_loc", "seq_lens", "ctx_lens", "alibi_slopes")]
+                + [("scale", c_float)]
+                + [(n, c_int32) for n in ("batch", "num_heads", "num_kv_heads", "head_size", "block_size",
+                                          "max_input_len", "block_table_stride")]
+                + [(n, c_int64) for n in ("q_stride_t", "q_stride_h", "k_stride_t", "k_stride_h", "v_stride_t",
+                                          "v_stride_h", "o_stride_t", "o_stride_h", "kc_block_stride",
+                                          "kc_head_stride", "vc_block_stride", "vc_head_stride")]
+                + [("dtype", c_int32), ("device", c_int32)])
+
+
 # name -> (restype, argtypes); every symbol include/b200_kv.h declares
 SIGNATURES = {
     "b200_kv_strerror": (c_char_p, [c_int32]),
@@ -63,6 +76,7 @@ SIGNATURES = {
     "b200_paged_attention_v1": (c_int32, [POINTER(PagedAttnArgs), c_void_p]),
     "b200_paged_attention_v2": (c_int32, [POINTER(PagedAttnArgs), c_void_p]),
     "b200_paged_attention_workspace_bytes": (c_int64, [POINTER(PagedAttnArgs)]),
+    "b200_context_attention_fwd": (c_int32, [POINTER(ContextAttnArgs), c_void_p]),
     "b200_reshape_and_cache": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int32,
                                          c_int32, c_int32, c_int32, c_int32, c_int64, c_int64,
                                          c_int64, c_int32, c_int32, c_void_p]),

@@ -63,3 +63,17 @@ class PagedAttentionImpl:
                                    input_metadata.context_lens, block_size, max_context_len,
                                    alibi_slopes, input_metadata.kv_cache_dtype)
         return output
+
+    @staticmethod
+    def forward_prefix(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor,
+                       value_cache: torch.Tensor, input_metadata,
+                       alibi_slopes: Optional[torch.Tensor]) -> torch.Tensor:
+        """reference paged_attn.py:113-138; `input_metadata` needs block_tables, start_loc, prompt_lens,
+        context_lens and max_seq_len."""
+        from .prefix_prefill import context_attention_fwd
+        output = torch.empty_like(query)
+        context_attention_fwd(query, key, value, output, key_cache, value_cache,
+                              input_metadata.block_tables,  # [BS, max_block_per_request]
+                              input_metadata.start_loc, input_metadata.prompt_lens,
+                              input_metadata.context_lens, input_metadata.max_seq_len, alibi_slopes)
+        return output
