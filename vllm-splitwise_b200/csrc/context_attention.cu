@@ -1,6 +1,9 @@
 // Host side of b200_context_attention_fwd: argument checks and dispatch.
 // Replaces the host function context_attention_fwd of the reference
 // (vllm/model_executor/layers/attention/ops/prefix_prefill.py:621-745).
+#include <stdlib.h>
+#include <string.h>
+
 #include "context_attention.cuh"
 
 extern "C" int b200_context_attention_fwd(const b200_context_attn_args_t* a, b200_stream_t stream) {
@@ -39,7 +42,12 @@ extern "C" int b200_context_attention_fwd(const b200_context_attn_args_t* a, b20
   DeviceGuard guard;
   B200_CUDA_TRY(guard.set(a->device));
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // development knob: B200_CTX_ATTN=mma forces the warp-level MMA kernel for head size 128 too
+  static const bool tc = [] {
+    const char* e = getenv("B200_CTX_ATTN");
+    return !(e && strcmp(e, "mma") == 0);
+  }();
   if (a->dtype == B200_F16)
-    return launch_ctx_attn_dtype<__half>(p, a->head_size, a->block_size, a->batch, a->max_input_len, st);
-  return launch_ctx_attn_dtype<__nv_bfloat16>(p, a->head_size, a->block_size, a->batch, a->max_input_len, st);
+    return launch_ctx_attn_dtype<__half>(p, a->head_size, a->block_size, a->batch, a->max_input_len, tc, st);
+  return launch_ctx_attn_dtype<__nv_bfloat16>(p, a->head_size, a->block_size, a->batch, a->max_input_len, tc, st);
 }

@@ -337,6 +337,6 @@ int launch_ctx_attn(const CtxAttnParams& p, int batch, int max_input_len, cudaSt
 
 template <typename MT>
 int launch_ctx_attn_dtype(const CtxAttnParams& p, int head_size, int block_size, int batch, int max_input_len,
-                          cudaStream_t stream);
+                          bool tensor_core_gen5, cudaStream_t stream);
 
 }  // namespace b200

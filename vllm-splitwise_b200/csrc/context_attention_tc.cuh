@@ -1,0 +1,451 @@
+// Prefix ("context") prefill attention on the 5th-generation tensor cores (tcgen05 + TMEM), head size 128.
+//
+// Same contract as context_attn_kernel (context_attention.cuh); this is the GEMM-shaped version:
+//   S = Q.K^T   : tcgen05.mma M=128 (query rows) x N=128 (KV tokens) x K=16, both operands from shared memory,
+//                 fp32 accumulator in TMEM (two S buffers, so Q.K^T of tile i+1 runs under the softmax of tile i)
+//   P           : the softmax warps read S from TMEM (one thread = one query row: max / sum need no shuffles),
+//                 and write P in the element type back to TMEM over the S columns they have consumed
+//   O_i = P.V   : tcgen05.mma with A = P from TMEM, B = V from shared memory, fresh accumulator per tile (two
+//                 buffers); the row owner folds it into its register accumulator  O = O*alpha + O_i
+//                 (no TMEM read-modify-write when the running max moves).
+// Warp roles (7 warps): 0-3 softmax/epilogue (TMEM lanes 32w..32w+31), 4 TMEM allocator + the single MMA-issuing
+// thread, 5 K loader (+ the Q tile), 6-7 V loaders.  Loaders move 16-byte granules with cp.async straight
+// into the no-swizzle canonical UMMA layouts -- the paged layouts are already made of those granules:
+//   Q, K (cached or new): [d-octet j][row]   K-major   core matrix = 8 rows x 16 B contiguous, SBO 128 B, LBO rows*16 B
+//   V cached  [D][bs]  -> [token-octet][d]   K-major B operand of P.V (n = d, k = token)
+//   V new   [token][D] -> [d-octet][token]   MN-major B operand
+// Pipelines: k_full/k_empty and v_full/v_empty (2 stages each, loaders <-> MMA via tcgen05.commit), s_full, p_full,
+// o_full, o_empty (MMA <-> softmax).  tcgen05.mma's execute in issue order, which is what frees an S buffer
+// (P.V of tile i is issued before Q.K^T of tile i+2).
+#pragma once
+
+#include <type_traits>
+
+#include "context_attention.cuh"
+
+namespace b200 {
+namespace tc {
+
+constexpr int kD = 128;        // head size of this kernel
+constexpr int kBM = 128;       // query rows per CTA = UMMA M
+constexpr int kBN = 128;       // KV tokens per tile = UMMA N of Q.K^T
+constexpr int kStages = 2;
+constexpr int kTileBytes = kBN * kD * 2;  // 32 KiB: one Q, K or V tile
+constexpr int kSoftmaxThreads = 128, kKLoaderThreads = 32, kVLoaderThreads = 64;
+constexpr int kThreads = kSoftmaxThreads + 32 + kKLoaderThreads + kVLoaderThreads;  // 256: 8 warps, so that the row-owning threads may use up to 255 registers
+constexpr int kSmemBytes = (1 + 2 * kStages) * kTileBytes + 256;
+
+// ---- tcgen05 wrappers --------------------------------------------------------------------------
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_alloc_512(uint32_t* smem_slot) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(smem_slot)) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_512(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(taddr) : "memory");
+}
+// arrives on the mbarrier once every tcgen05.mma issued so far by this thread has completed
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// D[tmem] (+)= A[smem] . B[smem]
+__device__ __forceinline__ void mma_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// D[tmem] (+)= A[tmem] . B[smem]
+__device__ __forceinline__ void mma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// shared-memory matrix descriptor, no swizzle (layout type 0), sm_100 descriptor version 1
+// (bit layout: cute/arch/mma_sm100_desc.hpp SmemDescriptor): start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46)
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return (uint64_t)((saddr >> 4) & 0x3fffu) | ((uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16) |
+         ((uint64_t)((sbo_bytes >> 4) & 0x3fffu) << 32) | (1ull << 46);
+}
+// instruction descriptor for kind::f16 (InstrDescriptor in the same header): fp32 accumulate, M=128
+template <typename MT>
+__device__ __forceinline__ constexpr uint32_t instr_desc(int n, bool b_mn_major) {
+  const uint32_t fmt = sizeof(MT) == 2 && std::is_same<MT, __nv_bfloat16>::value ? 1u : 0u;  // 0 = f16, 1 = bf16
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((b_mn_major ? 1u : 0u) << 16) | ((uint32_t)(n >> 3) << 17) |
+         ((uint32_t)(kBM >> 4) << 24);
+}
+
+// 32 consecutive fp32 columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+      "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+struct Barriers {
+  uint64_t q_full;
+  uint64_t k_full[kStages], k_empty[kStages], v_full[kStages], v_empty[kStages];
+  uint64_t s_full[2], p_full[2], o_full;
+  uint32_t tmem_base;
+};
+
+// granule index -> (row, d-octet) for sources laid out [row][D]: a warp covers 8 rows x 4 octets, i.e. 64-byte
+// global segments and four conflict-free 128-byte shared-memory lines
+__device__ __forceinline__ void row_major_granule(int e, int& row, int& j) {
+  row = ((e >> 5) & 15) * 8 + (e & 7);
+  j = (e >> 9) * 4 + ((e >> 3) & 3);
+}
+
+template <typename MT, int BS>
+__global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxAttnParams p) {
+  constexpr int G = kD / 8;    // 16-byte granules per row
+  constexpr int HG = BS / 8;   // token octets per cache block
+  constexpr int TILE_UNITS = kBN * G;
+  extern __shared__ __align__(1024) uint8_t tc_smem[];
+  uint4* q_s = reinterpret_cast<uint4*>(tc_smem);
+  uint4* k_s = q_s + TILE_UNITS;
+  uint4* v_s = k_s + kStages * TILE_UNITS;
+  Barriers* bar = reinterpret_cast<Barriers*>(v_s + kStages * TILE_UNITS);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int mblk = gridDim.x - 1 - blockIdx.x;
+  const int head = blockIdx.y, seq = blockIdx.z;
+  const int ctx_len = p.b_ctx_len[seq];
+  const int q_len = p.b_seq_len[seq] - ctx_len;
+  const int m0 = mblk * kBM;
+  if (m0 >= q_len) return;
+  const int64_t start = p.b_start_loc[seq];
+  const int kvh = head / (p.num_heads / p.num_kv_heads);
+  const int n_ctx_tiles = (ctx_len + kBN - 1) / kBN;
+  const int new_end = min(q_len, m0 + kBM);
+  const int n_tiles = n_ctx_tiles + (new_end + kBN - 1) / kBN;
+
+  if (tid == 0) {
+    mbar_init(&bar->q_full, kKLoaderThreads);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&bar->k_full[s], kKLoaderThreads);
+      mbar_init(&bar->v_full[s], kVLoaderThreads);
+      mbar_init(&bar->k_empty[s], 1);
+      mbar_init(&bar->v_empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&bar->s_full[s], 1);
+      mbar_init(&bar->p_full[s], kSoftmaxThreads);
+    }
+    mbar_init(&bar->o_full, 1);
+    mbar_fence_init();
+  }
+  if (warp == 4) tmem_alloc_512(&bar->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bar->tmem_base;
+
+  if (warp < 4) {
+    // ================= softmax + epilogue: thread = query row =================
+    const uint32_t lane_off = (uint32_t)(32 * warp) << 16;
+    const int qrow = m0 + tid;
+    const bool has_alibi = p.alibi_slopes != nullptr;
+    const float slope2 = has_alibi ? p.alibi_slopes[head] * 1.4426950408889634f : 0.f;
+    const uint32_t o_addr = tmem + lane_off + 256;
+    // m_used: the reference point of P and O.  It follows the running maximum lazily: it moves only when the
+    // maximum has grown by more than 2^8, so that the O accumulator in TMEM is rescaled rarely (exact either way:
+    // numerator and denominator carry the same reference point).
+    float m_used = -INFINITY, l_run = 0.f;
+
+    for (int i = 0; i < n_tiles; ++i) {
+      const int st = i & 1, u = i >> 1;
+      const bool is_ctx = i < n_ctx_tiles;
+      const int n0 = (is_ctx ? i : i - n_ctx_tiles) * kBN;
+      // columns [0, limit) of this tile are visible to this row
+      const int limit = is_ctx ? ctx_len - n0 : qrow - n0 + 1;
+      // key position minus query position of column 0 (ALiBi)
+      const float bias0 = slope2 * (float)(is_ctx ? n0 - ctx_len - qrow : n0 - qrow);
+      mbar_wait(&bar->s_full[st], u & 1);
+      tc_fence_after();
+      const uint32_t s_addr = tmem + lane_off + st * 128;
+      float s[kBN];
+#pragma unroll
+      for (int c4 = 0; c4 < 4; ++c4) tmem_ld32(s_addr + 32 * c4, reinterpret_cast<uint32_t*>(&s[32 * c4]));
+      tmem_ld_wait();
+      float mx = -INFINITY;
+#pragma unroll
+      for (int col = 0; col < kBN; ++col) {
+        float v = fmaf(s[col], p.scale_log2, has_alibi ? fmaf(slope2, (float)col, bias0) : 0.f);
+        v = col < limit ? v : -INFINITY;
+        s[col] = v;
+        mx = fmaxf(mx, v);
+      }
+      if (i > 0) {  // P_{i-1}.V_{i-1} has landed in O (one completion per tile: phase = tile index)
+        mbar_wait(&bar->o_full, (i - 1) & 1);
+        tc_fence_after();
+      }
+      if (__any_sync(0xffffffffu, mx > m_used + 8.f)) {
+        const float m_new = fmaxf(m_used, mx);
+        const float alpha = ex2_approx(m_used - m_new);
+        if (i > 0) {
+#pragma unroll
+          for (int c4 = 0; c4 < 4; ++c4) {
+            uint32_t r[32];
+            tmem_ld32(o_addr + 32 * c4, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int k = 0; k < 32; ++k) r[k] = __float_as_uint(__uint_as_float(r[k]) * alpha);
+            tmem_st16(o_addr + 32 * c4, r);
+            tmem_st16(o_addr + 32 * c4 + 16, r + 16);
+          }
+        }
+        l_run *= alpha;
+        m_used = m_new;
+      }
+      float sum = 0.f;
+#pragma unroll
+      for (int c4 = 0; c4 < 4; ++c4) {
+        uint32_t pk[16];
+#pragma unroll
+        for (int k = 0; k < 32; k += 2) {
+          const float e0 = ex2_approx(s[32 * c4 + k] - m_used);   // masked columns are -inf -> 0
+          const float e1 = ex2_approx(s[32 * c4 + k + 1] - m_used);
+          sum += e0 + e1;
+          pk[k >> 1] = pack2<MT>(e0, e1);
+        }
+        tmem_st16(s_addr + 16 * c4, pk);  // P over the S columns (all of S is in registers by now)
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(&bar->p_full[st]);
+      l_run += sum;
+    }
+
+    mbar_wait(&bar->o_full, (n_tiles - 1) & 1);
+    tc_fence_after();
+    const float inv = 1.f / l_run;
+    MT* orow = static_cast<MT*>(p.o) + (start + qrow) * p.o_ts + (int64_t)head * p.o_hs;
+#pragma unroll
+    for (int c4 = 0; c4 < 4; ++c4) {
+      uint32_t r[32];
+      tmem_ld32(o_addr + 32 * c4, r);
+      tmem_ld_wait();
+      if (qrow < q_len) {
+#pragma unroll
+        for (int k = 0; k < 32; k += 8) {
+          uint4 w;
+          w.x = pack2<MT>(__uint_as_float(r[k]) * inv, __uint_as_float(r[k + 1]) * inv);
+          w.y = pack2<MT>(__uint_as_float(r[k + 2]) * inv, __uint_as_float(r[k + 3]) * inv);
+          w.z = pack2<MT>(__uint_as_float(r[k + 4]) * inv, __uint_as_float(r[k + 5]) * inv);
+          w.w = pack2<MT>(__uint_as_float(r[k + 6]) * inv, __uint_as_float(r[k + 7]) * inv);
+          *reinterpret_cast<uint4*>(orow + 32 * c4 + k) = w;
+        }
+      }
+    }
+  } else if (warp == 4) {
+    // ================= the MMA-issuing thread =================
+    if (lane == 0) {
+      const uint32_t idesc_k = instr_desc<MT>(kBN, false);   // Q.K^T and P.V over cached V: K-major B
+      const uint32_t idesc_mn = instr_desc<MT>(kD, true);    // P.V over new V: MN-major B
+      const uint32_t q_addr = smem_u32(q_s);
+      mbar_wait(&bar->q_full, 0);
+      for (int i = 0; i <= n_tiles; ++i) {
+        if (i < n_tiles) {  // S_i = Q.K_i^T
+          const int st = i & 1;
+          mbar_wait(&bar->k_full[st], (i >> 1) & 1);
+          tc_fence_after();
+          const uint32_t k_addr = smem_u32(k_s + st * TILE_UNITS);
+#pragma unroll
+          for (int ks = 0; ks < kD / 16; ++ks)
+            mma_ss(tmem + st * 128, smem_desc(q_addr + ks * 2 * kBM * 16, kBM * 16, 128),
+                   smem_desc(k_addr + ks * 2 * kBN * 16, kBN * 16, 128), idesc_k, ks > 0);
+          tc_commit(&bar->k_empty[st]);
+          tc_commit(&bar->s_full[st]);
+        }
+        if (i >= 1) {  // O_j = P_j.V_j
+          const int j = i - 1, st = j & 1, u = j >> 1;
+          mbar_wait(&bar->v_full[st], u & 1);
+          mbar_wait(&bar->p_full[st], u & 1);  // implies the softmax threads have seen O_{j-1} (and rescaled it)
+          tc_fence_after();
+          const uint32_t v_addr = smem_u32(v_s + st * TILE_UNITS);
+          const bool is_ctx = j < n_ctx_tiles;
+#pragma unroll
+          for (int kt = 0; kt < kBN / 16; ++kt) {
+            // cached V: [token-octet][d] granules (K-major, LBO = next token octet, SBO = next 8 d rows);
+            // new V:    [d-octet][token] granules (MN-major, LBO = next 8 tokens, SBO = next d octet)
+            const uint64_t b = is_ctx ? smem_desc(v_addr + kt * 2 * kD * 16, kD * 16, 128)
+                                      : smem_desc(v_addr + kt * 16 * 16, 128, kBN * 16);
+            mma_ts(tmem + 256, tmem + st * 128 + kt * 8, b, is_ctx ? idesc_k : idesc_mn, (j | kt) > 0);
+          }
+          tc_commit(&bar->v_empty[st]);
+          tc_commit(&bar->o_full);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 5) {
+    // ================= K (and Q) loader =================
+    const int lt = tid - 5 * 32;
+    const MT* kc = static_cast<const MT*>(p.k_cache) + (int64_t)kvh * p.kc_hs;
+    const MT* kn = static_cast<const MT*>(p.k) + start * p.k_ts + (int64_t)kvh * p.k_hs;
+    const int32_t* bt = p.b_loc + (int64_t)seq * p.b_loc_stride;
+    auto issue_k = [&](int ti, int st) {
+      uint4* Ks = k_s + st * TILE_UNITS;
+      if (ti < n_ctx_tiles) {
+        const int n0 = ti * kBN;
+        // lane c holds the physical number of the tile's c-th cache block; the granule loop gets it by shuffle
+        // (all lanes of an iteration work on the same block), so no load sits in front of a cp.async
+        int my_bn = 0;
+        if (lane < kBN / BS && n0 + lane * BS < ctx_len) my_bn = bt[n0 / BS + lane];
+#pragma unroll 8
+        for (int e = lt; e < TILE_UNITS; e += kKLoaderThreads) {
+          const int tt = e % BS, j = (e / BS) % G, c = e / (BS * G);
+          const int tok = c * BS + tt;
+          const int64_t bn = __shfl_sync(0xffffffffu, my_bn, c);
+          if (n0 + tok < ctx_len) cp_async16(&Ks[j * kBN + tok], kc + bn * p.kc_bs + (j * BS + tt) * 8);
+        }
+      } else {
+        const int n0 = (ti - n_ctx_tiles) * kBN;
+#pragma unroll 8
+        for (int e = lt; e < TILE_UNITS; e += kKLoaderThreads) {
+          int tok, j;
+          row_major_granule(e, tok, j);
+          if (n0 + tok < q_len) cp_async16(&Ks[j * kBN + tok], kn + (int64_t)(n0 + tok) * p.k_ts + j * 8);
+        }
+      }
+    };
+    {
+      const MT* qb = static_cast<const MT*>(p.q) + (start + m0) * p.q_ts + (int64_t)head * p.q_hs;
+#pragma unroll 8
+      for (int e = lt; e < TILE_UNITS; e += kKLoaderThreads) {
+        int row, j;
+        row_major_granule(e, row, j);
+        if (m0 + row < q_len) cp_async16(&q_s[j * kBM + row], qb + (int64_t)row * p.q_ts + j * 8);
+        else q_s[j * kBM + row] = make_uint4(0u, 0u, 0u, 0u);
+      }
+      cp_async_commit();
+    }
+    issue_k(0, 0);
+    cp_async_commit();
+    cp_async_wait<1>();
+    fence_proxy_async_smem();
+    mbar_arrive(&bar->q_full);
+    if (n_tiles > 1) {
+      issue_k(1, 1);
+      cp_async_commit();
+    }
+    for (int i = 0; i < n_tiles; ++i) {
+      if (i + 1 < n_tiles) cp_async_wait<1>(); else cp_async_wait<0>();
+      fence_proxy_async_smem();
+      mbar_arrive(&bar->k_full[i & 1]);
+      if (i + 2 < n_tiles) {
+        mbar_wait(&bar->k_empty[i & 1], (i >> 1) & 1);
+        issue_k(i + 2, i & 1);
+        cp_async_commit();
+      }
+    }
+  } else {
+    // ================= V loaders =================
+    const int lt = tid - 6 * 32;
+    const MT* vc = static_cast<const MT*>(p.v_cache) + (int64_t)kvh * p.vc_hs;
+    const MT* vn = static_cast<const MT*>(p.v) + start * p.v_ts + (int64_t)kvh * p.v_hs;
+    const int32_t* bt = p.b_loc + (int64_t)seq * p.b_loc_stride;
+    auto issue_v = [&](int ti, int st) {
+      uint4* Vs = v_s + st * TILE_UNITS;
+      if (ti < n_ctx_tiles) {
+        const int n0 = ti * kBN;
+        int my_bn = 0;
+        if (lane < kBN / BS && n0 + lane * BS < ctx_len) my_bn = bt[n0 / BS + lane];
+#pragma unroll 8
+        for (int e = lt; e < TILE_UNITS; e += kVLoaderThreads) {
+          const int hh = e % HG, d = (e / HG) % kD, c = e / (HG * kD);
+          const int tg = c * HG + hh;
+          uint4* dst = &Vs[tg * kD + d];
+          const int64_t bn = __shfl_sync(0xffffffffu, my_bn, c);
+          if (n0 + tg * 8 < ctx_len) {
+            cp_async16(dst, vc + bn * p.vc_bs + d * BS + hh * 8);
+          } else {
+            *dst = make_uint4(0u, 0u, 0u, 0u);
+          }
+        }
+      } else {
+        const int n0 = (ti - n_ctx_tiles) * kBN;
+#pragma unroll 8
+        for (int e = lt; e < TILE_UNITS; e += kVLoaderThreads) {
+          int tok, j;
+          row_major_granule(e, tok, j);
+          uint4* dst = &Vs[j * kBN + tok];
+          if (n0 + tok < q_len) cp_async16(dst, vn + (int64_t)(n0 + tok) * p.v_ts + j * 8);
+          else *dst = make_uint4(0u, 0u, 0u, 0u);
+        }
+      }
+    };
+    issue_v(0, 0);
+    cp_async_commit();
+    if (n_tiles > 1) {
+      issue_v(1, 1);
+      cp_async_commit();
+    }
+    for (int i = 0; i < n_tiles; ++i) {
+      if (i + 1 < n_tiles) cp_async_wait<1>(); else cp_async_wait<0>();
+      if (i < n_ctx_tiles && i * kBN + kBN > ctx_len && ((ctx_len - i * kBN) & 7)) {
+        // the token octet that straddles ctx_len: slots past the end are stale cache memory (may be NaN / Inf)
+        asm volatile("bar.sync 1, %0;" ::"n"(kVLoaderThreads) : "memory");  // every V loader's copies of tile i landed
+        const int tgb = (ctx_len - i * kBN) >> 3, rem = (ctx_len - i * kBN) & 7;
+        for (int d = lt; d < kD; d += kVLoaderThreads) {
+          MT* gp = reinterpret_cast<MT*>(&v_s[(i & 1) * TILE_UNITS + tgb * kD + d]);
+          for (int x = rem; x < 8; ++x) gp[x] = MT(0.f);
+        }
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(&bar->v_full[i & 1]);
+      if (i + 2 < n_tiles) {
+        mbar_wait(&bar->v_empty[i & 1], (i >> 1) & 1);
+        issue_v(i + 2, i & 1);
+        cp_async_commit();
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 4) tmem_dealloc_512(tmem);
+}
+
+template <typename MT, int BS>
+int launch_ctx_attn_tc(const CtxAttnParams& p, int batch, int max_input_len, cudaStream_t stream) {
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  B200_CUDA_TRY(cudaGetDevice(&dev));
+  dev &= 63;
+  if (!attr_set[dev]) {
+    B200_CUDA_TRY(cudaFuncSetAttribute(context_attn_tc_kernel<MT, BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    attr_set[dev] = true;
+  }
+  dim3 grid((max_input_len + kBM - 1) / kBM, p.num_heads, batch);
+  context_attn_tc_kernel<MT, BS><<<grid, kThreads, kSmemBytes, stream>>>(p);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+}  // namespace tc
+}  // namespace b200
