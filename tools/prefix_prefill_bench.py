@@ -83,9 +83,18 @@ def run(name, B, H, Hkv, D, bs, L, ctx, dtype, iters=20):
                       "max_abs_diff_vs_sdpa": err}), flush=True)
 
 
+CASES = [
+    ("llama7b_chunk2k_ctx2k_f16", 8, 32, 32, 128, 16, 2048, 2048, torch.float16),
+    ("llama7b_prefill4k_noctx_f16", 4, 32, 32, 128, 16, 4096, 0, torch.float16),
+    ("llama70b_tp8_chunk1k_ctx3k_bf16", 16, 8, 1, 128, 16, 1024, 3072, torch.bfloat16),
+    ("mistral_gqa4_chunk512_ctx7680_bf16", 8, 32, 8, 128, 16, 512, 7680, torch.bfloat16),
+    ("ref_test_shape_f16", 10, 64, 8, 128, 32, 512, 512, torch.float16),
+    ("llama7b_d64_chunk2k_ctx2k_f16", 8, 32, 32, 64, 16, 2048, 2048, torch.float16),
+]
+
 if __name__ == "__main__":
-    run("llama7b_chunk2k_ctx2k_f16", 8, 32, 32, 128, 16, 2048, 2048, torch.float16)
-    run("llama7b_prefill4k_noctx_f16", 4, 32, 32, 128, 16, 4096, 0, torch.float16)
-    run("llama70b_tp8_chunk1k_ctx3k_bf16", 16, 8, 1, 128, 16, 1024, 3072, torch.bfloat16)
-    run("mistral_gqa4_chunk512_ctx7680_bf16", 8, 32, 8, 128, 16, 512, 7680, torch.bfloat16)
-    run("ref_test_shape_f16", 10, 64, 8, 128, 32, 512, 512, torch.float16)
+    only = sys.argv[1] if len(sys.argv) > 1 else None      # run one case (for ncu)
+    iters = int(sys.argv[2]) if len(sys.argv) > 2 else 20
+    for c in CASES:
+        if only is None or c[0] == only:
+            run(*c, iters=iters)

@@ -118,6 +118,85 @@ __device__ __forceinline__ void row_major_granule(int e, int& row, int& j) {
   j = (e >> 9) * 4 + ((e >> 3) & 3);
 }
 
+// ---- loaders: 16-byte granules, global -> canonical UMMA layouts in shared memory ------------------------------
+// Everything that depends on the lane is hoisted; per granule the loops issue one cp.async plus a pointer add.
+
+// [row][D] source (new K, new V, Q) -> [d-octet][row] granules.  A warp instruction covers 8 rows x 4 octets:
+// 64-byte global segments and four conflict-free 128-byte shared-memory lines.
+template <typename MT, int NT, bool ZERO_FILL>
+__device__ __forceinline__ void load_rows(uint4* tile, const MT* src, int64_t row_stride, int rows_valid, int lt) {
+  constexpr int JW = NT / 8;  // d-octets covered per pass
+  const int row_lo = lt & 7, j_lo = lt >> 3;
+  const MT* s0 = src + (int64_t)row_lo * row_stride + j_lo * 8;
+  uint4* d0 = tile + j_lo * kBN + row_lo;
+  const int64_t step = 8 * row_stride;
+  if (rows_valid >= kBN) {
+#pragma unroll
+    for (int jh = 0; jh < 16 / JW; ++jh) {
+      const MT* sp = s0 + jh * JW * 8;
+#pragma unroll
+      for (int rh = 0; rh < 16; ++rh, sp += step) cp_async16(d0 + jh * JW * kBN + rh * 8, sp);
+    }
+  } else {
+#pragma unroll
+    for (int jh = 0; jh < 16 / JW; ++jh) {
+      const MT* sp = s0 + jh * JW * 8;
+#pragma unroll 4
+      for (int rh = 0; rh < 16; ++rh, sp += step) {
+        if (rh * 8 + row_lo < rows_valid) cp_async16(d0 + jh * JW * kBN + rh * 8, sp);
+        else if (ZERO_FILL) d0[jh * JW * kBN + rh * 8] = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+  }
+}
+
+// cached K: chunks [D/8][BS][8] of the blocks bt[0..] -> [d-octet][token] granules
+template <typename MT, int BS, int NT>
+__device__ __forceinline__ void load_k_ctx(uint4* tile, const MT* kc, int64_t block_stride, const int32_t* bt,
+                                           int toks_valid, int lt, int lane) {
+  constexpr int JW = NT / BS;  // d-octets covered per pass
+  const int tt = lt % BS, jl = lt / BS;
+  // lane c holds the physical number of the tile's c-th block; the loop gets it by shuffle, so no load sits in
+  // front of a cp.async
+  int my_bn = 0;
+  if (lane < kBN / BS && lane * BS < toks_valid) my_bn = bt[lane];
+#pragma unroll
+  for (int c = 0; c < kBN / BS; ++c) {
+    const int64_t bn = __shfl_sync(0xffffffffu, my_bn, c);
+    if (c * BS + tt < toks_valid) {
+      const MT* sp = kc + bn * block_stride + (jl * BS + tt) * 8;
+      uint4* dp = tile + jl * kBN + c * BS + tt;
+#pragma unroll
+      for (int q = 0; q < 16 / JW; ++q) cp_async16(dp + q * JW * kBN, sp + q * JW * BS * 8);
+    }
+  }
+}
+
+// cached V: chunks [D][BS] -> [token-octet][d] granules; octets past the context end are zero-filled
+template <typename MT, int BS, int NT>
+__device__ __forceinline__ void load_v_ctx(uint4* tile, const MT* vc, int64_t block_stride, const int32_t* bt,
+                                           int toks_valid, int lt, int lane) {
+  constexpr int HG = BS / 8;   // token octets per block
+  constexpr int DW = NT / HG;  // d rows covered per pass
+  const int hh = lt % HG, dl = lt / HG;
+  int my_bn = 0;
+  if (lane < kBN / BS && lane * BS < toks_valid) my_bn = bt[lane];
+#pragma unroll
+  for (int c = 0; c < kBN / BS; ++c) {
+    const int64_t bn = __shfl_sync(0xffffffffu, my_bn, c);
+    const int tg = c * HG + hh;
+    uint4* dp = tile + tg * kD + dl;
+    if (tg * 8 < toks_valid) {
+      const MT* sp = vc + bn * block_stride + dl * BS + hh * 8;
+#pragma unroll
+      for (int q = 0; q < kD / DW; ++q) cp_async16(dp + q * DW, sp + q * DW * BS);
+    } else {
+#pragma unroll
+      for (int q = 0; q < kD / DW; ++q) dp[q * DW] = make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+}
+
 template <typename MT, int BS>
 __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxAttnParams p) {
   constexpr int G = kD / 8;    // 16-byte granules per row
@@ -311,38 +390,15 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       uint4* Ks = k_s + st * TILE_UNITS;
       if (ti < n_ctx_tiles) {
         const int n0 = ti * kBN;
-        // lane c holds the physical number of the tile's c-th cache block; the granule loop gets it by shuffle
-        // (all lanes of an iteration work on the same block), so no load sits in front of a cp.async
-        int my_bn = 0;
-        if (lane < kBN / BS && n0 + lane * BS < ctx_len) my_bn = bt[n0 / BS + lane];
-#pragma unroll 8
-        for (int e = lt; e < TILE_UNITS; e += kKLoaderThreads) {
-          const int tt = e % BS, j = (e / BS) % G, c = e / (BS * G);
-          const int tok = c * BS + tt;
-          const int64_t bn = __shfl_sync(0xffffffffu, my_bn, c);
-          if (n0 + tok < ctx_len) cp_async16(&Ks[j * kBN + tok], kc + bn * p.kc_bs + (j * BS + tt) * 8);
-        }
+        load_k_ctx<MT, BS, kKLoaderThreads>(Ks, kc, p.kc_bs, bt + n0 / BS, ctx_len - n0, lt, lane);
       } else {
         const int n0 = (ti - n_ctx_tiles) * kBN;
-#pragma unroll 8
-        for (int e = lt; e < TILE_UNITS; e += kKLoaderThreads) {
-          int tok, j;
-          row_major_granule(e, tok, j);
-          if (n0 + tok < q_len) cp_async16(&Ks[j * kBN + tok], kn + (int64_t)(n0 + tok) * p.k_ts + j * 8);
-        }
+        load_rows<MT, kKLoaderThreads, false>(Ks, kn + (int64_t)n0 * p.k_ts, p.k_ts, q_len - n0, lt);
       }
     };
-    {
-      const MT* qb = static_cast<const MT*>(p.q) + (start + m0) * p.q_ts + (int64_t)head * p.q_hs;
-#pragma unroll 8
-      for (int e = lt; e < TILE_UNITS; e += kKLoaderThreads) {
-        int row, j;
-        row_major_granule(e, row, j);
-        if (m0 + row < q_len) cp_async16(&q_s[j * kBM + row], qb + (int64_t)row * p.q_ts + j * 8);
-        else q_s[j * kBM + row] = make_uint4(0u, 0u, 0u, 0u);
-      }
-      cp_async_commit();
-    }
+    load_rows<MT, kKLoaderThreads, true>(q_s, static_cast<const MT*>(p.q) + (start + m0) * p.q_ts + (int64_t)head * p.q_hs,
+                                         p.q_ts, q_len - m0, lt);
+    cp_async_commit();
     issue_k(0, 0);
     cp_async_commit();
     cp_async_wait<1>();
@@ -372,30 +428,10 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       uint4* Vs = v_s + st * TILE_UNITS;
       if (ti < n_ctx_tiles) {
         const int n0 = ti * kBN;
-        int my_bn = 0;
-        if (lane < kBN / BS && n0 + lane * BS < ctx_len) my_bn = bt[n0 / BS + lane];
-#pragma unroll 8
-        for (int e = lt; e < TILE_UNITS; e += kVLoaderThreads) {
-          const int hh = e % HG, d = (e / HG) % kD, c = e / (HG * kD);
-          const int tg = c * HG + hh;
-          uint4* dst = &Vs[tg * kD + d];
-          const int64_t bn = __shfl_sync(0xffffffffu, my_bn, c);
-          if (n0 + tg * 8 < ctx_len) {
-            cp_async16(dst, vc + bn * p.vc_bs + d * BS + hh * 8);
-          } else {
-            *dst = make_uint4(0u, 0u, 0u, 0u);
-          }
-        }
+        load_v_ctx<MT, BS, kVLoaderThreads>(Vs, vc, p.vc_bs, bt + n0 / BS, ctx_len - n0, lt, lane);
       } else {
         const int n0 = (ti - n_ctx_tiles) * kBN;
-#pragma unroll 8
-        for (int e = lt; e < TILE_UNITS; e += kVLoaderThreads) {
-          int tok, j;
-          row_major_granule(e, tok, j);
-          uint4* dst = &Vs[j * kBN + tok];
-          if (n0 + tok < q_len) cp_async16(dst, vn + (int64_t)(n0 + tok) * p.v_ts + j * 8);
-          else *dst = make_uint4(0u, 0u, 0u, 0u);
-        }
+        load_rows<MT, kVLoaderThreads, true>(Vs, vn + (int64_t)n0 * p.v_ts, p.v_ts, q_len - n0, lt);
       }
     };
     issue_v(0, 0);
