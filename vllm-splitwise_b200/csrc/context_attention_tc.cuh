@@ -3,20 +3,22 @@
 // Same contract as context_attn_kernel (context_attention.cuh); this is the GEMM-shaped version:
 //   S = Q.K^T   : tcgen05.mma M=128 (query rows) x N=128 (KV tokens) x K=16, both operands from shared memory,
 //                 fp32 accumulator in TMEM (two S buffers, so Q.K^T of tile i+1 runs under the softmax of tile i)
-//   P           : the softmax warps read S from TMEM (one thread = one query row: max / sum need no shuffles),
-//                 and write P in the element type back to TMEM over the S columns they have consumed
-//   O_i = P.V   : tcgen05.mma with A = P from TMEM, B = V from shared memory, fresh accumulator per tile (two
-//                 buffers); the row owner folds it into its register accumulator  O = O*alpha + O_i
-//                 (no TMEM read-modify-write when the running max moves).
-// Warp roles (7 warps): 0-3 softmax/epilogue (TMEM lanes 32w..32w+31), 4 TMEM allocator + the single MMA-issuing
-// thread, 5 K loader (+ the Q tile), 6-7 V loaders.  Loaders move 16-byte granules with cp.async straight
-// into the no-swizzle canonical UMMA layouts -- the paged layouts are already made of those granules:
+//   P           : the softmax warps read S from TMEM (two threads per query row, 64 columns each; the row maximum
+//                 is exchanged through shared memory once per tile) and write P in the element type back to TMEM over
+//                 the S columns they have consumed
+//   O += P.V    : tcgen05.mma with A = P from TMEM, B = V from shared memory, one fp32 accumulator in TMEM for the whole
+//                 row block.  The softmax reference point follows the running maximum lazily (it moves only when the
+//                 maximum grew by more than 2^8), so the accumulator is rescaled in TMEM rarely.
+// Warp roles (12 warps): 0-7 softmax/epilogue (warp w reaches TMEM lanes 32*(w%4)..+31; warps 0-3 take tile columns
+// 0-63, warps 4-7 columns 64-127), 8 TMEM allocator + the single MMA-issuing thread, 9 K loader (+ the Q tile),
+// 10-11 V loaders.  Loaders move 16-byte granules with cp.async straight into the no-swizzle canonical UMMA layouts
+// -- the paged layouts are already made of those granules:
 //   Q, K (cached or new): [d-octet j][row]   K-major   core matrix = 8 rows x 16 B contiguous, SBO 128 B, LBO rows*16 B
 //   V cached  [D][bs]  -> [token-octet][d]   K-major B operand of P.V (n = d, k = token)
 //   V new   [token][D] -> [d-octet][token]   MN-major B operand
 // Pipelines: k_full/k_empty and v_full/v_empty (2 stages each, loaders <-> MMA via tcgen05.commit), s_full, p_full,
-// o_full, o_empty (MMA <-> softmax).  tcgen05.mma's execute in issue order, which is what frees an S buffer
-// (P.V of tile i is issued before Q.K^T of tile i+2).
+// o_full (MMA <-> softmax).  tcgen05.mma's execute in issue order, which is what frees an S buffer (P.V of tile i
+// is issued before Q.K^T of tile i+2).
 #pragma once
 
 #include <type_traits>
@@ -31,9 +33,10 @@ constexpr int kBM = 128;       // query rows per CTA = UMMA M
 constexpr int kBN = 128;       // KV tokens per tile = UMMA N of Q.K^T
 constexpr int kStages = 2;
 constexpr int kTileBytes = kBN * kD * 2;  // 32 KiB: one Q, K or V tile
-constexpr int kSoftmaxThreads = 128, kKLoaderThreads = 32, kVLoaderThreads = 64;
-constexpr int kThreads = kSoftmaxThreads + 32 + kKLoaderThreads + kVLoaderThreads;  // 256: 8 warps, so that the row-owning threads may use up to 255 registers
-constexpr int kSmemBytes = (1 + 2 * kStages) * kTileBytes + 256;
+constexpr int kSoftmaxThreads = 256, kKLoaderThreads = 32, kVLoaderThreads = 64;
+constexpr int kMmaWarp = kSoftmaxThreads / 32;
+constexpr int kThreads = kSoftmaxThreads + 32 + kKLoaderThreads + kVLoaderThreads;  // 384 = 12 warps (168 registers per thread)
+constexpr int kSmemBytes = (1 + 2 * kStages) * kTileBytes + 256 + 3 * 2 * 128 * 4;
 
 // ---- tcgen05 wrappers --------------------------------------------------------------------------
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -109,6 +112,10 @@ struct Barriers {
   uint64_t k_full[kStages], k_empty[kStages], v_full[kStages], v_empty[kStages];
   uint64_t s_full[2], p_full[2], o_full;
   uint32_t tmem_base;
+};
+struct Exchange {        // between the two threads of a query row
+  float m[2][2][128];    // [tile parity][column half][row] tile maximum
+  float l[2][128];       // [column half][row] partial denominators
 };
 
 // granule index -> (row, d-octet) for sources laid out [row][D]: a warp covers 8 rows x 4 octets, i.e. 64-byte
@@ -207,6 +214,7 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
   uint4* k_s = q_s + TILE_UNITS;
   uint4* v_s = k_s + kStages * TILE_UNITS;
   Barriers* bar = reinterpret_cast<Barriers*>(v_s + kStages * TILE_UNITS);
+  Exchange* xch = reinterpret_cast<Exchange*>(reinterpret_cast<uint8_t*>(bar) + 256);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int mblk = gridDim.x - 1 - blockIdx.x;
@@ -236,19 +244,22 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
     mbar_init(&bar->o_full, 1);
     mbar_fence_init();
   }
-  if (warp == 4) tmem_alloc_512(&bar->tmem_base);
+  if (warp == kMmaWarp) tmem_alloc_512(&bar->tmem_base);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = bar->tmem_base;
 
-  if (warp < 4) {
-    // ================= softmax + epilogue: thread = query row =================
-    const uint32_t lane_off = (uint32_t)(32 * warp) << 16;
-    const int qrow = m0 + tid;
+  if (warp < 8) {
+    // ================= softmax + epilogue: two threads per query row, 64 columns of every tile each =================
+    // warps 0-3 take columns [0,64), warps 4-7 columns [64,128) of the same 128 rows (a warp reaches the TMEM lanes
+    // 32*(warp%4)..+31).  The two halves of a row agree on the reference point through shared memory once per tile.
+    const int half = warp >> 2, row = tid & 127;
+    const uint32_t lane_off = (uint32_t)(32 * (warp & 3)) << 16;
+    const int qrow = m0 + row;
     const bool has_alibi = p.alibi_slopes != nullptr;
     const float slope2 = has_alibi ? p.alibi_slopes[head] * 1.4426950408889634f : 0.f;
-    const uint32_t o_addr = tmem + lane_off + 256;
+    const uint32_t o_addr = tmem + lane_off + 256 + 64 * half;
     // m_used: the reference point of P and O.  It follows the running maximum lazily: it moves only when the
     // maximum has grown by more than 2^8, so that the O accumulator in TMEM is rescaled rarely (exact either way:
     // numerator and denominator carry the same reference point).
@@ -257,26 +268,32 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
     for (int i = 0; i < n_tiles; ++i) {
       const int st = i & 1, u = i >> 1;
       const bool is_ctx = i < n_ctx_tiles;
-      const int n0 = (is_ctx ? i : i - n_ctx_tiles) * kBN;
-      // columns [0, limit) of this tile are visible to this row
+      const int n0 = (is_ctx ? i : i - n_ctx_tiles) * kBN + 64 * half;  // first column of this thread's half
+      // columns [0, limit) of this half are visible to this row
       const int limit = is_ctx ? ctx_len - n0 : qrow - n0 + 1;
-      // key position minus query position of column 0 (ALiBi)
+      // key position minus query position of this half's column 0 (ALiBi)
       const float bias0 = slope2 * (float)(is_ctx ? n0 - ctx_len - qrow : n0 - qrow);
       mbar_wait(&bar->s_full[st], u & 1);
       tc_fence_after();
       const uint32_t s_addr = tmem + lane_off + st * 128;
-      float s[kBN];
-#pragma unroll
-      for (int c4 = 0; c4 < 4; ++c4) tmem_ld32(s_addr + 32 * c4, reinterpret_cast<uint32_t*>(&s[32 * c4]));
+      float s[64];
+      tmem_ld32(s_addr + 64 * half, reinterpret_cast<uint32_t*>(&s[0]));
+      tmem_ld32(s_addr + 64 * half + 32, reinterpret_cast<uint32_t*>(&s[32]));
       tmem_ld_wait();
-      float mx = -INFINITY;
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-      for (int col = 0; col < kBN; ++col) {
+      for (int col = 0; col < 64; ++col) {
         float v = fmaf(s[col], p.scale_log2, has_alibi ? fmaf(slope2, (float)col, bias0) : 0.f);
         v = col < limit ? v : -INFINITY;
         s[col] = v;
-        mx = fmaxf(mx, v);
+        mx4[col & 3] = fmaxf(mx4[col & 3], v);
       }
+      float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+      // the row's other half: exchange maxima (double-buffered by tile parity; one barrier per tile).  After the
+      // barrier both halves have S in registers, so P may overwrite the S columns.
+      xch->m[st][half][row] = mx;
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      mx = fmaxf(mx, xch->m[st][half ^ 1][row]);
       if (i > 0) {  // P_{i-1}.V_{i-1} has landed in O (one completion per tile: phase = tile index)
         mbar_wait(&bar->o_full, (i - 1) & 1);
         tc_fence_after();
@@ -286,46 +303,48 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
         const float alpha = ex2_approx(m_used - m_new);
         if (i > 0) {
 #pragma unroll
-          for (int c4 = 0; c4 < 4; ++c4) {
+          for (int c = 0; c < 2; ++c) {
             uint32_t r[32];
-            tmem_ld32(o_addr + 32 * c4, r);
+            tmem_ld32(o_addr + 32 * c, r);
             tmem_ld_wait();
 #pragma unroll
             for (int k = 0; k < 32; ++k) r[k] = __float_as_uint(__uint_as_float(r[k]) * alpha);
-            tmem_st16(o_addr + 32 * c4, r);
-            tmem_st16(o_addr + 32 * c4 + 16, r + 16);
+            tmem_st16(o_addr + 32 * c, r);
+            tmem_st16(o_addr + 32 * c + 16, r + 16);
           }
         }
         l_run *= alpha;
         m_used = m_new;
       }
-      float sum = 0.f;
+      float sum4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int c4 = 0; c4 < 4; ++c4) {
+      for (int c = 0; c < 2; ++c) {
         uint32_t pk[16];
 #pragma unroll
         for (int k = 0; k < 32; k += 2) {
-          const float e0 = ex2_approx(s[32 * c4 + k] - m_used);   // masked columns are -inf -> 0
-          const float e1 = ex2_approx(s[32 * c4 + k + 1] - m_used);
-          sum += e0 + e1;
+          const float e0 = ex2_approx(s[32 * c + k] - m_used);   // masked columns are -inf -> 0
+          const float e1 = ex2_approx(s[32 * c + k + 1] - m_used);
+          sum4[(k >> 1) & 3] += e0 + e1;
           pk[k >> 1] = pack2<MT>(e0, e1);
         }
-        tmem_st16(s_addr + 16 * c4, pk);  // P over the S columns (all of S is in registers by now)
+        tmem_st16(s_addr + 32 * half + 16 * c, pk);  // P (2 elements per column) over the consumed S columns
       }
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(&bar->p_full[st]);
-      l_run += sum;
+      l_run += (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
     }
 
+    xch->l[half][row] = l_run;
+    asm volatile("bar.sync 2, 256;" ::: "memory");
+    const float inv = 1.f / (l_run + xch->l[half ^ 1][row]);
     mbar_wait(&bar->o_full, (n_tiles - 1) & 1);
     tc_fence_after();
-    const float inv = 1.f / l_run;
-    MT* orow = static_cast<MT*>(p.o) + (start + qrow) * p.o_ts + (int64_t)head * p.o_hs;
+    MT* orow = static_cast<MT*>(p.o) + (start + qrow) * p.o_ts + (int64_t)head * p.o_hs + 64 * half;
 #pragma unroll
-    for (int c4 = 0; c4 < 4; ++c4) {
+    for (int c = 0; c < 2; ++c) {
       uint32_t r[32];
-      tmem_ld32(o_addr + 32 * c4, r);
+      tmem_ld32(o_addr + 32 * c, r);
       tmem_ld_wait();
       if (qrow < q_len) {
 #pragma unroll
@@ -335,11 +354,11 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
           w.y = pack2<MT>(__uint_as_float(r[k + 2]) * inv, __uint_as_float(r[k + 3]) * inv);
           w.z = pack2<MT>(__uint_as_float(r[k + 4]) * inv, __uint_as_float(r[k + 5]) * inv);
           w.w = pack2<MT>(__uint_as_float(r[k + 6]) * inv, __uint_as_float(r[k + 7]) * inv);
-          *reinterpret_cast<uint4*>(orow + 32 * c4 + k) = w;
+          *reinterpret_cast<uint4*>(orow + 32 * c + k) = w;
         }
       }
     }
-  } else if (warp == 4) {
+  } else if (warp == kMmaWarp) {
     // ================= the MMA-issuing thread =================
     if (lane == 0) {
       const uint32_t idesc_k = instr_desc<MT>(kBN, false);   // Q.K^T and P.V over cached V: K-major B
@@ -380,9 +399,9 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       }
     }
     __syncwarp();
-  } else if (warp == 5) {
+  } else if (warp == kMmaWarp + 1) {
     // ================= K (and Q) loader =================
-    const int lt = tid - 5 * 32;
+    const int lt = tid - (kMmaWarp + 1) * 32;
     const MT* kc = static_cast<const MT*>(p.k_cache) + (int64_t)kvh * p.kc_hs;
     const MT* kn = static_cast<const MT*>(p.k) + start * p.k_ts + (int64_t)kvh * p.k_hs;
     const int32_t* bt = p.b_loc + (int64_t)seq * p.b_loc_stride;
@@ -420,7 +439,7 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
     }
   } else {
     // ================= V loaders =================
-    const int lt = tid - 6 * 32;
+    const int lt = tid - (kMmaWarp + 2) * 32;
     const MT* vc = static_cast<const MT*>(p.v_cache) + (int64_t)kvh * p.vc_hs;
     const MT* vn = static_cast<const MT*>(p.v) + start * p.v_ts + (int64_t)kvh * p.v_hs;
     const int32_t* bt = p.b_loc + (int64_t)seq * p.b_loc_stride;
@@ -464,7 +483,7 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  if (warp == 4) tmem_dealloc_512(tmem);
+  if (warp == kMmaWarp) tmem_dealloc_512(tmem);
 }
 
 template <typename MT, int BS>
