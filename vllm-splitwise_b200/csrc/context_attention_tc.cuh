@@ -2,7 +2,7 @@
 //
 // Same contract as context_attn_kernel (context_attention.cuh); this is the GEMM-shaped version:
 //   S = Q.K^T   : tcgen05.mma M=128 (query rows) x N=128 (KV tokens) x K=16, both operands from shared memory,
-//                 fp32 accumulator in TMEM (two S buffers, so Q.K^T of tile i+1 runs under the softmax of tile i)
+//                 fp32 accumulator in TMEM (three S buffers: Q.K^T runs two tiles ahead of the softmax)
 //   P           : the softmax warps read S from TMEM (two threads per query row, 64 columns each; the row maximum
 //                 is exchanged through shared memory once per tile) and write P in the element type back to TMEM over
 //                 the S columns they have consumed
@@ -18,7 +18,7 @@
 //   V new   [token][D] -> [d-octet][token]   MN-major B operand
 // Pipelines: k_full/k_empty and v_full/v_empty (2 stages each, loaders <-> MMA via tcgen05.commit), s_full, p_full,
 // o_full (MMA <-> softmax).  tcgen05.mma's execute in issue order, which is what frees an S buffer (P.V of tile i
-// is issued before Q.K^T of tile i+2).
+// is issued before Q.K^T of tile i+3).
 #pragma once
 
 #include <type_traits>
@@ -110,7 +110,7 @@ __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.
 struct Barriers {
   uint64_t q_full;
   uint64_t k_full[kStages], k_empty[kStages], v_full[kStages], v_empty[kStages];
-  uint64_t s_full[2], p_full[2], o_full;
+  uint64_t s_full[3], p_full[3], o_full;
   uint32_t tmem_base;
 };
 struct Exchange {        // between the two threads of a query row
@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       mbar_init(&bar->k_empty[s], 1);
       mbar_init(&bar->v_empty[s], 1);
     }
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < 3; ++s) {
       mbar_init(&bar->s_full[s], 1);
       mbar_init(&bar->p_full[s], kSoftmaxThreads);
     }
@@ -259,40 +259,52 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
     const int qrow = m0 + row;
     const bool has_alibi = p.alibi_slopes != nullptr;
     const float slope2 = has_alibi ? p.alibi_slopes[head] * 1.4426950408889634f : 0.f;
-    const uint32_t o_addr = tmem + lane_off + 256 + 64 * half;
+    const uint32_t o_addr = tmem + lane_off + 384 + 64 * half;
     // m_used: the reference point of P and O.  It follows the running maximum lazily: it moves only when the
     // maximum has grown by more than 2^8, so that the O accumulator in TMEM is rescaled rarely (exact either way:
     // numerator and denominator carry the same reference point).
     float m_used = -INFINITY, l_run = 0.f;
 
     for (int i = 0; i < n_tiles; ++i) {
-      const int st = i & 1, u = i >> 1;
+      const int sb = i % 3, st = i & 1;  // S/P buffer, exchange-slot parity
       const bool is_ctx = i < n_ctx_tiles;
       const int n0 = (is_ctx ? i : i - n_ctx_tiles) * kBN + 64 * half;  // first column of this thread's half
       // columns [0, limit) of this half are visible to this row
       const int limit = is_ctx ? ctx_len - n0 : qrow - n0 + 1;
       // key position minus query position of this half's column 0 (ALiBi)
       const float bias0 = slope2 * (float)(is_ctx ? n0 - ctx_len - qrow : n0 - qrow);
-      mbar_wait(&bar->s_full[st], u & 1);
+      mbar_wait(&bar->s_full[sb], (i / 3) & 1);
       tc_fence_after();
-      const uint32_t s_addr = tmem + lane_off + st * 128;
+      const uint32_t s_addr = tmem + lane_off + sb * 128;
       float s[64];
       tmem_ld32(s_addr + 64 * half, reinterpret_cast<uint32_t*>(&s[0]));
       tmem_ld32(s_addr + 64 * half + 32, reinterpret_cast<uint32_t*>(&s[32]));
       tmem_ld_wait();
       float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+      // fast path (warp-uniform): every column of this half is visible to every row of the warp and there is no
+      // bias -> the maximum is taken on the raw scores and the scale is folded into the exponent's FMA
+      const bool plain = !has_alibi && __all_sync(0xffffffffu, limit >= 64);
+      float mx, mul;
+      if (plain) {
 #pragma unroll
-      for (int col = 0; col < 64; ++col) {
-        float v = fmaf(s[col], p.scale_log2, has_alibi ? fmaf(slope2, (float)col, bias0) : 0.f);
-        v = col < limit ? v : -INFINITY;
-        s[col] = v;
-        mx4[col & 3] = fmaxf(mx4[col & 3], v);
+        for (int col = 0; col < 64; ++col) mx4[col & 3] = fmaxf(mx4[col & 3], s[col]);
+        mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;  // scale > 0
+        mul = p.scale_log2;
+      } else {
+#pragma unroll
+        for (int col = 0; col < 64; ++col) {
+          float v = fmaf(s[col], p.scale_log2, has_alibi ? fmaf(slope2, (float)col, bias0) : 0.f);
+          v = col < limit ? v : -INFINITY;
+          s[col] = v;
+          mx4[col & 3] = fmaxf(mx4[col & 3], v);
+        }
+        mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        mul = 1.f;
       }
-      float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       // the row's other half: exchange maxima (double-buffered by tile parity; one barrier per tile).  After the
       // barrier both halves have S in registers, so P may overwrite the S columns.
       xch->m[st][half][row] = mx;
-      asm volatile("bar.sync 2, 256;" ::: "memory");
+      asm volatile("bar.sync %0, 64;" ::"r"(2 + (warp & 3)) : "memory");  // the two warps that share these 32 rows
       mx = fmaxf(mx, xch->m[st][half ^ 1][row]);
       if (i > 0) {  // P_{i-1}.V_{i-1} has landed in O (one completion per tile: phase = tile index)
         mbar_wait(&bar->o_full, (i - 1) & 1);
@@ -322,8 +334,8 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
         uint32_t pk[16];
 #pragma unroll
         for (int k = 0; k < 32; k += 2) {
-          const float e0 = ex2_approx(s[32 * c + k] - m_used);   // masked columns are -inf -> 0
-          const float e1 = ex2_approx(s[32 * c + k + 1] - m_used);
+          const float e0 = ex2_approx(fmaf(s[32 * c + k], mul, -m_used));   // masked columns are -inf -> 0
+          const float e1 = ex2_approx(fmaf(s[32 * c + k + 1], mul, -m_used));
           sum4[(k >> 1) & 3] += e0 + e1;
           pk[k >> 1] = pack2<MT>(e0, e1);
         }
@@ -331,12 +343,12 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       }
       tmem_st_wait();
       tc_fence_before();
-      mbar_arrive(&bar->p_full[st]);
+      mbar_arrive(&bar->p_full[sb]);
       l_run += (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
     }
 
     xch->l[half][row] = l_run;
-    asm volatile("bar.sync 2, 256;" ::: "memory");
+    asm volatile("bar.sync %0, 64;" ::"r"(2 + (warp & 3)) : "memory");
     const float inv = 1.f / (l_run + xch->l[half ^ 1][row]);
     mbar_wait(&bar->o_full, (n_tiles - 1) & 1);
     tc_fence_after();
@@ -365,23 +377,27 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       const uint32_t idesc_mn = instr_desc<MT>(kD, true);    // P.V over new V: MN-major B
       const uint32_t q_addr = smem_u32(q_s);
       mbar_wait(&bar->q_full, 0);
-      for (int i = 0; i <= n_tiles; ++i) {
-        if (i < n_tiles) {  // S_i = Q.K_i^T
-          const int st = i & 1;
-          mbar_wait(&bar->k_full[st], (i >> 1) & 1);
-          tc_fence_after();
-          const uint32_t k_addr = smem_u32(k_s + st * TILE_UNITS);
+      auto issue_qk = [&](int i) {  // S_i = Q.K_i^T into S buffer i%3
+        const int st = i & 1;
+        mbar_wait(&bar->k_full[st], (i >> 1) & 1);
+        tc_fence_after();
+        const uint32_t k_addr = smem_u32(k_s + st * TILE_UNITS);
 #pragma unroll
-          for (int ks = 0; ks < kD / 16; ++ks)
-            mma_ss(tmem + st * 128, smem_desc(q_addr + ks * 2 * kBM * 16, kBM * 16, 128),
-                   smem_desc(k_addr + ks * 2 * kBN * 16, kBN * 16, 128), idesc_k, ks > 0);
-          tc_commit(&bar->k_empty[st]);
-          tc_commit(&bar->s_full[st]);
-        }
-        if (i >= 1) {  // O_j = P_j.V_j
-          const int j = i - 1, st = j & 1, u = j >> 1;
-          mbar_wait(&bar->v_full[st], u & 1);
-          mbar_wait(&bar->p_full[st], u & 1);  // implies the softmax threads have seen O_{j-1} (and rescaled it)
+        for (int ks = 0; ks < kD / 16; ++ks)
+          mma_ss(tmem + (i % 3) * 128, smem_desc(q_addr + ks * 2 * kBM * 16, kBM * 16, 128),
+                 smem_desc(k_addr + ks * 2 * kBN * 16, kBN * 16, 128), idesc_k, ks > 0);
+        tc_commit(&bar->k_empty[st]);
+        tc_commit(&bar->s_full[i % 3]);
+      };
+      // Q.K^T runs two tiles ahead of P.V (three S buffers): S_{j+1} is ready when the softmax warps finish tile j
+      issue_qk(0);
+      if (n_tiles > 1) issue_qk(1);
+      for (int j = 0; j < n_tiles; ++j) {
+        if (j + 2 < n_tiles) issue_qk(j + 2);
+        {  // O += P_j.V_j
+          const int st = j & 1, sb = j % 3;
+          mbar_wait(&bar->v_full[st], (j >> 1) & 1);
+          mbar_wait(&bar->p_full[sb], (j / 3) & 1);  // implies the softmax threads have seen O_{j-1} (and rescaled it)
           tc_fence_after();
           const uint32_t v_addr = smem_u32(v_s + st * TILE_UNITS);
           const bool is_ctx = j < n_ctx_tiles;
@@ -391,7 +407,7 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
             // new V:    [d-octet][token] granules (MN-major, LBO = next 8 tokens, SBO = next d octet)
             const uint64_t b = is_ctx ? smem_desc(v_addr + kt * 2 * kD * 16, kD * 16, 128)
                                       : smem_desc(v_addr + kt * 16 * 16, 128, kBN * 16);
-            mma_ts(tmem + 256, tmem + st * 128 + kt * 8, b, is_ctx ? idesc_k : idesc_mn, (j | kt) > 0);
+            mma_ts(tmem + 384, tmem + sb * 128 + kt * 8, b, is_ctx ? idesc_k : idesc_mn, (j | kt) > 0);
           }
           tc_commit(&bar->v_empty[st]);
           tc_commit(&bar->o_full);
