@@ -306,14 +306,17 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       xch->m[st][half][row] = mx;
       asm volatile("bar.sync %0, 64;" ::"r"(2 + (warp & 3)) : "memory");  // the two warps that share these 32 rows
       mx = fmaxf(mx, xch->m[st][half ^ 1][row]);
-      if (i > 0) {  // P_{i-1}.V_{i-1} has landed in O (one completion per tile: phase = tile index)
-        mbar_wait(&bar->o_full, (i - 1) & 1);
-        tc_fence_after();
-      }
+      // O is touched by these threads only when the reference point moves.  The completion of P_{i-1}.V_{i-1}
+      // (o_full: one phase per tile) is awaited up front in that case and otherwise at the end of the tile, where
+      // it costs nothing -- waiting for every phase in order is what keeps the parity tracking exact.
+      bool o_seen = i == 0;
       if (__any_sync(0xffffffffu, mx > m_used + 8.f)) {
         const float m_new = fmaxf(m_used, mx);
         const float alpha = ex2_approx(m_used - m_new);
         if (i > 0) {
+          mbar_wait(&bar->o_full, (i - 1) & 1);
+          tc_fence_after();
+          o_seen = true;
 #pragma unroll
           for (int c = 0; c < 2; ++c) {
             uint32_t r[32];
@@ -342,6 +345,7 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
         tmem_st16(s_addr + 32 * half + 16 * c, pk);  // P (2 elements per column) over the consumed S columns
       }
       tmem_st_wait();
+      if (!o_seen) mbar_wait(&bar->o_full, (i - 1) & 1);
       tc_fence_before();
       mbar_arrive(&bar->p_full[sb]);
       l_run += (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
@@ -393,8 +397,7 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       issue_qk(0);
       if (n_tiles > 1) issue_qk(1);
       for (int j = 0; j < n_tiles; ++j) {
-        if (j + 2 < n_tiles) issue_qk(j + 2);
-        {  // O += P_j.V_j
+        {  // O += P_j.V_j (first: it is on the softmax warps' critical path)
           const int st = j & 1, sb = j % 3;
           mbar_wait(&bar->v_full[st], (j >> 1) & 1);
           mbar_wait(&bar->p_full[sb], (j / 3) & 1);  // implies the softmax threads have seen O_{j-1} (and rescaled it)
@@ -412,6 +415,7 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
           tc_commit(&bar->v_empty[st]);
           tc_commit(&bar->o_full);
         }
+        if (j + 2 < n_tiles) issue_qk(j + 2);
       }
     }
     __syncwarp();
