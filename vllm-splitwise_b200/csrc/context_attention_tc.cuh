@@ -33,9 +33,12 @@ constexpr int kBM = 128;       // query rows per CTA = UMMA M
 constexpr int kBN = 128;       // KV tokens per tile = UMMA N of Q.K^T
 constexpr int kStages = 2;
 constexpr int kTileBytes = kBN * kD * 2;  // 32 KiB: one Q, K or V tile
-constexpr int kSoftmaxThreads = 256, kKLoaderThreads = 32, kVLoaderThreads = 64;
+constexpr int kSoftmaxThreads = 256, kKLoaderThreads = 64, kVLoaderThreads = 128;
 constexpr int kMmaWarp = kSoftmaxThreads / 32;
-constexpr int kThreads = kSoftmaxThreads + 32 + kKLoaderThreads + kVLoaderThreads;  // 384 = 12 warps (168 registers per thread)
+// 16 warps = 4 warpgroups: 0-1 softmax, 2 = {MMA warp, 2 K-loader warps, 1 spare}, 3 = 4 V-loader warps.  The kernel is
+// launched with 128 registers per thread; setmaxnreg moves registers from the loader groups to the softmax groups.
+constexpr int kThreads = 512;
+constexpr int kRegsSoftmax = 168, kRegsOther = 88;  // (2*168 + 2*88) * 128 threads = 64 Ki registers
 constexpr int kSmemBytes = (1 + 2 * kStages) * kTileBytes + 256 + 3 * 2 * 128 * 4;
 
 // ---- tcgen05 wrappers --------------------------------------------------------------------------
@@ -251,6 +254,7 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
   const uint32_t tmem = bar->tmem_base;
 
   if (warp < 8) {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsSoftmax));
     // ================= softmax + epilogue: two threads per query row, 64 columns of every tile each =================
     // warps 0-3 take columns [0,64), warps 4-7 columns [64,128) of the same 128 rows (a warp reaches the TMEM lanes
     // 32*(warp%4)..+31).  The two halves of a row agree on the reference point through shared memory once per tile.
@@ -374,7 +378,9 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
         }
       }
     }
-  } else if (warp == kMmaWarp) {
+  } else if (warp < 12) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));
+   if (warp == kMmaWarp) {
     // ================= the MMA-issuing thread =================
     if (lane == 0) {
       const uint32_t idesc_k = instr_desc<MT>(kBN, false);   // Q.K^T and P.V over cached V: K-major B
@@ -419,8 +425,8 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       }
     }
     __syncwarp();
-  } else if (warp == kMmaWarp + 1) {
-    // ================= K (and Q) loader =================
+   } else if (warp < kMmaWarp + 3) {
+    // ================= K (and Q) loaders =================
     const int lt = tid - (kMmaWarp + 1) * 32;
     const MT* kc = static_cast<const MT*>(p.k_cache) + (int64_t)kvh * p.kc_hs;
     const MT* kn = static_cast<const MT*>(p.k) + start * p.k_ts + (int64_t)kvh * p.k_hs;
@@ -457,9 +463,11 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
         cp_async_commit();
       }
     }
+   }
   } else {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));
     // ================= V loaders =================
-    const int lt = tid - (kMmaWarp + 2) * 32;
+    const int lt = tid - 12 * 32;
     const MT* vc = static_cast<const MT*>(p.v_cache) + (int64_t)kvh * p.vc_hs;
     const MT* vn = static_cast<const MT*>(p.v) + start * p.v_ts + (int64_t)kvh * p.v_hs;
     const int32_t* bt = p.b_loc + (int64_t)seq * p.b_loc_stride;
