@@ -38,6 +38,7 @@ extern "C" int b200_context_attention_fwd(const b200_context_attn_args_t* a, b20
   p.b_loc_stride = a->block_table_stride;
   p.num_heads = a->num_heads;
   p.num_kv_heads = a->num_kv_heads;
+  p.row_limit = (a->max_input_len + 127) / 128 * 128;
 
   DeviceGuard guard;
   B200_CUDA_TRY(guard.set(a->device));

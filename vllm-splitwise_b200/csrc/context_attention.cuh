@@ -47,6 +47,7 @@ struct CtxAttnParams {
   int32_t b_loc_stride;
   int32_t num_heads;
   int32_t num_kv_heads;
+  int32_t row_limit;  // new-token rows >= row_limit are not computed: ceil(max_input_len / 128) * 128 (the reference's grid)
 };
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
