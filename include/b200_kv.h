@@ -244,6 +244,29 @@ typedef struct {
 
 B200_API int b200_context_attention_fwd(const b200_context_attn_args_t* args, b200_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Device-side decode metadata.
+ * Replaces the per-step Python list building + H2D copies of ModelRunner._prepare_decode
+ * (vllm/worker/model_runner.py:274-399).  Persistent device state, owned by the caller:
+ *   state_block_tables int32 [max_seqs, max_blocks_per_seq]   physical block of every logical block
+ *   state_seq_lens     int32 [max_seqs]                       tokens of the sequence so far
+ * b200_block_tables_append: appends = int32 triples (state_row, block_index, physical_block) on the device --
+ *   the blocks the block manager allocated since the last step (block_manager.py:268-309).
+ * b200_decode_metadata_step: for batch entry b with row r = batch_rows[b] (r < 0 = CUDA-graph padding entry):
+ *   seq_len = ++state_seq_lens[r]; positions[b] = seq_len-1; context_lens[b] = min(seq_len, sliding_window) (or
+ *   seq_len when sliding_window <= 0); slot_mapping[b] = table[r][pos / bs]*bs + pos % bs;
+ *   block_tables[b, :] = the sequence's blocks (the last sliding_window/bs of them with a window), zero padded to
+ *   out_blocks.  Padding entries get position 0, slot -1 (_PAD_SLOT_ID), context 1, a zero row (:336-341).
+ *   A row must appear at most once per batch.  Never allocates, never synchronises (CUDA-graph capturable).
+ * ------------------------------------------------------------------------------------------ */
+B200_API int b200_block_tables_append(int32_t* state_block_tables, const int32_t* appends, int32_t num_appends,
+                                      int32_t max_blocks_per_seq, b200_stream_t stream);
+B200_API int b200_decode_metadata_step(const int32_t* state_block_tables, int32_t* state_seq_lens,
+                                       const int32_t* batch_rows, int32_t batch, int32_t max_blocks_per_seq,
+                                       int32_t block_size, int32_t sliding_window, int64_t* positions,
+                                       int64_t* slot_mapping, int32_t* context_lens, int32_t* block_tables,
+                                       int32_t out_blocks, b200_stream_t stream);
+
 /* Replaces cuda_utils (csrc/cuda_utils_kernels.cu:5-35). */
 B200_API int b200_get_device_attribute(int32_t attribute, int32_t device_id);
 B200_API int b200_get_max_shared_memory_per_block_device_attribute(int32_t device_id);

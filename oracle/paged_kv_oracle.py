@@ -393,3 +393,34 @@ def context_attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: 
         logits = logits.masked_fill((kpos[None, :] > qpos[:, None])[None], float("-inf"))
         probs = torch.softmax(logits, dim=-1)
         o[s0:s0 + L] = torch.einsum("hmn,nhd->mhd", probs, vals).to(o.dtype)
+
+
+# --------------------------------------------------------------------------------------------
+# decode metadata  
+# --------------------------------------------------------------------------------------------
+def prepare_decode(seq_lens: Sequence[int], block_tables: Sequence[Sequence[int]], block_size: int,
+                   sliding_window: Optional[int] = None, pad_to: Optional[int] = None,
+                   out_blocks: Optional[int] = None):
+    """Restates ModelRunner._prepare_decode (vllm/worker/model_runner.py:289-377) for one step: `seq_lens[i]` is
+    the sequence length INCLUDING the token being fed (seq_data.get_len(), :303), `block_tables[i]` its physical
+    blocks.  Returns (positions int64 [B,1], slot_mapping int64 [B,1], context_lens int32 [B], block_tables int32
+    [B, out_blocks]) with the reference's padding: entries past the real batch get position 0, slot -1, context 1
+    and an empty table (:336-341); tables are padded with 0 (:370-376).
+    Pinned by tests/golden/decode_metadata_ref.json (the reference method itself, executed by
+    oracle/make_golden_metadata.py)."""
+    positions, slots, ctx, tables = [], [], [], []
+    for n, bt in zip(seq_lens, block_tables):
+        pos = n - 1
+        positions.append([pos])
+        ctx.append(n if sliding_window is None else min(n, sliding_window))
+        slots.append([bt[pos // block_size] * block_size + pos % block_size])
+        bt = list(bt)
+        if sliding_window is not None:
+            bt = bt[-(sliding_window // block_size):]
+        tables.append(bt)
+    for _ in range((pad_to or 0) - len(positions)):
+        positions.append([0]); slots.append([-1]); ctx.append(1); tables.append([])
+    width = out_blocks or max(len(t) for t in tables)
+    tables = [t + [0] * (width - len(t)) for t in tables]
+    return (torch.tensor(positions, dtype=torch.long), torch.tensor(slots, dtype=torch.long),
+            torch.tensor(ctx, dtype=torch.int32), torch.tensor(tables, dtype=torch.int32))
