@@ -267,6 +267,25 @@ B200_API int b200_decode_metadata_step(const int32_t* state_block_tables, int32_
                                        int64_t* slot_mapping, int32_t* context_lens, int32_t* block_tables,
                                        int32_t out_blocks, b200_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------
+ * One-shot all-reduce (sum) over NVLink peer memory: the tensor-parallel reduction after the
+ * attention output projection.  Replaces the reference's custom all-reduce, 1-stage kernel
+ * (csrc/custom_all_reduce.cuh:215-262, :420-470; vllm/model_executor/parallel_utils/custom_all_reduce.py).
+ * Every rank owns an input buffer and two uint64 flag arrays start[world], done[world] (zero at creation), mapped
+ * into all peers with b200_kv_ipc_* / peer access.  Per call (the same `epoch` = 1, 2, 3, ... on all ranks):
+ *   peer_inputs[r]      rank r's input buffer as seen from this rank (own buffer for r == rank)
+ *   peer_start_slots[r] address of start[rank] inside rank r's start array;  peer_done_slots[r] likewise for done
+ *   my_start / my_done  this rank's own arrays;  counter: local uint32, zero between calls
+ *   out[i] = sum over r = 0..world-1 (fp32, in rank order -> identical bits on every rank) of input_r[i]
+ * numel * sizeof(elt) must be a multiple of 16.  Spins are bounded (max_spins, default 5e7): on expiry *timeout_flag
+ * is set to 1 and the kernel completes.  Never allocates, never synchronises the host.
+ * ------------------------------------------------------------------------------------------ */
+B200_API int b200_allreduce_oneshot(const int64_t* peer_inputs, const int64_t* peer_start_slots,
+                                    const int64_t* peer_done_slots, const uint64_t* my_start, const uint64_t* my_done,
+                                    uint32_t* counter, int32_t* timeout_flag, void* out, int64_t numel, int32_t dtype,
+                                    int32_t rank, int32_t world, uint64_t epoch, int64_t max_spins, int32_t max_ctas,
+                                    b200_stream_t stream);
+
 /* Replaces cuda_utils (csrc/cuda_utils_kernels.cu:5-35). */
 B200_API int b200_get_device_attribute(int32_t attribute, int32_t device_id);
 B200_API int b200_get_max_shared_memory_per_block_device_attribute(int32_t device_id);

@@ -424,3 +424,18 @@ def prepare_decode(seq_lens: Sequence[int], block_tables: Sequence[Sequence[int]
     tables = [t + [0] * (width - len(t)) for t in tables]
     return (torch.tensor(positions, dtype=torch.long), torch.tensor(slots, dtype=torch.long),
             torch.tensor(ctx, dtype=torch.int32), torch.tensor(tables, dtype=torch.int32))
+
+
+# --------------------------------------------------------------------------------------------
+# tensor-parallel all-reduce  
+# --------------------------------------------------------------------------------------------
+def all_reduce_sum(inputs: Sequence[torch.Tensor]) -> torch.Tensor:
+    """Restates the arithmetic of the reference's 1-stage custom all-reduce (csrc/custom_all_reduce.cuh:139-166
+    packed_reduce + :215-262): every element is widened to fp32, the ranks' values are added in rank order
+    0..world-1, and the sum is narrowed once to the element type.  UNPINNED by a run of the reference here (its
+    kernel needs several GPUs; the reference's own test, tests/distributed/test_custom_all_reduce.py, compares
+    against NCCL with allclose) -- anchored on that call site and on the published algorithm."""
+    acc = torch.zeros(inputs[0].shape, dtype=torch.float32)
+    for t in inputs:
+        acc = acc + t.to(torch.float32)
+    return acc.to(inputs[0].dtype)
