@@ -286,6 +286,18 @@ B200_API int b200_allreduce_oneshot(const int64_t* peer_inputs, const int64_t* p
                                     int32_t rank, int32_t world, uint64_t epoch, int64_t max_spins, int32_t max_ctas,
                                     b200_stream_t stream);
 
+/* Two-stage variant for large messages (reference cross_device_reduce_2stage, custom_all_reduce.cuh:264-330):
+ * reduce-scatter into a peer-visible scratch buffer (peer_tmps[r] = rank r's scratch as seen from this rank, at least
+ * as large as the message), a per-CTA flag barrier (mid array uint64 [160][world] per rank, zero at creation;
+ * peer_mid_slots[r] = address of mid[0][rank] inside rank r's array), then an all-gather of the slices.  Same results,
+ * bit for bit, as the one-shot kernel.  All ranks must call it with the same numel. */
+B200_API int b200_allreduce_twostage(const int64_t* peer_inputs, const int64_t* peer_tmps,
+                                     const int64_t* peer_start_slots, const int64_t* peer_done_slots,
+                                     const int64_t* peer_mid_slots, const uint64_t* my_start, const uint64_t* my_done,
+                                     const uint64_t* my_mid, uint32_t* counter, int32_t* timeout_flag, void* out,
+                                     int64_t numel, int32_t dtype, int32_t rank, int32_t world, uint64_t epoch,
+                                     int64_t max_spins, b200_stream_t stream);
+
 /* Replaces cuda_utils (csrc/cuda_utils_kernels.cu:5-35). */
 B200_API int b200_get_device_attribute(int32_t attribute, int32_t device_id);
 B200_API int b200_get_max_shared_memory_per_block_device_attribute(int32_t device_id);

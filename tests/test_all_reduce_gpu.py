@@ -18,8 +18,11 @@ def _comms(world):
     return comms
 
 
-def _run(world, numel, dtype, calls=3):
+def _run(world, numel, dtype, calls=3, two_stage_min_bytes=None):
     comms = _comms(world)
+    for c in comms:
+        if two_stage_min_bytes is not None:
+            c.two_stage_min_bytes = two_stage_min_bytes
     for call in range(calls):
         g = torch.Generator().manual_seed(100 * call + world)
         xs = [(torch.rand(numel, generator=g) * 4 - 2).to(dtype) for _ in range(world)]
@@ -47,6 +50,16 @@ def test_multi_gpu(world, dtype):
         pytest.skip(f"needs {world} GPUs")
     for numel in (8, 64 * 4096, 256 * 8192):   # C2 and C3 decode activations [batch, hidden]
         _run(world, numel, dtype)
+
+
+@pytest.mark.parametrize("world", [4, 8])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16, torch.float32])
+def test_two_stage_multi_gpu(world, dtype):
+    """reduce-scatter + all-gather path, forced for every size (ragged ranges included): same bits as the oracle"""
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    for numel in (8, 8 * 37, 64 * 4096 + 24, 2048 * 1280):
+        _run(world, numel, dtype, calls=2, two_stage_min_bytes=0)
 
 
 def test_registered_input_skips_the_staging_copy():

@@ -80,6 +80,9 @@ SIGNATURES = {
     "b200_allreduce_oneshot": (c_int32, [POINTER(c_int64), POINTER(c_int64), POINTER(c_int64), c_void_p, c_void_p,
                                          c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_int32, c_uint64,
                                          c_int64, c_int32, c_void_p]),
+    "b200_allreduce_twostage": (c_int32, [POINTER(c_int64), POINTER(c_int64), POINTER(c_int64), POINTER(c_int64),
+                                          POINTER(c_int64), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                          c_int64, c_int32, c_int32, c_int32, c_uint64, c_int64, c_void_p]),
     "b200_block_tables_append": (c_int32, [c_void_p, c_void_p, c_int32, c_int32, c_void_p]),
     "b200_decode_metadata_step": (c_int32, [c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_void_p,
                                             c_void_p, c_void_p, c_void_p, c_int32, c_void_p]),

@@ -13,6 +13,9 @@ from . import _lib
 from ._C._common import dtype_code, stream_ptr
 
 
+_MAX_CTAS = 160  # rows of the per-CTA barrier array (kMaxCtas2 in csrc/all_reduce.cu)
+
+
 class CustomAllreduce:
 
     def __init__(self, rank: int, world_size: int, device, group=None, max_size: int = 8 << 20,
@@ -22,8 +25,13 @@ class CustomAllreduce:
         self.rank, self.world_size = rank, world_size
         self.device = torch.device(device)
         self.max_size = max_size
-        self.buffer = torch.zeros(max_size, dtype=torch.uint8, device=self.device)
-        self.flags = torch.zeros(2, world_size, dtype=torch.int64, device=self.device)  # start[world], done[world]
+        # registered input (first half) and the two-stage kernel's scratch (second half), one allocation
+        self.buffer = torch.zeros(2 * max_size, dtype=torch.uint8, device=self.device)
+        # start[world], done[world], mid[160][world]
+        self.flags = torch.zeros(2 + _MAX_CTAS, world_size, dtype=torch.int64, device=self.device)
+        # messages of at least this many bytes go through reduce-scatter + all-gather when world_size > 2
+        # (the reference switches at 512 KiB / 256 KiB for 4 / 8 ranks, custom_all_reduce.cuh:452-463)
+        self.two_stage_min_bytes = 1 << 20
         self.counter = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.timeout = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.epoch = 0
@@ -32,6 +40,8 @@ class CustomAllreduce:
         self._in = (ctypes.c_int64 * world_size)()
         self._start = (ctypes.c_int64 * world_size)()
         self._done = (ctypes.c_int64 * world_size)()
+        self._tmp = (ctypes.c_int64 * world_size)()
+        self._mid = (ctypes.c_int64 * world_size)()
         if group is not None:
             self._connect_ipc(group)
 
@@ -40,6 +50,8 @@ class CustomAllreduce:
         self._in[r] = buf_ptr
         self._start[r] = flags_ptr + 8 * self.rank                      # start_of_rank_r[my rank]
         self._done[r] = flags_ptr + 8 * (self.world_size + self.rank)   # done_of_rank_r[my rank]
+        self._tmp[r] = buf_ptr + self.max_size
+        self._mid[r] = flags_ptr + 8 * (2 * self.world_size + self.rank)  # mid_of_rank_r[CTA 0][my rank]
 
     @staticmethod
     def connect_local(comms: Sequence["CustomAllreduce"]) -> None:
@@ -99,6 +111,14 @@ class CustomAllreduce:
         if inp.data_ptr() != self.buffer.data_ptr():   # registered input (all_reduce_reg, :218-224): no staging copy
             self.buffer[:nbytes].copy_(inp.view(-1).view(torch.uint8), non_blocking=True)  # all_reduce_unreg (:226-229)
         self.epoch += 1
+        if self.world_size > 2 and nbytes >= self.two_stage_min_bytes:
+            st = _lib.load().b200_allreduce_twostage(
+                self._in, self._tmp, self._start, self._done, self._mid, self.flags.data_ptr(),
+                self.flags.data_ptr() + 8 * self.world_size, self.flags.data_ptr() + 16 * self.world_size,
+                self.counter.data_ptr(), self.timeout.data_ptr(), out.data_ptr(), inp.numel(), dtype_code(inp, "input"),
+                self.rank, self.world_size, self.epoch, 0, stream_ptr(self.device))
+            _lib.check(st, "all_reduce (two-stage)")
+            return out
         st = _lib.load().b200_allreduce_oneshot(
             self._in, self._start, self._done, self.flags.data_ptr(), self.flags.data_ptr() + 8 * self.world_size,
             self.counter.data_ptr(), self.timeout.data_ptr(), out.data_ptr(), inp.numel(), dtype_code(inp, "input"),
@@ -115,7 +135,7 @@ class CustomAllreduce:
         nbytes = n * torch.tensor([], dtype=dtype).element_size()
         if nbytes > self.max_size:
             raise RuntimeError("registered_input: larger than the registered buffer")
-        return self.buffer[:nbytes].view(dtype).view(*shape)
+        return self.buffer[:nbytes].view(dtype).view(*shape)  # the first half of the allocation is the input
 
     def timed_out(self) -> bool:
         return bool(self.timeout.item())
