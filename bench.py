@@ -5,6 +5,7 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
         --master-port P bench.py --gpus N --steps K --warmup W
     python bench.py --impl reference ...        # the reference's CPU path (oracle port) on the host cores
+    python bench.py --workload n1 [...]         # SURVEY 8f N1, prefix prefill: TFLOP/s against the tensor peak
 
 Step       = one layer-call of the decode path over one batch: reshape_and_cache of the step's new
              token per sequence, then paged_attention (v1 signature by default) over the whole context.
@@ -464,13 +465,134 @@ def run_b200(args, w):
     return 0
 
 
+# ---------------------------------------------------------------------------------------------
+# prefix ("context") prefill through the reference-named host function.  GEMM-shaped: the
+# metric is TFLOP/s and the roofline is the tensor peak.  `--workload n1` (single GPU).
+# ---------------------------------------------------------------------------------------------
+N1 = dict(B=8, H=32, Hkv=32, D=128, bs=16, L=2048, ctx=2048, dtype="float16",
+          name="N1 Llama-2-7B chunked prefill: 8 sequences x (2048 new + 2048 cached tokens), 32 heads, head 128, "
+               "block 16, fp16")
+
+
+def n1_flops(w) -> float:
+    return 4.0 * w["D"] * w["H"] * w["B"] * (w["L"] * w["ctx"] + w["L"] * (w["L"] + 1) / 2)
+
+
+def run_n1(args):
+    import torch
+    w = N1
+    B, H, Hkv, D, bs, L, ctx = (w[k] for k in ("B", "H", "Hkv", "D", "bs", "L", "ctx"))
+    flops = n1_flops(w)
+    if args.impl == "reference":  # CPU: the oracle's restatement of the reference kernels, on a bounded sample
+        from oracle import paged_kv_oracle as O
+        torch.manual_seed(0)
+        sub = dict(w, B=1, H=4, Hkv=4, L=512, ctx=512)
+        q = torch.rand(sub["L"], sub["H"], D).half(); k = torch.rand(sub["L"], sub["Hkv"], D).half(); v = torch.rand_like(k)
+        nb = sub["ctx"] // bs
+        kc = torch.rand(nb, sub["Hkv"], D // 8, bs, 8).half(); vc = torch.rand(nb, sub["Hkv"], D, bs).half()
+        o = torch.zeros_like(q)
+        fn = lambda: O.context_attention_fwd(q, k, v, o, kc, vc, torch.arange(nb).view(1, nb), torch.tensor([0]),  # noqa: E731
+                                             torch.tensor([sub["L"] + sub["ctx"]]), torch.tensor([sub["ctx"]]), sub["L"])
+        for _ in range(args.warmup):
+            fn()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            fn()
+        dt = time.perf_counter() - t0
+        val = n1_flops(sub) * args.steps / dt / 1e12
+        sample = "1 sequence x (512 new + 512 cached), 4 heads per step; oracle port of prefix_prefill.py:10-199, torch CPU"
+        print(json.dumps({"impl": "reference", "metric": "prefix_prefill_throughput", "value": round(val, 5),
+                          "unit": "TFLOP/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+                          "ms_per_step": round(dt / args.steps * 1e3, 3), "higher_is_better": True, "scaling": "weak",
+                          "vs_baseline": None, "dtype": "float16", "data": "synthetic",
+                          "config": {"workload": w["name"], "sample": sample},
+                          "cpu_baseline": {"value": round(val, 5), "unit": "TFLOP/s", "cores": torch.get_num_threads(),
+                                           "kind": "port", "sample": sample},
+                          "e2e": {"value": round(val, 5), "unit": "TFLOP/s", "h2d_bytes_per_step": 0,
+                                  "d2h_bytes_per_step": 0}}), flush=True)
+        return 0
+    from vllm_splitwise_b200.prefix_prefill import context_attention_fwd
+    dev = torch.device("cuda:0")
+    torch.cuda.set_device(dev)
+    g = torch.Generator(device=dev).manual_seed(0)
+    scale = D ** -0.5
+    n = B * L
+    mk = lambda *shape: torch.empty(*shape, dtype=torch.float16, device=dev).uniform_(-scale, scale, generator=g)  # noqa: E731
+    nb = (ctx + bs - 1) // bs
+    layers = []
+    for _ in range(2):  # two distinct 0.5 GB K/V sets, alternated: larger than L2
+        layers.append((mk(n, H, D), mk(n, Hkv, D), mk(n, Hkv, D), mk(B * nb, Hkv, D // 8, bs, 8), mk(B * nb, Hkv, D, bs)))
+    bt = torch.randperm(B * nb, device=dev, generator=g).view(B, nb).int()
+    start = (torch.arange(B, device=dev) * L).int()
+    seq = torch.full((B,), L + ctx, dtype=torch.int32, device=dev)
+    cl = torch.full((B,), ctx, dtype=torch.int32, device=dev)
+    o = torch.empty(n, H, D, dtype=torch.float16, device=dev)
+    step = lambda i: context_attention_fwd(*layers[i % 2][:3], o, *layers[i % 2][3:], bt, start, seq, cl, L)  # noqa: E731
+    for i in range(args.warmup):
+        step(i)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(0)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = _lib_launch_count()
+    e0.record()
+    for i in range(args.steps):
+        step(i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    launches = _lib_launch_count() - launches0
+    clocks = sampler.stop()
+    # end to end: q, k, v of the step from pinned host memory, the output read back
+    hq, hk, hv = (t.cpu().pin_memory() for t in layers[0][:3])
+    ho = torch.empty(o.shape, dtype=o.dtype).pin_memory()
+    dq, dk, dv = (torch.empty_like(t) for t in layers[0][:3])
+    e2e_steps = max(3, min(args.steps, 10))
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(e2e_steps):
+        dq.copy_(hq, non_blocking=True); dk.copy_(hk, non_blocking=True); dv.copy_(hv, non_blocking=True)
+        context_attention_fwd(dq, dk, dv, o, *layers[0][3:], bt, start, seq, cl, L)
+        ho.copy_(o, non_blocking=True)
+    e1.record()
+    torch.cuda.synchronize()
+    e2e_ms = e0.elapsed_time(e1) / e2e_steps
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"])
+        peak_src = "MEASURED_PEAKS.json bf16_tflops (cuBLAS bf16 8192^3, burst)"
+    except Exception:
+        peak, peak_src = 2250.0, "fallback: nominal dense bf16 2.25 PFLOP/s (MEASURED_PEAKS.json absent)"
+    tf = flops / ms / 1e9
+    line = {"metric": "prefix_prefill_throughput", "value": round(tf, 1), "unit": "TFLOP/s", "n_gpus": 1,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "float16", "data": "synthetic",
+            "config": {"workload": w["name"], "l2": "inputs larger than L2: two 0.5 GB K/V sets alternated",
+                       "step": "one context_attention_fwd call over the batch (one launch)"},
+            "clocks": clocks,
+            "e2e": {"value": round(flops / e2e_ms / 1e9, 1), "unit": "TFLOP/s",
+                    "h2d_bytes_per_step": int(sum(t.numel() * 2 for t in (hq, hk, hv))),
+                    "d2h_bytes_per_step": int(ho.numel() * 2), "ms_per_step": round(e2e_ms, 4)},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "tensor", "achieved": round(tf, 1), "peak": peak, "unit": "TFLOP/s",
+                         "frac": round(tf / peak, 4), "traffic": None,
+                         "kernel": "tc::context_attn_tc_kernel (tcgen05.mma, TMEM accumulators)", "kernel_ms": round(ms, 4),
+                         "algorithmic_flops_per_launch": flops, "peak_source": peak_src}}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def _lib_launch_count() -> int:
+    from vllm_splitwise_b200 import _lib
+    return int(_lib.load().b200_kv_launch_count())
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=500)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
-    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c2")
+    ap.add_argument("--workload", choices=sorted(WORKLOADS) + ["n1"], default="c2")
     ap.add_argument("--version", choices=["v1", "v2"], default="v1")
     ap.add_argument("--layers", type=int, default=3, help="distinct layer caches cycled by consecutive steps")
     ap.add_argument("--traffic", type=float, default=None,
@@ -478,6 +600,10 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.workload == "n1":
+        if args.steps == 500:
+            args.steps = 50 if args.impl == "b200" else 3
+        return run_n1(args)
     w = WORKLOADS[args.workload]
     return run_reference(args, w) if args.impl == "reference" else run_b200(args, w)
 
