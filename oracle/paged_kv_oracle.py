@@ -13,6 +13,12 @@ Each function restates, in this repository's own words, the reference algorithm 
   * cache writes / block copies: the reference states them only as inline loops inside GPU tests
     (tests/kernels/test_cache.py:85-91,148-158,222-226); restated here and pinned on the GPU box
     bit-for-bit against the reference's compiled kernels (oracle/_ref).
+  * prefix prefill: outputs of the reference's own Triton kernels, run with Triton's CPU interpreter
+    (oracle/make_golden_prefix.py -> tests/golden/prefix_prefill_ref.npz).
+  * decode metadata: outputs of the reference's own ModelRunner._prepare_decode
+    (oracle/make_golden_metadata.py -> tests/golden/decode_metadata_ref.json).
+  * rotary embedding: the reference's RotaryEmbedding._forward (oracle/make_golden.py -> tests/golden/rope_ref.*).
+  * all-reduce: PARITY UNPINNED by a reference run (multi-GPU kernel); restates custom_all_reduce.cuh:139-166.
   * KV transfer: MSCCL++ (third-party, un-vendored, no pinned version:
     docs/source/splitwise/installing_mscclpp.rst:11-18) -- semantics are "same bytes at the same
     block offsets" (csrc/kv_comm_kernels.cu:15); parity for fragmented lists is UNPINNED by any
