@@ -3,7 +3,7 @@
  * Second, independent statement of oracle/paged_kv_oracle.py (the two are cross-checked in
  * tests/test_oracle_golden.py) and the multi-threaded CPU baseline that bench.py can time.
  * Built by oracle/build_oracle.sh into oracle/_build/liboracle_c.so; never linked into or
- * loaded by the product (vllm-splitwise_b200/).
+ * loaded by the product (vllm_splitwise_b200/).
  *
  * Cited reference lines are relative to the reference tree.
  */

@@ -95,7 +95,7 @@ def _bindings():
 def test_compiled_binding_is_built_and_selected():
     """build() compiles lib/_b200_torch.so; `_C` must pick it (the ctypes layer is the spare)."""
     from vllm_splitwise_b200 import _C
-    assert os.path.exists(os.path.join(ROOT, "vllm-splitwise_b200", "lib", "_b200_torch.so"))
+    assert os.path.exists(os.path.join(ROOT, "vllm_splitwise_b200", "lib", "_b200_torch.so"))
     assert _C.BINDING == "torch"
     for sub, names in (("ops", ["paged_attention_v1", "paged_attention_v2"]),
                        ("cache_ops", ["reshape_and_cache", "copy_blocks", "swap_blocks", "convert_fp8_e5m2"]),
@@ -122,7 +122,7 @@ def test_ops_refuse_cpu_tensors(which):
 
 
 def test_product_never_imports_the_oracle():
-    pkg = os.path.join(ROOT, "vllm-splitwise_b200")
+    pkg = os.path.join(ROOT, "vllm_splitwise_b200")
     for dirpath, _, files in os.walk(pkg):
         for f in files:
             if f.endswith((".py", ".cu", ".cuh", ".inc", ".h")):

@@ -33,7 +33,7 @@ _want = os.environ.get("B200_KV_BINDING", "auto")
 _mod = _load_compiled() if _want in ("auto", "torch") else None
 if _mod is None and _want == "torch":
     raise ImportError("B200_KV_BINDING=torch but lib/_b200_torch.so is not built "
-                      "(bash vllm-splitwise_b200/csrc/build_torch_binding.sh)")
+                      "(bash vllm_splitwise_b200/csrc/build_torch_binding.sh)")
 if _mod is not None:
     ops, cache_ops, cuda_utils = _mod.ops, _mod.cache_ops, _mod.cuda_utils
     BINDING = "torch"

@@ -1,13 +1,14 @@
-"""Importable alias of the `vllm-splitwise_b200/` package directory.
+"""B200-native (sm_100a) paged KV-cache hot path of vLLM-splitwise.
 
-The product lives in `vllm-splitwise_b200/` (a hyphen is not a legal Python identifier); this
-module gives it the import name `vllm_splitwise_b200` by pointing `__path__` at that directory.
+Drop-in for the reference's `vllm._C` ops on this path and for its KV-transfer manager:
+
+    from vllm_splitwise_b200._C import ops, cache_ops, cuda_utils      # = vllm._C
+    from vllm_splitwise_b200.paged_attn import PagedAttentionImpl      # = ...attention/ops/paged_attn.py
+    from vllm_splitwise_b200.cache_engine import CacheEngine           # = vllm/worker/cache_engine.py
+    from vllm_splitwise_b200.comm_utils import KVCacheCommManager      # = vllm/worker/comm_utils.py
+
+Everything computes in hand-written CUDA behind the C ABI of `include/b200_kv.h`
+(`lib/libb200kv.so`).  There is no CPU or PyTorch fallback: importing `_C` without the built
+library raises.
 """
-import os as _os
-
-_pkg_dir = _os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))),
-                         "vllm-splitwise_b200")
-__path__ = [_pkg_dir]
-__file__ = _os.path.join(_pkg_dir, "__init__.py")
-with open(__file__) as _f:
-    exec(compile(_f.read(), __file__, "exec"))
+__version__ = "0.1.0"

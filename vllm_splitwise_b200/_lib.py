@@ -128,7 +128,7 @@ def load():
     if not os.path.exists(LIB_PATH):
         raise ImportError(
             f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; "
-            "g.build()'` (or `make -C vllm-splitwise_b200/csrc`). There is no CPU fallback.")
+            "g.build()'` (or `make -C vllm_splitwise_b200/csrc`). There is no CPU fallback.")
     lib = ctypes.CDLL(LIB_PATH)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError here = header/library mismatch
