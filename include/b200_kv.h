@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define B200_KV_ABI_VERSION 1
+#define B200_KV_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define B200_API __attribute__((visibility("default")))
@@ -82,12 +82,14 @@ B200_API uint64_t b200_kv_launch_count(void);
  * v2 only (caller-allocated scratch, reference paged_attn.py:83-93), P = max_num_partitions:
  *   tmp_out [num_seqs, num_heads, P, head_size] T; exp_sums, max_logits f32 [num_seqs, num_heads, P]
  *   partition p covers tokens [512p, 512p+512) exactly as in the reference.
- * Optional workspace (v1 only): the library may split contexts into partitions so that its persistent
- *   grid stays evenly loaded, and combine the partials inside the same kernel; it needs up to
- *   b200_paged_attention_workspace_bytes() bytes of caller-owned scratch (less is fine: the split is
- *   limited to what fits).  The first 256 KiB hold reduce tickets: they must be ZERO before the first
- *   call that uses the buffer and every call leaves them zero again, so one cudaMemset at allocation
- *   is enough; do not share one workspace between calls that may run concurrently.
+ * Optional workspace (v1 only): when the (sequence, kv-head) items of a call cannot fill the persistent grid
+ *   the library splits contexts into partitions and combines the partials inside the same kernel; it needs
+ *   b200_paged_attention_workspace_bytes(args) bytes of caller-owned scratch for exactly these arguments
+ *   (0 when the call is not split; a few MB at most; less is fine: the split is limited to what fits).
+ *   The first 256 KiB hold reduce tickets: they must be ZERO before the first call that uses the buffer
+ *   and every call leaves them zero again, so one cudaMemset at allocation is enough.
+ *   Two calls that may EXECUTE concurrently (different streams; a graph replay against an eager call)
+ *   must not share a workspace: keep one per stream and one per captured graph, as the torch front does.
  *   workspace == NULL disables splitting (never an error).
  * ------------------------------------------------------------------------------------------ */
 typedef struct {
@@ -266,6 +268,45 @@ B200_API int b200_decode_metadata_step(const int32_t* state_block_tables, int32_
                                        int32_t block_size, int32_t sliding_window, int64_t* positions,
                                        int64_t* slot_mapping, int32_t* context_lens, int32_t* block_tables,
                                        int32_t out_blocks, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * One decode step of one attention layer in a single call: [decode metadata ->] RoPE + cache write -> paged
+ * attention, the sequence the reference runs per layer inside its captured decode graphs
+ * (vllm/worker/model_runner.py:274-399 then :826-873; vllm/model_executor/models/llama.py:156-158;
+ * .../attention/ops/paged_attn.py:21-36, 38-111).  Same results, bit for bit, as calling
+ * b200_decode_metadata_step, b200_rotary_embedding_reshape_and_cache (or b200_reshape_and_cache when
+ * cos_sin_cache == NULL) and b200_paged_attention_v1 (v2 when attn.exp_sums != NULL) one after the other;
+ * the launches are chained with programmatic dependent launch so their prologues overlap.
+ *   attn                   the attention call of the step.  attn.query is rotated in place first;
+ *                          attn.block_tables / attn.context_lens are the tensors the metadata kernel WRITES
+ *                          (int32 [num_seqs, attn.max_num_blocks_per_seq] / [num_seqs]) when state_block_tables
+ *                          != NULL, plain inputs otherwise.
+ *   state_*, batch_rows, sliding_window, positions, slot_mapping   as b200_decode_metadata_step;
+ *                          state_block_tables == NULL skips the metadata kernel (layers 2..L of a model step
+ *                          reuse the tensors the first layer's call produced).
+ *   key, value             the step's new K / V rows [num_seqs, num_kv_heads, head_size], row strides in elements.
+ * Never allocates, never synchronises: CUDA-graph capturable.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  b200_paged_attn_args_t attn;
+  const int32_t* state_block_tables; /* NULL: no metadata kernel */
+  int32_t* state_seq_lens;
+  const int32_t* batch_rows;
+  int32_t state_max_blocks_per_seq;
+  int32_t sliding_window;
+  int64_t* positions;    /* int64 [num_seqs]: written by the metadata kernel, read by RoPE */
+  int64_t* slot_mapping; /* int64 [num_seqs]: written by the metadata kernel, read by the cache write */
+  void* key;
+  const void* value;
+  const void* cos_sin_cache; /* [max_position, rot_dim] of the query dtype, or NULL = no rotary embedding */
+  int32_t rot_dim;
+  int32_t is_neox;
+  int64_t key_stride;
+  int64_t value_stride;
+  int64_t num_blocks; /* blocks in key_cache / value_cache (slots beyond are never written) */
+} b200_decode_step_args_t;
+
+B200_API int b200_decode_step(const b200_decode_step_args_t* args, b200_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
  * One-shot all-reduce (sum) over NVLink peer memory: the tensor-parallel reduction after the

@@ -5,8 +5,8 @@ from typing import Dict, List
 
 import torch
 
-from .. import _lib
-from ._common import device_ctx, dtype_code, require_cuda, stream_ptr
+from vllm_splitwise_b200 import _lib
+from vllm_splitwise_b200._C._common import device_ctx, dtype_code, require_cuda, stream_ptr
 
 
 def reshape_and_cache(key: torch.Tensor, value: torch.Tensor, key_cache: torch.Tensor,
@@ -117,7 +117,7 @@ def rotary_embedding_reshape_and_cache(positions: torch.Tensor, query: torch.Ten
                                        slot_mapping: torch.Tensor, kv_cache_dtype: str) -> None:
     """ops.rotary_embedding(positions, query, key, ...) followed by reshape_and_cache(key, value, ...) in one
     call; query/key/value are [..., heads * head_size]."""
-    from ._ctypes_ops import _rotary_shape
+    from .ops import _rotary_shape
     n, hq, hkv, rot, qs, ks = _rotary_shape(positions, query, key, head_size, cos_sin_cache)
     for name, t in (("value", value), ("key_cache", key_cache), ("value_cache", value_cache),
                     ("slot_mapping", slot_mapping)):

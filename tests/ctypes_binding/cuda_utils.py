@@ -1,5 +1,5 @@
 """vllm._C.cuda_utils (reference csrc/pybind.cpp:101-111, csrc/cuda_utils_kernels.cu:5-35)."""
-from .. import _lib
+from vllm_splitwise_b200 import _lib
 
 
 def get_device_attribute(attribute: int, device_id: int) -> int:

@@ -1,4 +1,8 @@
-"""vllm._C.ops on the hot path: paged_attention_v1 / paged_attention_v2.
+"""TEST HELPER -- a second, independent binding of the C ABI (ctypes instead of pybind11), used by the tests to
+prove that include/b200_kv.h is bindable without torch types and that both bindings give identical bits.
+The product binding is vllm_splitwise_b200/csrc/torch_binding.cpp.
+
+vllm._C.ops on the hot path: paged_attention_v1 / paged_attention_v2.
 
 Positional signatures are the reference's (csrc/ops.h:5-34); all tensors are caller-allocated,
 ops write in place and return None, launches go to torch's current stream.
@@ -8,11 +12,9 @@ from typing import Optional
 
 import torch
 
-from .. import _lib
-from ._common import device_ctx, dtype_code, require_cuda, stream_ptr
+from vllm_splitwise_b200 import _lib
+from vllm_splitwise_b200._C._common import device_ctx, dtype_code, require_cuda, stream_ptr
 
-_workspaces = {}  # device index -> uint8 tensor (scratch for the internal split of v1 calls)
-_WORKSPACE_CAP = 256 << 20
 
 
 def _cache_dtype_code(kv_cache_dtype: str, query: torch.Tensor, cache: torch.Tensor) -> int:
@@ -72,16 +74,12 @@ def _detail(a: _lib.PagedAttnArgs, status: int):
 
 
 def _workspace_for(a: _lib.PagedAttnArgs, device: torch.device) -> Optional[torch.Tensor]:
-    need = min(_lib.load().b200_paged_attention_workspace_bytes(ctypes.byref(a)), _WORKSPACE_CAP)
-    ws = _workspaces.get(device.index)
-    if ws is None or ws.numel() < need:
-        if torch.cuda.is_current_stream_capturing():
-            return ws  # never allocate inside a CUDA-graph capture; use what exists (or none)
-        # zero-filled: the head of the workspace holds the in-kernel reduce tickets, which every call
-        # leaves at zero again (include/b200_kv.h)
-        ws = torch.zeros(need, dtype=torch.uint8, device=device)
-        _workspaces[device.index] = ws
-    return ws
+    """Test helper: a fresh zeroed buffer of exactly the size this call needs (never shared between calls;
+    the product binding, csrc/torch_binding.cpp, keeps one per stream and one per captured graph)."""
+    need = _lib.load().b200_paged_attention_workspace_bytes(ctypes.byref(a))
+    if need <= 0:
+        return None
+    return torch.zeros(need, dtype=torch.uint8, device=device)
 
 
 def paged_attention_v1(out: torch.Tensor, query: torch.Tensor, key_cache: torch.Tensor,

@@ -44,12 +44,20 @@ def test_struct_layout_matches_header():
     got = list(map(int, subprocess.run([exe], capture_output=True, text=True, check=True).stdout.split()))
     assert got[0] == ctypes.sizeof(_lib.PagedAttnArgs)
     assert got[1:] == [getattr(_lib.PagedAttnArgs, f).offset for f in fields]
+    # b200_decode_step_args_t too
+    fields = [f[0] for f in _lib.DecodeStepArgs._fields_]
+    prog = '#include <stdio.h>\n#include <stddef.h>\n#include "b200_kv.h"\nint main(){printf("%zu", sizeof(b200_decode_step_args_t));' + \
+        "".join(f'printf(" %zu", offsetof(b200_decode_step_args_t, {f}));' for f in fields) + "return 0;}"
+    subprocess.run(["gcc", "-x", "c", "-", "-I", os.path.join(ROOT, "include"), "-o", exe], input=prog, text=True, check=True)
+    got = list(map(int, subprocess.run([exe], capture_output=True, text=True, check=True).stdout.split()))
+    assert got[0] == ctypes.sizeof(_lib.DecodeStepArgs)
+    assert got[1:] == [getattr(_lib.DecodeStepArgs, f).offset for f in fields]
 
 
 def test_status_strings_and_validation_without_gpu():
     from vllm_splitwise_b200 import _lib
     lib = _lib.load()
-    assert lib.b200_kv_abi_version() == 1
+    assert lib.b200_kv_abi_version() == 2
     assert lib.b200_kv_strerror(_lib.ERR_HEAD_SIZE) == b"Unsupported head size"
     assert lib.b200_kv_strerror(_lib.ERR_BLOCK_SIZE) == b"Unsupported block size"
     assert lib.b200_kv_strerror(_lib.ERR_DTYPE) == b"Unsupported data type"
@@ -85,7 +93,7 @@ def test_status_strings_and_validation_without_gpu():
 def _bindings():
     """(name, ops, cache_ops) for every binding of the C ABI that is built: compiled pybind front, ctypes."""
     from vllm_splitwise_b200 import _C
-    from vllm_splitwise_b200._C import _ctypes_cache_ops, _ctypes_ops
+    from ctypes_binding import cache_ops as _ctypes_cache_ops, ops as _ctypes_ops
     out = [("ctypes", _ctypes_ops, _ctypes_cache_ops)]
     if _C.BINDING == "torch":
         out.append(("torch", _C.ops, _C.cache_ops))
@@ -93,7 +101,7 @@ def _bindings():
 
 
 def test_compiled_binding_is_built_and_selected():
-    """build() compiles lib/_b200_torch.so; `_C` must pick it (the ctypes layer is the spare)."""
+    """build() compiles lib/_b200_torch.so; `_C` must pick it (tests/ctypes_binding is a test helper)."""
     from vllm_splitwise_b200 import _C
     assert os.path.exists(os.path.join(ROOT, "vllm_splitwise_b200", "lib", "_b200_torch.so"))
     assert _C.BINDING == "torch"

@@ -11,7 +11,7 @@ pytestmark = pytest.mark.gpu
 
 def _both():
     from vllm_splitwise_b200 import _C
-    from vllm_splitwise_b200._C import _ctypes_cache_ops, _ctypes_ops
+    from ctypes_binding import cache_ops as _ctypes_cache_ops, ops as _ctypes_ops
     if _C.BINDING != "torch":
         pytest.skip("compiled binding not built")
     return (_C.ops, _C.cache_ops), (_ctypes_ops, _ctypes_cache_ops)

@@ -99,6 +99,32 @@ def test_reshape_and_cache_prefill_sized(cache_ops, kv_cache_factory, dtype, kv_
 
 
 @pytest.mark.parametrize("kv_cache_dtype", ["auto", "fp8_e5m2"])
+@pytest.mark.parametrize("block_size", [8, 16, 24, 32])
+@pytest.mark.parametrize("contiguous", [True, False])
+def test_reshape_and_cache_large_prefill_32_token_tiles(cache_ops, kv_cache_factory, block_size, contiguous, kv_cache_dtype):
+    """Large prefills (ceil(N / 32) * heads >= 32 * SMs CTAs) take the 32-token tile variant of the kernel
+    (csrc/cache_ops.cu launch_reshape_and_cache): 8195 tokens x 32 heads, every block size of the op contract
+    plus 24 -- a block size that does not divide the tile, which must fall back to the element-wise V path --
+    with consecutive and with scattered slots.  Bit-exact against the reference kernel and the oracle."""
+    from oracle import paged_kv_oracle as O
+    _seed(5)
+    dtype = torch.half
+    N, H, D = 8195, 32, 128
+    NB = (N + block_size - 1) // block_size + 64
+    key, value, kc, vc, slots = _rc_inputs(N, H, D, block_size, NB, dtype, kv_cache_dtype, kv_cache_factory,
+                                           pad_every=0 if contiguous else 13, contiguous_slots=contiguous)
+    kc_o, vc_o = kc.cpu().clone(), vc.cpu().clone()
+    kc_r, vc_r = kc.clone(), vc.clone()
+    cache_ops.reshape_and_cache(key, value, kc, vc, slots, kv_cache_dtype)
+    O.reshape_and_cache(key.cpu(), value.cpu(), kc_o, vc_o, slots.cpu(), kv_cache_dtype)
+    assert _same(kc, kc_o) and _same(vc, vc_o)
+    ref = load_ref_cuda()
+    if ref is not None:
+        ref.cache_ops.reshape_and_cache(key, value, kc_r, vc_r, slots, kv_cache_dtype)
+        assert _same(kc, kc_r) and _same(vc, vc_r)
+
+
+@pytest.mark.parametrize("kv_cache_dtype", ["auto", "fp8_e5m2"])
 @pytest.mark.parametrize("dtype", DTYPES)
 @pytest.mark.parametrize("block_size", BLOCK_SIZES)
 @pytest.mark.parametrize("max_prompt_len", [64, 77])

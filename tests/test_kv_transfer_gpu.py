@@ -226,6 +226,31 @@ def test_semaphores_are_counters_and_wait_times_out():
     assert m.kvcache_comm.timed_out()
     with pytest.raises(ValueError):
         m.put(256, 0, 0, 1)
+    # The timeout is not swallowed: the step-boundary check raises, names the semaphore and resynchronises it
+    # (without that, `expected` would stay one ahead and every later wait on semaphore 11 would spin out).
+    from vllm_splitwise_b200.comm_utils import KVWaitTimeout
+    with pytest.raises(KVWaitTimeout) as ei:
+        m.check_timeouts()
+    assert ei.value.sem_ids == [11]
+    assert not m.kvcache_comm.timed_out()
+    m.check_timeouts()  # nothing pending any more
+    # signal-after-timeout: the late transfer of that sequence, then the next wait, complete normally
+    m.kvcache_comm.wait_max_spins = 100000000
+    m.put(11, 0, 2, 3)
+    m.signal_and_flush(11)
+    m.wait(11)
+    torch.cuda.synchronize()
+    assert not m.kvcache_comm.timed_out()
+    assert int(m.kvcache_comm.local_flags[11]) == 1 and m.kvcache_comm.expected[11] == 1
+    # an aborted sequence: the signal arrives but the token side never waits for it -> reset_semaphore realigns
+    m.signal_and_flush(11)
+    torch.cuda.synchronize()
+    m.reset_semaphore(11)
+    assert m.kvcache_comm.expected[11] == 2
+    m.signal_and_flush(11)
+    m.wait(11)
+    torch.cuda.synchronize()
+    assert not m.kvcache_comm.timed_out()
     m.destroy_comm()
 
 

@@ -20,7 +20,7 @@ DTYPES = [torch.half, torch.bfloat16, torch.float]
 
 def _bindings():
     from vllm_splitwise_b200 import _C
-    from vllm_splitwise_b200._C import _ctypes_cache_ops, _ctypes_ops
+    from ctypes_binding import cache_ops as _ctypes_cache_ops, ops as _ctypes_ops
     out = [("ctypes", _ctypes_ops, _ctypes_cache_ops)]
     if _C.BINDING == "torch":
         out.append(("torch", _C.ops, _C.cache_ops))

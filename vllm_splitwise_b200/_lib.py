@@ -67,6 +67,28 @@ class ContextAttnArgs(Structure):
                 + [("dtype", c_int32), ("device", c_int32)])
 
 
+class DecodeStepArgs(Structure):
+    """Mirror of b200_decode_step_args_t (field order and types must match the header)."""
+    _fields_ = [
+        ("attn", PagedAttnArgs),
+        ("state_block_tables", c_void_p),
+        ("state_seq_lens", c_void_p),
+        ("batch_rows", c_void_p),
+        ("state_max_blocks_per_seq", c_int32),
+        ("sliding_window", c_int32),
+        ("positions", c_void_p),
+        ("slot_mapping", c_void_p),
+        ("key", c_void_p),
+        ("value", c_void_p),
+        ("cos_sin_cache", c_void_p),
+        ("rot_dim", c_int32),
+        ("is_neox", c_int32),
+        ("key_stride", c_int64),
+        ("value_stride", c_int64),
+        ("num_blocks", c_int64),
+    ]
+
+
 # name -> (restype, argtypes); every symbol include/b200_kv.h declares
 SIGNATURES = {
     "b200_kv_strerror": (c_char_p, [c_int32]),
@@ -86,6 +108,7 @@ SIGNATURES = {
     "b200_block_tables_append": (c_int32, [c_void_p, c_void_p, c_int32, c_int32, c_void_p]),
     "b200_decode_metadata_step": (c_int32, [c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_void_p,
                                             c_void_p, c_void_p, c_void_p, c_int32, c_void_p]),
+    "b200_decode_step": (c_int32, [POINTER(DecodeStepArgs), c_void_p]),
     "b200_reshape_and_cache": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int32,
                                          c_int32, c_int32, c_int32, c_int32, c_int64, c_int64,
                                          c_int64, c_int32, c_int32, c_void_p]),

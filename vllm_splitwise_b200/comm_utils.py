@@ -72,6 +72,15 @@ def _runs_array(runs: Sequence[Tuple[int, int]]):
     return out
 
 
+class KVWaitTimeout(RuntimeError):
+    """A KV-transfer wait() ran out of polls: the prompt side never signalled these semaphores."""
+
+    def __init__(self, sem_ids) -> None:
+        super().__init__(f"KV wait timed out on semaphore(s) {list(sem_ids)}: the blocks of these sequences did "
+                         "not arrive; results computed from them are invalid")
+        self.sem_ids = list(sem_ids)
+
+
 class KVCacheCommunicator:
     """put / signal / wait on one prompt<->token pair.
 
@@ -100,7 +109,9 @@ class KVCacheCommunicator:
         self.wait_max_spins = wait_max_spins
         self.sent = [0] * MAX_SLOT_IDS       # signals issued per semaphore (prompt side)
         self.expected = [0] * MAX_SLOT_IDS   # signals awaited per semaphore (token side)
-        self.timeout_flag = torch.zeros(1, dtype=torch.int32, device=device)
+        # one sticky flag per semaphore, set by a wait kernel whose bounded spin expired (csrc/kv_transfer.cu);
+        # read by check_timeouts() / timed_out()
+        self.timeout_flags = torch.zeros(MAX_SLOT_IDS, dtype=torch.int32, device=device)
         self._lib = _lib.load()
         # put() batching: the attention backends call put() once per coalesced run per semaphore per layer
         # (reference flash_attn.py:81-86).  With defer_puts the runs of one layer are collected on the host
@@ -227,7 +238,7 @@ class KVCacheCommunicator:
         with torch.cuda.device(self.device):
             # always on the caller's stream: the decode kernels that follow on it must see the blocks
             st = self._lib.b200_kv_wait(self.local_flags.data_ptr() + 8 * sem_id, self.expected[sem_id],
-                                        self.wait_max_spins, self.timeout_flag.data_ptr(),
+                                        self.wait_max_spins, self.timeout_flags.data_ptr() + 4 * sem_id,
                                         torch.cuda.current_stream(self.device).cuda_stream)
         _lib.check(st, "kv wait")
 
@@ -247,8 +258,31 @@ class KVCacheCommunicator:
         self._put(2 * first_layer, 2 * num_layers, runs)
 
     def timed_out(self) -> bool:
-        """True if any wait() expired (synchronises; for tests / health checks)."""
-        return bool(self.timeout_flag.item())
+        """True if any wait() expired since the last check_timeouts()/reset (synchronises)."""
+        return bool(self.timeout_flags.any().item())
+
+    def reset_semaphore(self, sem_id: int) -> None:
+        """Abort / resynchronise one semaphore after a missed or cancelled transfer (synchronises): the next
+        wait(sem_id) expects the signal after the last one that actually ARRIVED, and the timeout flag is cleared.
+        Without this a single missed signal would leave `expected` one ahead for ever and every later wait on the
+        semaphore would spin out its full bound."""
+        self._check_sem(sem_id)
+        torch.cuda.current_stream(self.device).synchronize()
+        self.expected[sem_id] = int(self.local_flags[sem_id].item())
+        self.timeout_flags[sem_id] = 0
+
+    def check_timeouts(self) -> None:
+        """Call at a step boundary on the token side (synchronises).  If a wait() expired, the decode kernels
+        enqueued behind it ran over blocks that never arrived: raise KVWaitTimeout naming the semaphores, after
+        resynchronising them (reset_semaphore) so that the worker can drop those sequences and carry on.
+        The reference's MSCCL++ wait(maxSpinCount) aborts the process on expiry (kv_comm_kernels.cu:7)."""
+        flags = self.timeout_flags.cpu()
+        bad = flags.nonzero().flatten().tolist()
+        if not bad:
+            return
+        for sem in bad:
+            self.reset_semaphore(sem)
+        raise KVWaitTimeout(bad)
 
 
 class KVCacheCommManager:
@@ -369,6 +403,12 @@ class KVCacheCommManager:
 
     def wait(self, sem_id: int) -> None:
         self.kvcache_comm.wait(sem_id)
+
+    def check_timeouts(self) -> None:
+        self.kvcache_comm.check_timeouts()
+
+    def reset_semaphore(self, sem_id: int) -> None:
+        self.kvcache_comm.reset_semaphore(sem_id)
 
     def signal_and_flush(self, sem_id: int) -> None:
         self.kvcache_comm.signal_and_flush(sem_id)

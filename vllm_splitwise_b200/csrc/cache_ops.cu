@@ -26,6 +26,8 @@ void set_last_cuda_error(cudaError_t e, const char* where) {
            cudaGetErrorName(e), cudaGetErrorString(e));
 }
 
+thread_local bool tl_pdl_launch = false;
+
 static std::atomic<unsigned long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
@@ -79,6 +81,8 @@ __global__ void __launch_bounds__(512) reshape_and_cache_token_kernel(
     CT* __restrict__ value_cache, const int64_t* __restrict__ slot_mapping, int64_t key_stride,
     int64_t value_stride, int num_heads, int head_size, int block_size, int64_t num_blocks) {
   constexpr int PER = 16 / (int)sizeof(T);
+  griddep_launch_dependents();  // the attention kernel that follows may set itself up now
+  griddep_wait();               // (launched as a programmatic dependent inside b200_decode_step)
   const int64_t token = blockIdx.x;
   const int n = num_heads * head_size;
   const int n_kvec = n / X;    // 16-byte cache vectors of the K row
@@ -198,7 +202,9 @@ __global__ void __launch_bounds__(256) reshape_and_cache_tile_kernel(
     const int loff = __shfl_sync(0xffffffffu, off, lead & 31);
     const bool ok = t >= TOK || (nt == TOK && base >= 0 && base == lbase && off == loff + (t - lead) && (loff % G) == 0);
     const bool all_ok = __all_sync(0xffffffffu, ok);
-    if (t == 0) s_fast = VEC && all_ok;
+    // whole groups only: a block size that does not divide the tile (e.g. 24 with 32-token tiles) would leave
+    // the tile's last tokens without a group, so it takes the element-wise path
+    if (t == 0) s_fast = VEC && all_ok && (TOK % G == 0);
   }
 
   // ---- K: one 16-byte cache vector per (token, chunk), token-fastest ----
@@ -269,8 +275,10 @@ static int launch_reshape_and_cache(const void* key, const void* value, void* ke
                    (head_size % PER == 0) && (reinterpret_cast<uintptr_t>(value_cache) % 16 == 0) && (block_size % 8 == 0);
 #define B200_RC_LAUNCH(KERNEL, GRID, THREADS, SMEM, ...)                                                  \
   do {                                                                                                    \
-    if (vec) KERNEL<T, CT, FP8, X, true><<<GRID, THREADS, SMEM, stream>>>(__VA_ARGS__);                    \
-    else KERNEL<T, CT, FP8, X, false><<<GRID, THREADS, SMEM, stream>>>(__VA_ARGS__);                       \
+    if (vec) B200_CUDA_TRY(launch_kernel(KERNEL<T, CT, FP8, X, true>, dim3(GRID), dim3(THREADS), SMEM, stream,   \
+                                         tl_pdl_launch, __VA_ARGS__));                                    \
+    else B200_CUDA_TRY(launch_kernel(KERNEL<T, CT, FP8, X, false>, dim3(GRID), dim3(THREADS), SMEM, stream,      \
+                                     tl_pdl_launch, __VA_ARGS__));                                        \
   } while (0)
 #define B200_RC_LAUNCH_TILE(KS, TK, GRID, SMEM, ...)                                                      \
   do {                                                                                                    \

@@ -70,8 +70,45 @@ struct DeviceGuard {
 
 int num_sms(int device);
 
+// ---- programmatic dependent launch (PDL) ----------------------------------------------------
+// The kernels of one decode step (metadata -> RoPE + cache write -> attention) run back to back on one stream.
+// Every one of them executes griddepcontrol.wait before it touches memory a predecessor may have written and
+// griddepcontrol.launch_dependents as soon as it has started, so a successor launched with the programmatic
+// stream-serialization attribute gets its CTAs resident (barrier init, shared-memory carve-up) while the
+// predecessor is still running.  Both instructions are no-ops for a kernel launched the ordinary way.
+// tl_pdl_launch: set by b200_decode_step around its 2nd and 3rd launch; the attention kernel always uses it.
+extern thread_local bool tl_pdl_launch;
+struct PdlScope {
+  bool prev;
+  explicit PdlScope(bool on) : prev(tl_pdl_launch) { tl_pdl_launch = on; }
+  ~PdlScope() { tl_pdl_launch = prev; }
+};
+
+#ifdef __CUDACC__
+// Launch `kern` on `stream`; with pdl the launch carries cudaLaunchAttributeProgrammaticStreamSerialization.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                 bool pdl, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
+
 // ---- device-side PTX helpers --------------------------------------------------------------
 #ifdef __CUDACC__
+
+// PDL: order this grid after the memory of the grid it programmatically depends on / let the next grid start.
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));

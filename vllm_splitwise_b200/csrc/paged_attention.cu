@@ -170,14 +170,21 @@ int dispatch(const b200_paged_attn_args_t* a, const AttnParams& p, const TilePla
   return t.mma ? dispatch_mma(a, p, t.gt, budget, sms, stream) : dispatch_simt(a, p, t.gt, budget, sms, stream);
 }
 
-// Work counters of the persistent kernel: one per launch in flight, handed out round-robin.  A launch
-// leaves its counter at zero, so a slot is reusable as soon as that launch has finished; 1024 slots means
-// a collision needs more than a thousand attention launches in flight at once on one device.
-constexpr unsigned kSchedSlots = 1024;
-__device__ unsigned int g_sched[kSchedSlots];
+// Work counters of the persistent kernel: one per launch in flight.  A launch leaves its counter at zero, so
+// a slot is reusable as soon as that launch has finished.
+//   eager launches    round-robin over kEagerSlots: two launches can only collide if more than a thousand
+//                     attention kernels are EXECUTING at once on one device.
+//   captured launches (the reference captures decode, model_runner.py:826-834) bake the slot address into the
+//                     graph, and a replay may overlap any later eager call or other graph -- so every captured
+//                     launch gets a slot of its own, never handed out again.  When those run out the launch
+//                     falls back to a static round-robin schedule (p.sched == nullptr), which needs no counter.
+constexpr unsigned kEagerSlots = 1024;
+constexpr unsigned kCaptureSlots = 31 * 1024;
+__device__ unsigned int g_sched[kEagerSlots + kCaptureSlots];
 std::atomic<unsigned> g_sched_seq{0};
+std::atomic<unsigned> g_capture_seq[64];
 
-int attach_sched(AttnParams& p) {
+int attach_sched(AttnParams& p, cudaStream_t stream) {
   static unsigned int* base[64] = {nullptr};
   int dev = 0;
   B200_CUDA_TRY(cudaGetDevice(&dev));
@@ -187,7 +194,20 @@ int attach_sched(AttnParams& p) {
     B200_CUDA_TRY(cudaGetSymbolAddress(&sym, g_sched));
     base[dev] = static_cast<unsigned int*>(sym);
   }
-  p.sched = base[dev] + (g_sched_seq.fetch_add(1, std::memory_order_relaxed) % kSchedSlots);
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &cs) != cudaSuccess) {
+    (void)cudaGetLastError();
+    cs = cudaStreamCaptureStatusNone;
+  }
+  static const bool force_static = getenv("B200_ATTN_STATIC_SCHED") != nullptr;  // test knob
+  if (force_static) {
+    p.sched = nullptr;
+  } else if (cs != cudaStreamCaptureStatusNone) {
+    const unsigned k = g_capture_seq[dev].fetch_add(1, std::memory_order_relaxed);
+    p.sched = k < kCaptureSlots ? base[dev] + kEagerSlots + k : nullptr;
+  } else {
+    p.sched = base[dev] + (g_sched_seq.fetch_add(1, std::memory_order_relaxed) % kEagerSlots);
+  }
   return B200_OK;
 }
 
@@ -199,16 +219,26 @@ constexpr int kMaxSplit = 64;
 // items c, c + slots, ...  With equal contexts the call lasts ceil(items / slots) rounds of
 // (partition_blocks + per-item overhead) block times, so choose the partition count that minimises that:
 // it fills the last round without making items so small that the per-item epilogue shows.
-int plan_v1_split(const b200_paged_attn_args_t* a, int tiles_per_seq, int slots, int* partition_blocks) {
+int plan_v1_split(const b200_paged_attn_args_t* a, int tiles_per_seq, int slots, int64_t ws_avail, int* partition_blocks,
+                  int64_t* need_out = nullptr) {
   *partition_blocks = 0;
+  if (need_out) *need_out = 0;
   const long long base_items = (long long)a->num_seqs * tiles_per_seq;
   const int max_blocks = (a->max_context_len + a->block_size - 1) / a->block_size;
-  if (!a->workspace || base_items > kTicketInts || max_blocks < 16) return 1;
+  if (ws_avail <= 0 || base_items > kTicketInts || max_blocks < 16) return 1;
+  auto need_for = [&](int np_eff) {
+    return kTicketBytes + (long long)a->num_seqs * a->num_heads * np_eff *
+                              ((long long)a->head_size * dtype_size(a->query_dtype) + 8) + 64;
+  };
   if (const char* e = getenv("B200_ATTN_SPLIT")) {  // tuning knob: force a partition count
     const int np = std::max(1, std::min(atoi(e), kMaxSplit));
     if (np == 1) return 1;
-    *partition_blocks = (max_blocks + np - 1) / np;
-    return (max_blocks + *partition_blocks - 1) / *partition_blocks;
+    const int pb = (max_blocks + np - 1) / np;
+    const int np_eff = (max_blocks + pb - 1) / pb;
+    if (need_for(np_eff) > ws_avail) return 1;
+    *partition_blocks = pb;
+    if (need_out) *need_out = need_for(np_eff);
+    return np_eff;
   }
   // Measured (profiles/r02_split_sweep.txt): with dynamically scheduled items an unsplit call runs at the HBM
   // ceiling as soon as the items cover ~3/4 of the resident CTAs, and every extra partition costs a few
@@ -221,11 +251,10 @@ int plan_v1_split(const b200_paged_attn_args_t* a, int tiles_per_seq, int slots,
   for (; np > 1; --np) {
     const int pb = (max_blocks + np - 1) / np;
     const int np_eff = (max_blocks + pb - 1) / pb;
-    const long long need = kTicketBytes + (long long)a->num_seqs * a->num_heads * np_eff *
-                                              ((long long)a->head_size * dtype_size(a->query_dtype) + 8) + 64;
-    if (need <= a->workspace_bytes) {
+    if (need_for(np_eff) <= ws_avail) {
       best_np = np_eff;
       best_pb = pb;
+      if (need_out) *need_out = need_for(np_eff);
       break;
     }
   }
@@ -241,10 +270,18 @@ using namespace b200;
 extern "C" {
 
 B200_API int64_t b200_paged_attention_workspace_bytes(const b200_paged_attn_args_t* a) {
-  if (!a || a->num_seqs <= 0 || a->num_heads <= 0) return 0;
-  // tickets + room for the largest split plan_v1_split may choose
-  return kTicketBytes + 64 +
-         (int64_t)a->num_seqs * a->num_heads * kMaxSplit * ((int64_t)a->head_size * dtype_size(a->query_dtype) + 8);
+  // Exactly what a v1 call with these arguments uses (0 when the planner does not split it): the split only
+  // happens when the (sequence, head tile) items cannot fill the resident CTAs, so the partials stay small
+  // (< 2 x resident CTAs x 16 rows), a few MB at most.
+  if (!a || check_common(a) != B200_OK || a->num_seqs <= 0) return 0;
+  const TilePlan tile = plan_tile(a);
+  const int group = a->num_heads / a->num_kv_heads;
+  const int tiles_per_seq = a->num_kv_heads * ((group + tile.gt - 1) / tile.gt);
+  int ctas_per_sm = 2, pb = 0;
+  (void)pick_smem_budget(a, tile, &ctas_per_sm);
+  int64_t need = 0;
+  (void)plan_v1_split(a, tiles_per_seq, ctas_per_sm * num_sms(a->device), INT64_MAX, &pb, &need);
+  return need;
 }
 
 B200_API int b200_paged_attention_v1(const b200_paged_attn_args_t* a, b200_stream_t stream_) {
@@ -261,7 +298,7 @@ B200_API int b200_paged_attention_v1(const b200_paged_attn_args_t* a, b200_strea
   int ctas_per_sm = 2;
   const int budget = pick_smem_budget(a, tile, &ctas_per_sm);
   int pb = 0;
-  const int np = plan_v1_split(a, p.tiles_per_seq, ctas_per_sm * sms, &pb);
+  const int np = plan_v1_split(a, p.tiles_per_seq, ctas_per_sm * sms, a->workspace ? a->workspace_bytes : 0, &pb);
   p.partition_blocks = pb;
   p.max_num_partitions = np;
   p.always_partials = 0;
@@ -277,7 +314,7 @@ B200_API int b200_paged_attention_v1(const b200_paged_attn_args_t* a, b200_strea
     p.max_logits = p.exp_sums + rows;
   }
   p.total_items = (long long)np * a->num_seqs * p.tiles_per_seq;
-  st = attach_sched(p);
+  st = attach_sched(p, stream);
   if (st != B200_OK) return st;
   return dispatch(a, p, tile, budget, sms, stream);
 }
@@ -307,7 +344,7 @@ B200_API int b200_paged_attention_v2(const b200_paged_attn_args_t* a, b200_strea
   const int sms = num_sms(a->device);
   int ctas_per_sm = 2;
   const int budget = pick_smem_budget(a, tile, &ctas_per_sm);
-  st = attach_sched(p);
+  st = attach_sched(p, stream);
   if (st != B200_OK) return st;
   st = dispatch(a, p, tile, budget, sms, stream);
   if (st != B200_OK) return st;

@@ -282,6 +282,9 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_kernel(const __grid_c
     mbar_fence_init();
   }
   __syncthreads();
+  // Everything above overlaps the tail of the previous kernel of the stream when this launch is a programmatic
+  // dependent (it always is: launch_attn); nothing below may run before that kernel's memory is visible.
+  griddep_wait();
 
   if (warp == NW) {
     // ================= producer =================
@@ -308,6 +311,10 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_kernel(const __grid_c
       if (done) break;
       if (it.nblk > 0)
         attn_produce_item<CT>(p, it, pos, lane, stages, Impl::kStageBytes, Impl::kKBytes, full_bar, empty_bar, pol);
+      if (p.sched == nullptr) {  // no counter slot left for this launch (see attach_sched): static round-robin
+        item += gridDim.x;
+        continue;
+      }
       unsigned int raw = 0;
       if (lane == 0) {
         raw = atomicAdd(p.sched, 1u);
@@ -657,7 +664,7 @@ int launch_attn(const AttnParams& p_in, int smem_budget, int sms, cudaStream_t s
   }
   long long grid = (long long)occ_val[dev] * sms;
   if (grid > p.total_items) grid = p.total_items;
-  kern<<<(unsigned)grid, kAttnThreads, smem, stream>>>(p);
+  B200_CUDA_TRY(launch_kernel(kern, dim3((unsigned)grid), dim3(kAttnThreads), (size_t)smem, stream, /*pdl=*/true, p));
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

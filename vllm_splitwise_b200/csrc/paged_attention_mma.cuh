@@ -19,6 +19,8 @@
 // ldmatrix gives for 1-byte data.
 #pragma once
 
+#include <type_traits>
+
 #include "paged_attention.cuh"
 
 namespace b200 {
@@ -111,6 +113,12 @@ struct MmaImpl {
   static constexpr int D = D_, BS = BS_, GT = GT_;
   static constexpr bool HI = GT_ == 16;
   static constexpr bool FP8 = sizeof(CT) == 1;
+  // bf16 queries over an fp8 cache run the f16 tensor-core path (e5m2 widens to f16 exactly, by a byte permute).
+  // bf16 has 8 exponent bits, f16 five: each query row is first scaled by a power of two that brings its
+  // largest magnitude into [1, 2) (exact), and the logit scale carries the inverse, so no query overflows
+  // or flushes where the reference (fp8 -> bf16 widening, fp32 dot; dtype_fp8_e5m2.cuh, attention_utils.cuh:31-37)
+  // would not.  Elements more than 2^24 below their row's maximum round to zero: below fp32 dot-product noise.
+  static constexpr bool NORM = FP8 && sizeof(T) == 2 && !std::is_same<T, __half>::value;
   static constexpr int R = HI ? 2 : 1;     // row sets per thread (head g, head g + 8)
   static constexpr int KS = D / 16;        // k-steps of Q.K^T
   static constexpr int NT = D / 8;         // n-tiles of P.V
@@ -128,7 +136,7 @@ struct MmaImpl {
     float o[NT][2 * R];         // O[head g (+8)][d = 8*tile + 2t, +1]
     uint32_t qa[KS][2 * R];     // A fragments of Q: [k-step][a0, (a1), a2, (a3)]
     float alibi2[R];            // alibi slope * log2(e)
-    float scale2;               // softmax scale * log2(e)
+    float scale2[R];            // softmax scale * log2(e) (* the row's power-of-two query normaliser, NORM)
     int k_lane_off, v_lane_off; // per-lane ldmatrix row offsets (bytes) inside a K / V chunk
   };
 
@@ -148,6 +156,34 @@ struct MmaImpl {
     // 2-byte caches; for fp8 the thread's ldmatrix word holds d = 4t..4t+3, so slots (2t,2t+1) <- d (4t,4t+1)
     // and (2t+8,2t+9) <- d (4t+2,4t+3).
     const T* qrow = static_cast<const T*>(p.q) + (long long)it.seq * p.q_stride + (long long)it.head0 * D;
+    float qmul[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      qmul[r] = 1.f;
+      st.scale2[r] = p.scale * kLog2e;
+    }
+    if constexpr (NORM) {
+      // the quad (t = 0..3) of a row holds all D elements of head g (+8) between them
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const int h = g + 8 * r;
+        float mx = 0.f;
+        if (h < it.ng) {
+          const T* qh = qrow + h * D;
+#pragma unroll
+          for (int kk = 0; kk < KS; ++kk)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) mx = fmaxf(mx, fabsf(to_f32<T>(qh[16 * kk + 4 * t + e])));
+        }
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        int ex = (int)((__float_as_uint(mx) >> 23) & 0xffu) - 127;  // floor(log2(mx)) for normal mx
+        if (!(mx > 0.f) || ex > 127) ex = 0;                        // all-zero row, Inf/NaN: leave as is
+        ex = max(-100, min(100, ex));
+        qmul[r] = __uint_as_float((uint32_t)(127 - ex) << 23);      // 2^-ex
+        st.scale2[r] *= __uint_as_float((uint32_t)(127 + ex) << 23);
+      }
+    }
 #pragma unroll
     for (int kk = 0; kk < KS; ++kk) {
       const int d_lo = FP8 ? 16 * kk + 4 * t : 16 * kk + 2 * t;
@@ -158,8 +194,8 @@ struct MmaImpl {
         float x0 = 0.f, x1 = 0.f, y0 = 0.f, y1 = 0.f;
         if (h < it.ng) {
           const T* qh = qrow + h * D;
-          x0 = to_f32<T>(qh[d_lo]); x1 = to_f32<T>(qh[d_lo + 1]);
-          y0 = to_f32<T>(qh[d_hi]); y1 = to_f32<T>(qh[d_hi + 1]);
+          x0 = to_f32<T>(qh[d_lo]) * qmul[r]; x1 = to_f32<T>(qh[d_lo + 1]) * qmul[r];
+          y0 = to_f32<T>(qh[d_hi]) * qmul[r]; y1 = to_f32<T>(qh[d_hi + 1]) * qmul[r];
         }
         st.qa[kk][r] = pack2<MT>(x0, x1);       // a0 (r=0) / a1 (r=1)
         st.qa[kk][R + r] = pack2<MT>(y0, y1);   // a2 / a3
@@ -168,7 +204,6 @@ struct MmaImpl {
 #pragma unroll
     for (int r = 0; r < R; ++r)
       st.alibi2[r] = (p.alibi_slopes != nullptr && g + 8 * r < it.ng) ? p.alibi_slopes[it.head0 + g + 8 * r] * kLog2e : 0.f;
-    st.scale2 = p.scale * kLog2e;
     const int mi = lane >> 3, rr = lane & 7;
     if constexpr (FP8) {
       // K x2: matrix (mi & 1) = token tile; row rr -> token (rr>>1)*4 + (rr&1) + 2*tile
@@ -244,7 +279,7 @@ struct MmaImpl {
           for (int e = 0; e < 2; ++e) {
             const int tok_in = FP8 ? (4 * t + 2 * nt + e) : (8 * nt + 2 * t + e);
             const int t_idx = blk * BS + sb * 16 + tok_in;
-            float x = (s[0][nt][2 * r + e] + s[1][nt][2 * r + e]) * st.scale2;
+            float x = (s[0][nt][2 * r + e] + s[1][nt][2 * r + e]) * st.scale2[r];
             if (has_alibi) x = fmaf(st.alibi2[r], (float)(t_idx - ctx + 1), x);
             if (last) x = t_idx < ctx ? x : -FLT_MAX;
             sv[nt][e] = x;

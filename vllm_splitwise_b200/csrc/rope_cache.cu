@@ -105,6 +105,8 @@ __global__ void __launch_bounds__(256) rope_reshape_and_cache_token_kernel(
     const int64_t* __restrict__ slot_mapping, int block_size, int64_t num_blocks) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* ks = reinterpret_cast<T*>(smem_raw);  // [num_kv_heads * head_size]
+  griddep_launch_dependents();
+  griddep_wait();  // positions / slot_mapping may come from the decode-metadata kernel right before (b200_decode_step)
   const int64_t token = blockIdx.x;
   const int64_t pos = positions[token];
   const int64_t slot = slot_mapping[token];
@@ -216,6 +218,8 @@ __global__ void __launch_bounds__(512) rope_vec_kernel(
     CT* __restrict__ key_cache, CT* __restrict__ value_cache, const int64_t* __restrict__ slot_mapping, int block_size,
     int64_t num_blocks) {
   constexpr int PER = 16 / (int)sizeof(T);
+  griddep_launch_dependents();
+  griddep_wait();  // positions / slot_mapping may come from the decode-metadata kernel right before (b200_decode_step)
   const int64_t token = blockIdx.x;
   int64_t pos = positions[token];
   if (cache_offsets != nullptr) pos += cache_offsets[token];
@@ -367,9 +371,10 @@ int launch_fused_token(const int64_t* positions, void* query, void* key, const v
                       num_kv_heads * head_size / PER;
     const int threads = std::max(32, std::min((items + 31) / 32 * 32, 512));
 #define B200_FUSED_VEC(NEOX)                                                                                      \
-  rope_vec_kernel<T, CT, FP8, X, NEOX, true><<<(unsigned)num_tokens, threads, 0, stream>>>(                       \
+  B200_CUDA_TRY(launch_kernel(rope_vec_kernel<T, CT, FP8, X, NEOX, true>, dim3((unsigned)num_tokens), dim3(threads), 0, \
+      stream, tl_pdl_launch,                                                                                      \
       positions, nullptr, (T*)query, (T*)key, (const T*)value, (const T*)cos_sin_cache, rot_dim, qs, ks, vs,      \
-      num_heads, num_kv_heads, head_size, (CT*)key_cache, (CT*)value_cache, slots, block_size, num_blocks)
+      num_heads, num_kv_heads, head_size, (CT*)key_cache, (CT*)value_cache, slots, block_size, num_blocks))
     if (neox) B200_FUSED_VEC(true);
     else B200_FUSED_VEC(false);
 #undef B200_FUSED_VEC
@@ -379,9 +384,10 @@ int launch_fused_token(const int64_t* positions, void* query, void* key, const v
   const size_t smem = (size_t)num_kv_heads * head_size * sizeof(T);
   if (smem > 48 * 1024) return B200_ERR_ARG;
 #define B200_FUSED(NEOX)                                                                                          \
-  rope_reshape_and_cache_token_kernel<T, CT, FP8, X, NEOX><<<(unsigned)num_tokens, 256, smem, stream>>>(          \
+  B200_CUDA_TRY(launch_kernel(rope_reshape_and_cache_token_kernel<T, CT, FP8, X, NEOX>, dim3((unsigned)num_tokens),  \
+      dim3(256), smem, stream, tl_pdl_launch,                                                                     \
       positions, (T*)query, (T*)key, (const T*)value, (const T*)cos_sin_cache, rot_dim, qs, ks, vs, num_heads,    \
-      num_kv_heads, head_size, (CT*)key_cache, (CT*)value_cache, slots, block_size, num_blocks)
+      num_kv_heads, head_size, (CT*)key_cache, (CT*)value_cache, slots, block_size, num_blocks))
   if (neox) B200_FUSED(true);
   else B200_FUSED(false);
 #undef B200_FUSED

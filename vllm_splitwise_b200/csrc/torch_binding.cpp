@@ -13,6 +13,7 @@
 
 #include <map>
 #include <mutex>
+#include <tuple>
 #include <vector>
 
 #include "../../include/b200_kv.h"
@@ -96,23 +97,46 @@ b200_paged_attn_args_t fill_args(torch::Tensor& out, torch::Tensor& query, torch
   return a;
 }
 
-// Scratch for the internal split of v1 calls: one zero-initialised buffer per device, grown on demand
-// (never inside a CUDA-graph capture).  The head of it holds reduce tickets the kernel leaves at zero.
-constexpr int64_t kWorkspaceCap = 256ll << 20;
-std::mutex g_ws_mutex;
-std::map<int, torch::Tensor> g_workspaces;
-
-torch::Tensor* workspace_for(const b200_paged_attn_args_t& a, const torch::Tensor& like) {
-  const int64_t need = std::min<int64_t>(b200_paged_attention_workspace_bytes(&a), kWorkspaceCap);
-  std::lock_guard<std::mutex> lock(g_ws_mutex);
-  auto it = g_workspaces.find(a.device);
-  if (it == g_workspaces.end() || it->second.numel() < need) {
-    if (c10::cuda::currentStreamCaptureStatusMayInitCtx() != c10::cuda::CaptureStatus::None)
-      return it == g_workspaces.end() ? nullptr : &it->second;
-    g_workspaces[a.device] = torch::zeros({need}, like.options().dtype(torch::kUInt8));
-    it = g_workspaces.find(a.device);
+// Scratch for the internal split of v1 calls (partials + reduce tickets; b200_kv.h).  Two calls that may execute
+// concurrently must not share it, so there is one buffer per (device, stream) for eager calls and one per
+// (device, stream-capture id) for calls recorded into a CUDA graph: a graph replay can then overlap any eager
+// call or any other graph.  b200_paged_attention_workspace_bytes() is exact for the call's arguments (0 when the
+// planner does not split; a few MB at most).  A buffer that must grow is replaced by a larger zeroed one; the
+// old one goes back to torch's caching allocator, which only reuses it in stream order.  Buffers recorded into a
+// graph are never replaced (the capture id is unique), so a captured pointer stays valid while the graph lives;
+// allocation during capture comes from the graph's private pool, as every other tensor the capture creates.
+struct WsKey {
+  int device;
+  int captured;
+  unsigned long long id;  // stream handle (eager) or capture id
+  bool operator<(const WsKey& o) const {
+    return std::tie(device, captured, id) < std::tie(o.device, o.captured, o.id);
   }
-  return &it->second;
+};
+std::mutex g_ws_mutex;
+std::map<WsKey, torch::Tensor>& workspaces() {
+  static auto* m = new std::map<WsKey, torch::Tensor>();  // never destroyed: tensors must not outlive-race CUDA teardown
+  return *m;
+}
+
+void attach_workspace(b200_paged_attn_args_t& a, const torch::Tensor& like) {
+  if (a.max_context_len < 256 || a.exp_sums != nullptr) return;
+  const int64_t need = b200_paged_attention_workspace_bytes(&a);
+  if (need <= 0) return;
+  const cudaStream_t stream = at::cuda::getCurrentCUDAStream().stream();
+  WsKey key{a.device, 0, (unsigned long long)reinterpret_cast<uintptr_t>(stream)};
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  unsigned long long cap_id = 0;
+  if (cudaStreamGetCaptureInfo(stream, &cs, &cap_id) == cudaSuccess && cs == cudaStreamCaptureStatusActive)
+    key = WsKey{a.device, 1, cap_id};
+  else
+    (void)cudaGetLastError();
+  std::lock_guard<std::mutex> lock(g_ws_mutex);
+  torch::Tensor& ws = workspaces()[key];
+  if (!ws.defined() || ws.numel() < need)
+    ws = torch::zeros({std::max<int64_t>(need, 1 << 20)}, like.options().dtype(torch::kUInt8));
+  a.workspace = ws.data_ptr();
+  a.workspace_bytes = ws.numel();
 }
 
 void paged_attention_v1(torch::Tensor& out, torch::Tensor& query, torch::Tensor& key_cache, torch::Tensor& value_cache,
@@ -122,12 +146,7 @@ void paged_attention_v1(torch::Tensor& out, torch::Tensor& query, torch::Tensor&
   b200_paged_attn_args_t a = fill_args(out, query, key_cache, value_cache, num_kv_heads, scale, block_tables,
                                        context_lens, block_size, max_context_len, alibi_slopes, kv_cache_dtype);
   const at::cuda::OptionalCUDAGuard guard(device_of(query));
-  if (a.max_context_len >= 256) {
-    if (torch::Tensor* ws = workspace_for(a, query)) {
-      a.workspace = ws->data_ptr();
-      a.workspace_bytes = ws->numel();
-    }
-  }
+  attach_workspace(a, query);
   const int st = b200_paged_attention_v1(&a, at::cuda::getCurrentCUDAStream().stream());
   check_status(st, "paged_attention_v1", st == B200_ERR_HEAD_SIZE ? a.head_size : a.block_size);
 }
@@ -327,6 +346,86 @@ void rotary_embedding_reshape_and_cache(torch::Tensor& positions, torch::Tensor&
   check_status(st, "rotary_embedding_reshape_and_cache");
 }
 
+// One decode step of one attention layer in one call (b200_decode_step): [metadata ->] RoPE + cache write ->
+// attention.  query [S, Hq, D], key / value [S, Hkv, D] are the views the model holds after qkv.split
+// (vllm/model_executor/models/llama.py:155): dense in their last two dims, any row stride.
+void decode_step(torch::Tensor& out, torch::Tensor& query, torch::Tensor& key, torch::Tensor& value,
+                 torch::Tensor& key_cache, torch::Tensor& value_cache, int num_kv_heads, float scale,
+                 torch::Tensor& block_tables, torch::Tensor& context_lens, int block_size, int max_context_len,
+                 const c10::optional<torch::Tensor>& alibi_slopes, const std::string& kv_cache_dtype,
+                 torch::Tensor& positions, torch::Tensor& slot_mapping,
+                 const c10::optional<torch::Tensor>& cos_sin_cache, bool is_neox,
+                 const c10::optional<torch::Tensor>& state_block_tables, const c10::optional<torch::Tensor>& state_seq_lens,
+                 const c10::optional<torch::Tensor>& batch_rows, int sliding_window,
+                 const c10::optional<torch::Tensor>& exp_sums, const c10::optional<torch::Tensor>& max_logits,
+                 const c10::optional<torch::Tensor>& tmp_out) {
+  b200_decode_step_args_t d{};
+  d.attn = fill_args(out, query, key_cache, value_cache, num_kv_heads, scale, block_tables, context_lens, block_size,
+                     max_context_len, alibi_slopes, kv_cache_dtype);
+  check_kv_source(key, "key"); check_kv_source(value, "value");
+  TORCH_CHECK(key.scalar_type() == query.scalar_type() && value.scalar_type() == query.scalar_type(),
+              "query, key and value must have the same dtype");
+  TORCH_CHECK(key.size(0) == query.size(0) && value.size(0) == query.size(0) && key.size(1) == num_kv_heads &&
+                  value.size(1) == num_kv_heads && key.size(2) == query.size(2) && value.size(2) == query.size(2),
+              "key/value must be [num_seqs, num_kv_heads, head_size]");
+  require_cuda(positions, "positions"); require_cuda(slot_mapping, "slot_mapping");
+  TORCH_CHECK(positions.scalar_type() == at::ScalarType::Long && positions.is_contiguous() &&
+                  positions.numel() >= query.size(0),
+              "positions must be a contiguous int64 tensor with one entry per sequence");
+  TORCH_CHECK(slot_mapping.scalar_type() == at::ScalarType::Long && slot_mapping.is_contiguous() &&
+                  slot_mapping.numel() >= query.size(0),
+              "slot_mapping must be a contiguous int64 tensor with one entry per sequence");
+  TORCH_CHECK(key_cache.is_contiguous() && value_cache.is_contiguous() && block_tables.is_contiguous() &&
+                  context_lens.is_contiguous(),
+              "key_cache / value_cache / block_tables / context_lens must be contiguous");
+  d.positions = positions.data_ptr<int64_t>();
+  d.slot_mapping = slot_mapping.data_ptr<int64_t>();
+  d.key = key.data_ptr();
+  d.value = value.data_ptr();
+  d.key_stride = key.stride(0);
+  d.value_stride = value.stride(0);
+  d.num_blocks = key_cache.size(0);
+  d.is_neox = is_neox ? 1 : 0;
+  if (cos_sin_cache.has_value() && cos_sin_cache->defined()) {
+    require_cuda(*cos_sin_cache, "cos_sin_cache");
+    TORCH_CHECK(cos_sin_cache->dim() == 2 && cos_sin_cache->is_contiguous() &&
+                    cos_sin_cache->scalar_type() == query.scalar_type(),
+                "cos_sin_cache must be a contiguous [max_position, rot_dim] tensor of the query dtype");
+    d.cos_sin_cache = cos_sin_cache->data_ptr();
+    d.rot_dim = (int32_t)cos_sin_cache->size(1);
+  }
+  if (state_block_tables.has_value() && state_block_tables->defined()) {
+    TORCH_CHECK(state_seq_lens.has_value() && batch_rows.has_value(), "state_seq_lens and batch_rows are required with state_block_tables");
+    require_cuda(*state_block_tables, "state_block_tables"); require_cuda(*state_seq_lens, "state_seq_lens");
+    require_cuda(*batch_rows, "batch_rows");
+    TORCH_CHECK(state_block_tables->scalar_type() == at::ScalarType::Int && state_block_tables->dim() == 2 &&
+                    state_block_tables->is_contiguous() && state_seq_lens->scalar_type() == at::ScalarType::Int &&
+                    state_seq_lens->is_contiguous() && batch_rows->scalar_type() == at::ScalarType::Int &&
+                    batch_rows->is_contiguous() && batch_rows->numel() >= query.size(0),
+                "decode state tensors must be contiguous int32");
+    d.state_block_tables = state_block_tables->data_ptr<int32_t>();
+    d.state_seq_lens = state_seq_lens->data_ptr<int32_t>();
+    d.batch_rows = batch_rows->data_ptr<int32_t>();
+    d.state_max_blocks_per_seq = (int32_t)state_block_tables->size(1);
+    d.sliding_window = sliding_window;
+  }
+  if (exp_sums.has_value() && exp_sums->defined()) {
+    TORCH_CHECK(max_logits.has_value() && tmp_out.has_value(), "v2 scratch: exp_sums, max_logits and tmp_out go together");
+    TORCH_CHECK(exp_sums->scalar_type() == at::ScalarType::Float && max_logits->scalar_type() == at::ScalarType::Float &&
+                    tmp_out->scalar_type() == query.scalar_type() && exp_sums->is_contiguous() &&
+                    max_logits->is_contiguous() && tmp_out->is_contiguous(),
+                "v2 scratch tensors must be contiguous (f32, f32, query dtype)");
+    d.attn.exp_sums = exp_sums->data_ptr<float>();
+    d.attn.max_logits = max_logits->data_ptr<float>();
+    d.attn.tmp_out = tmp_out->data_ptr();
+    d.attn.max_num_partitions = (int32_t)exp_sums->size(2);
+  }
+  const at::cuda::OptionalCUDAGuard guard(device_of(query));
+  attach_workspace(d.attn, query);
+  const int st = b200_decode_step(&d, at::cuda::getCurrentCUDAStream().stream());
+  check_status(st, "decode_step", st == B200_ERR_HEAD_SIZE ? d.attn.head_size : d.attn.block_size);
+}
+
 }  // namespace
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
@@ -334,6 +433,17 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   ops.def("paged_attention_v1", &paged_attention_v1,
           "Compute the attention between an input query and the cached keys/values using PagedAttention.");
   ops.def("paged_attention_v2", &paged_attention_v2, "PagedAttention V2.");
+  ops.def("decode_step", &decode_step,
+          "One decode step of one attention layer: [decode metadata ->] RoPE + cache write -> paged attention",
+          pybind11::arg("out"), pybind11::arg("query"), pybind11::arg("key"), pybind11::arg("value"),
+          pybind11::arg("key_cache"), pybind11::arg("value_cache"), pybind11::arg("num_kv_heads"), pybind11::arg("scale"),
+          pybind11::arg("block_tables"), pybind11::arg("context_lens"), pybind11::arg("block_size"),
+          pybind11::arg("max_context_len"), pybind11::arg("alibi_slopes"), pybind11::arg("kv_cache_dtype"),
+          pybind11::arg("positions"), pybind11::arg("slot_mapping"), pybind11::arg("cos_sin_cache") = pybind11::none(),
+          pybind11::arg("is_neox") = true, pybind11::arg("state_block_tables") = pybind11::none(),
+          pybind11::arg("state_seq_lens") = pybind11::none(), pybind11::arg("batch_rows") = pybind11::none(),
+          pybind11::arg("sliding_window") = 0, pybind11::arg("exp_sums") = pybind11::none(),
+          pybind11::arg("max_logits") = pybind11::none(), pybind11::arg("tmp_out") = pybind11::none());
   ops.def("rotary_embedding", &rotary_embedding, "Apply GPT-NeoX or GPT-J style rotary embedding to query and key");
   ops.def("batched_rotary_embedding", &batched_rotary_embedding,
           "Apply GPT-NeoX or GPT-J style rotary embedding to query and key (supports multiple loras)");

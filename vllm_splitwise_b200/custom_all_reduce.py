@@ -16,6 +16,10 @@ from ._C._common import dtype_code, stream_ptr
 _MAX_CTAS = 160  # rows of the per-CTA barrier array (kMaxCtas2 in csrc/all_reduce.cu)
 
 
+class AllReduceTimeout(RuntimeError):
+    pass
+
+
 class CustomAllreduce:
 
     def __init__(self, rank: int, world_size: int, device, group=None, max_size: int = 8 << 20,
@@ -139,6 +143,15 @@ class CustomAllreduce:
 
     def timed_out(self) -> bool:
         return bool(self.timeout.item())
+
+    def check_timeout(self) -> None:
+        """Call at a step boundary (synchronises).  A kernel whose bounded flag spin expired completed WITHOUT all
+        peers' data, so the sums of that call are wrong: raise, after clearing the flag.  The protocol itself
+        needs no repair -- epochs are monotonic, a late peer's flag satisfies every later call."""
+        if self.timed_out():
+            self.timeout.zero_()
+            raise AllReduceTimeout(f"custom all-reduce on rank {self.rank}: a peer did not arrive within the spin "
+                                   "bound; the results of the affected call(s) are invalid")
 
     def close(self) -> None:
         for base in self._opened:

@@ -51,59 +51,49 @@ def kv_cache_shapes(num_blocks: int, block_size: int, num_kv_heads: int, head_si
             (num_blocks, num_kv_heads, head_size, block_size))
 
 
-def _fill_random_fp8_e5m2(tensor: torch.Tensor, low: float, high: float) -> None:
-    # uniform fp16 values pushed through the cache's own converter: never produces Inf/NaN bytes
-    # (reference vllm/utils.py:311-329)
-    from ._C import cache_ops
-    tmp = torch.empty_like(tensor, dtype=torch.float16)
-    tmp.uniform_(low, high)
-    cache_ops.convert_fp8_e5m2(tmp, tensor)
+def resolve_cache_dtype(cache_dtype, model_dtype=None) -> torch.dtype:
+    """Storage dtype of a KV cache: "auto" follows the model dtype, "fp8_e5m2" is stored as uint8
+    (reference vllm/utils.py:30-35); a torch.dtype passes through."""
+    if isinstance(cache_dtype, torch.dtype):
+        return cache_dtype
+    if cache_dtype == "auto":
+        cache_dtype = model_dtype
+        if isinstance(cache_dtype, torch.dtype):
+            return cache_dtype
+        if cache_dtype not in STR_DTYPE_TO_TORCH_DTYPE:
+            raise ValueError(f"Invalid model dtype: {model_dtype}")
+    if not isinstance(cache_dtype, str) or cache_dtype not in STR_DTYPE_TO_TORCH_DTYPE:
+        raise ValueError(f"Invalid kv cache dtype: {cache_dtype}")
+    return STR_DTYPE_TO_TORCH_DTYPE[cache_dtype]
 
 
-def create_kv_caches_with_random(
-    num_blocks: int,
-    block_size: int,
-    num_layers: int,
-    num_heads: int,
-    head_size: int,
-    cache_dtype: Optional[Union[str, torch.dtype]],
-    model_dtype: Optional[Union[str, torch.dtype]] = None,
-    seed: Optional[int] = 0,
-    device: Optional[str] = "cuda",
-) -> Tuple[List[torch.Tensor], List[torch.Tensor]]:
-    """Test/benchmark fixture with the reference's recipe (vllm/utils.py:332-397):
-    uniform(-D^-0.5, D^-0.5) values in the paged layouts."""
+def _random_cache(shape, dtype: torch.dtype, as_fp8: bool, bound: float, device) -> torch.Tensor:
+    """uniform(-bound, bound) in a paged layout.  fp8 caches are drawn in fp16 and narrowed by the cache's own
+    converter, so no byte pattern is Inf/NaN (the reference fixture's trick, vllm/utils.py:311-329)."""
+    if as_fp8:
+        from ._C import cache_ops
+        out = torch.empty(shape, dtype=torch.uint8, device=device)
+        cache_ops.convert_fp8_e5m2(torch.empty(shape, dtype=torch.float16, device=device).uniform_(-bound, bound), out)
+        return out
+    if not dtype.is_floating_point:
+        raise ValueError(f"Does not support cache of type {dtype}")
+    return torch.empty(shape, dtype=dtype, device=device).uniform_(-bound, bound)
+
+
+def create_kv_caches_with_random(num_blocks: int, block_size: int, num_layers: int, num_heads: int, head_size: int,
+                                 cache_dtype: Optional[Union[str, torch.dtype]],
+                                 model_dtype: Optional[Union[str, torch.dtype]] = None, seed: Optional[int] = 0,
+                                 device: Optional[str] = "cuda") -> Tuple[List[torch.Tensor], List[torch.Tensor]]:
+    """Random per-layer (key_caches, value_caches) for tests and benchmarks: same arguments, value range
+    (+-head_size^-0.5) and draw order (every key cache, then every value cache) as the reference's fixture of the
+    same name (vllm/utils.py:332-397; tests/kernels/conftest.py hands it out as `kv_cache_factory`)."""
     torch.random.manual_seed(seed)
     if torch.cuda.is_available():
         torch.cuda.manual_seed(seed)
-    if isinstance(cache_dtype, str):
-        if cache_dtype == "auto":
-            if isinstance(model_dtype, str):
-                torch_dtype = STR_DTYPE_TO_TORCH_DTYPE[model_dtype]
-            elif isinstance(model_dtype, torch.dtype):
-                torch_dtype = model_dtype
-            else:
-                raise ValueError(f"Invalid model dtype: {model_dtype}")
-        elif cache_dtype in ("half", "bfloat16", "float", "fp8_e5m2"):
-            torch_dtype = STR_DTYPE_TO_TORCH_DTYPE[cache_dtype]
-        else:
-            raise ValueError(f"Invalid kv cache dtype: {cache_dtype}")
-    elif isinstance(cache_dtype, torch.dtype):
-        torch_dtype = cache_dtype
-    else:
-        raise ValueError(f"Invalid kv cache dtype: {cache_dtype}")
-
-    scale = head_size ** -0.5
-    kshape, vshape = kv_cache_shapes(num_blocks, block_size, num_heads, head_size, torch_dtype)
-    key_caches, value_caches = [], []
-    for shape, bucket in ((kshape, key_caches), (vshape, value_caches)):
-        for _ in range(num_layers):
-            t = torch.empty(size=shape, dtype=torch_dtype, device=device)
-            if cache_dtype == "fp8_e5m2":
-                _fill_random_fp8_e5m2(t, -scale, scale)
-            elif torch_dtype in (torch.half, torch.bfloat16, torch.float):
-                t.uniform_(-scale, scale)
-            else:
-                raise ValueError(f"Does not support cache of type {cache_dtype}")
-            bucket.append(t)
-    return key_caches, value_caches
+    dtype = resolve_cache_dtype(cache_dtype, model_dtype)
+    as_fp8 = cache_dtype == "fp8_e5m2"
+    bound = head_size ** -0.5
+    kshape, vshape = kv_cache_shapes(num_blocks, block_size, num_heads, head_size, dtype)
+    keys = [_random_cache(kshape, dtype, as_fp8, bound, device) for _ in range(num_layers)]
+    values = [_random_cache(vshape, dtype, as_fp8, bound, device) for _ in range(num_layers)]
+    return keys, values
