@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- the paged-KV decode hot path on B200, one JSON line per run.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3tp8|c3tp2|c4] [--version v1|v2]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3tp8|c3|c4|long|...] [--version v1|v2]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
         --master-port P bench.py --gpus N --steps K --warmup W
     python bench.py --impl reference ...        # the reference's CPU path (oracle port) on the host cores
@@ -17,15 +17,22 @@ Workload   = BASELINE.json configs[1] (C2: Llama-2-7B decode shape, 32 heads, he
              SURVEY 8e); block tables are replicated.  `--workload c3tp8` etc. run the other configs.
 value      = algorithmic GB/s of the whole job with inputs resident in HBM (bytes formula: BASELINE.md
              section 3), device-timed with CUDA events, max over ranks.
-e2e        = same metric through the reference-facing API (PagedAttentionImpl.reshape_and_cache +
-             forward_decode) with the step's query/key/value/block_tables/context_lens/slot_mapping
-             coming from pinned HOST memory and the output copied back to the host every step, copies
-             and the per-step sync inside the timed region.  (The KV cache itself is the path's
-             persistent device state, as in the reference's CacheEngine.)
+e2e        = the same metric through the repo's composed decode step (decode_step.PipelinedDecodeStep over
+             ops.decode_step): every step copies its packed q/k/v rows from PINNED HOST memory to the device,
+             builds positions / slot_mapping / context_lens / block_tables on the device, runs RoPE fused into
+             the cache write and paged attention, and copies the attention output back to pinned host memory;
+             copies and kernels of neighbouring steps overlap (two steps in flight), the host waits for every
+             step's result.  `e2e.sync_each_step` is the same step as ONE captured graph (H2D -> kernels -> D2H)
+             with a host synchronise after every replay (nothing overlaps).  The context grows by one token per
+             step, as in a real decode loop; bytes are counted per step from the actual context length.
 roofline   = attention kernel only: algorithmic bytes per launch / mean launch duration (CUDA events on
              the launching stream inside the timed region) against MEASURED_PEAKS.json hbm_gbs.
 cpu_baseline = the oracle port of the reference's torch CPU path (tests/kernels/test_attention.py:58-111)
              on the host cores, on a bounded sample of the same workload.
+extra      = the rest of BASELINE.json's metric in the same run (each block carries its own roofline / e2e):
+             N = 1: c3tp8, c3 (unsharded), c4_v1, c4_v2, refbench, long_v2 / long_v1 (ctx 32768);
+             N >= 2: c3_strong (the FIXED C3 problem split by KV head over the N ranks), kv_transfer (ranks
+             0..N/2-1 -> N/2..N-1 through KVCacheCommManager over CUDA IPC; N = 8 is C5), allreduce (N4).
 """
 import argparse
 import json
@@ -54,17 +61,33 @@ WORKLOADS = {
                   S=256, Hq=16, Hkv=2, D=128, bs=16, ctx=4096, dtype="bfloat16", kv="auto"),
     "c3tp2": dict(desc="C3 Llama-2-70B GQA tp=2 shard: 32 q / 4 kv heads, batch 256, ctx 4096, bf16",
                   S=256, Hq=32, Hkv=4, D=128, bs=16, ctx=4096, dtype="bfloat16", kv="auto"),
-    "c3": dict(desc="C3 Llama-2-70B GQA unsharded: 64 q / 8 kv heads, batch 256, ctx 4096, bf16",
+    "c3": dict(desc="C3 Llama-2-70B GQA unsharded: 64 q / 8 kv heads, head 128, block 16, batch 256, ctx 4096, bf16",
                S=256, Hq=64, Hkv=8, D=128, bs=16, ctx=4096, dtype="bfloat16", kv="auto"),
     "c4": dict(desc="C4 Mistral-7B GQA: 32 q / 8 kv heads, head 128, block 16, batch 128, ctx 8192, bf16 query, fp8_e5m2 KV",
                S=128, Hq=32, Hkv=8, D=128, bs=16, ctx=8192, dtype="bfloat16", kv="fp8_e5m2"),
     "refbench": dict(desc="reference benchmark default (benchmarks/kernels/benchmark_paged_attention.py): 64 q / 8 kv heads, "
                           "head 128, block 16, batch 8, ctx 4096, fp16",
                      S=8, Hq=64, Hkv=8, D=128, bs=16, ctx=4096, dtype="float16", kv="auto"),
+    "long": dict(desc="long context: 32 q / 8 kv heads, head 128, block 16, batch 16, ctx 32768, bf16 (the op wrapper picks "
+                      "v2 above 8192 tokens, paged_attn.py:62-63)",
+                 S=16, Hq=32, Hkv=8, D=128, bs=16, ctx=32768, dtype="bfloat16", kv="auto"),
     "small": dict(desc="small batch: 32 q / 8 kv heads, head 128, block 16, batch 4, ctx 8192, bf16 query, fp8_e5m2 KV",
                   S=4, Hq=32, Hkv=8, D=128, bs=16, ctx=8192, dtype="bfloat16", kv="fp8_e5m2"),
     "c1": dict(desc="C1 OPT-125m shape: 12 heads, head 64, block 16, batch 8, ctx 512, fp32",
                S=8, Hq=12, Hkv=12, D=64, bs=16, ctx=512, dtype="float32", kv="auto"),
+}
+
+# what the N = 1 line carries besides the headline workload: (key, workload, version)
+EXTRA_N1 = [("c3tp8", "c3tp8", "v1"), ("c3", "c3", "v1"), ("c4_v1", "c4", "v1"), ("c4_v2", "c4", "v2"),
+            ("refbench", "refbench", "v1"), ("long_v2", "long", "v2"), ("long_v1", "long", "v1")]
+
+# dram__bytes_read.sum + dram__bytes_write.sum per attention launch, taken from the committed `ncu --set full`
+# captures of the same commands (mean of the captured launches) -- NOT measured by this run; the file is named in
+# roofline.traffic_source.  Workloads without a capture report traffic null.
+NCU_TRAFFIC = {
+    "c2": (4_295_847_500 + 4_181_760, "profiles/r03_c2_attn_ncu_full.txt"),
+    "c4": (2_148_911_000 + 4_078_976, "profiles/r03_c4_attn_ncu_full.txt"),
+    "c3tp8": (537_709_952 + 3_330_560, "profiles/r03_c3tp8_attn_ncu_full.txt"),
 }
 
 
@@ -72,13 +95,14 @@ def elt_bytes(name: str) -> int:
     return {"float32": 4, "float16": 2, "bfloat16": 2}[name]
 
 
-def attention_bytes(w) -> int:
+def attention_bytes(w, ctx=None) -> int:
     """Algorithmic bytes of one paged_attention call (SURVEY 8d / BASELINE.md section 3):
     K+V once per KV head + q in + out + block table + context_lens."""
+    ctx = w["ctx"] if ctx is None else ctx
     cache_elt = 1 if w["kv"] == "fp8_e5m2" else elt_bytes(w["dtype"])
-    kv = w["S"] * w["ctx"] * w["Hkv"] * w["D"] * 2 * cache_elt
+    kv = w["S"] * ctx * w["Hkv"] * w["D"] * 2 * cache_elt
     qo = 2 * w["S"] * w["Hq"] * w["D"] * elt_bytes(w["dtype"])
-    tables = w["S"] * math.ceil(w["ctx"] / w["bs"]) * 4 + w["S"] * 4
+    tables = w["S"] * math.ceil(ctx / w["bs"]) * 4 + w["S"] * 4
     return kv + qo + tables
 
 
@@ -88,12 +112,6 @@ def reshape_and_cache_bytes(w) -> int:
     return w["S"] * w["Hkv"] * w["D"] * 2 * (elt_bytes(w["dtype"]) + cache_elt) + w["S"] * 8
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per attention launch from the committed ncu --set full captures
-# of the same commands (profiles/r03_{c2,c4,c3tp8}_attn_ncu_full.txt, mean of the two captured launches); null
-# for workloads without a capture.
-NCU_TRAFFIC = {"c2": 4_295_847_500 + 4_181_760, "c4": 2_148_911_000 + 4_078_976, "c3tp8": 537_709_952 + 3_330_560}
-
-
 def kernel_name(w) -> str:
     """Which consumer the library's dispatch picks (csrc/paged_attention.cu plan_tile)."""
     grouped = w["Hq"] != w["Hkv"] and w["dtype"] != "float32" and w["bs"] in (16, 32)
@@ -101,8 +119,17 @@ def kernel_name(w) -> str:
         "paged_attn_kernel<SimtImpl> (persistent, SIMT consumer)"
 
 
-def step_bytes(w) -> int:
-    return attention_bytes(w) + reshape_and_cache_bytes(w)
+def step_bytes(w, ctx=None) -> int:
+    return attention_bytes(w, ctx) + reshape_and_cache_bytes(w)
+
+
+def workload_config(w, version, layers, world=1, per_gpu_note=True):
+    """The `config` object: the same keys for this arm and for `--impl reference` (the driver compares them)."""
+    return {"workload": w["desc"] + (" per GPU (KV-head shard of an N-times-wider model)" if world > 1 and per_gpu_note else ""),
+            "version": version, "layers_cycled": layers,
+            "l2": "inputs larger than L2: each layer cache is %.2f GB, distinct physical blocks, %d layers cycled"
+                  % (attention_bytes(w) / 1e9, layers),
+            "step": "reshape_and_cache + paged_attention_%s for one layer" % version}
 
 
 def max_over_ranks(values, device, world):
@@ -195,17 +222,20 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------
 # workload construction (device)
 # ---------------------------------------------------------------------------------------------
-def build_device_workload(w, num_layers, device, seed):
+def build_device_workload(w, num_layers, device, seed, spare_blocks=0):
     """Layer caches by the reference fixture recipe (vllm/utils.py:366-392), distinct physical blocks per
-    (sequence, position) in a random permutation (SURVEY 8d rule 1), one spare block per sequence."""
+    (sequence, position) in a random permutation (SURVEY 8d rule 1).  `spare_blocks` extra blocks per sequence
+    back the tokens the e2e decode loop appends."""
     import torch
     from vllm_splitwise_b200.utils import create_kv_caches_with_random
     dt = getattr(torch, w["dtype"])
     S, ctx, bs = w["S"], w["ctx"], w["bs"]
     nblk = math.ceil(ctx / bs)
-    NB = S * nblk
+    ncol = nblk + spare_blocks
+    NB = S * ncol
     g = torch.Generator().manual_seed(seed)
-    bt = torch.randperm(NB, generator=g)[:S * nblk].view(S, nblk).to(torch.int32)
+    table = torch.randperm(NB, generator=g).view(S, ncol).to(torch.int32)
+    bt = table[:, :nblk].contiguous()
     kcs, vcs = create_kv_caches_with_random(NB, bs, num_layers, w["Hkv"], w["D"], w["kv"], dt, seed, device)
     scale = float(w["D"] ** -0.5)
     host = dict(
@@ -216,21 +246,172 @@ def build_device_workload(w, num_layers, device, seed):
         cl=torch.full((S,), ctx, dtype=torch.int32).pin_memory(),
         # the step's new token is the last one of the context: slot = table[(ctx-1)//bs]*bs + (ctx-1)%bs
         slots=(bt[:, (ctx - 1) // bs].long() * bs + (ctx - 1) % bs).pin_memory(),
-        out=torch.empty(S, w["Hq"], w["D"], dtype=dt).pin_memory(),
     )
     dev = {k: v.to(device) for k, v in host.items()}
-    return dict(kcs=kcs, vcs=vcs, host=host, dev=dev, scale=scale, NB=NB)
+    return dict(kcs=kcs, vcs=vcs, host=host, dev=dev, scale=scale, NB=NB, table=table)
 
 
-class Meta:
-    """Duck-typed InputMetadata (vllm/model_executor/input_metadata.py) for the op wrapper."""
+# ---------------------------------------------------------------------------------------------
+# one workload on this rank: device-resident timing + end to end.  Returns per-rank times; the caller takes the
+# max over ranks.
+# ---------------------------------------------------------------------------------------------
+def measure_workload(w, version, steps, warmup, layers, device, seed, barrier, e2e=True, clocks_index=None):
+    import torch
+    from vllm_splitwise_b200 import _lib
+    from vllm_splitwise_b200._C import cache_ops, ops
+    lib = _lib.load()
+    total_e2e_steps = warmup + steps
+    spare = (total_e2e_steps + w["bs"] - 1) // w["bs"] + 1 if e2e else 0  # blocks the e2e decode loops append into
+    wl = build_device_workload(w, layers, device, seed, spare_blocks=spare)
+    d = wl["dev"]
+    S, Hq, D = w["S"], w["Hq"], w["D"]
+    P = math.ceil(w["ctx"] / 512)
+    out = torch.empty_like(d["q"])
+    if version == "v2":
+        tmp = torch.empty(S, Hq, P, D, dtype=out.dtype, device=device)
+        es = torch.empty(S, Hq, P, dtype=torch.float32, device=device)
+        ml = torch.empty_like(es)
 
-    def __init__(self, slot_mapping, block_tables, context_lens, max_context_len, kv_cache_dtype):
-        self.slot_mapping = slot_mapping
-        self.block_tables = block_tables
-        self.context_lens = context_lens
-        self.max_context_len = max_context_len
-        self.kv_cache_dtype = kv_cache_dtype
+    def attention(layer):
+        if version == "v1":
+            ops.paged_attention_v1(out, d["q"], wl["kcs"][layer], wl["vcs"][layer], w["Hkv"], wl["scale"], d["bt"],
+                                   d["cl"], w["bs"], w["ctx"], None, w["kv"])
+        else:
+            ops.paged_attention_v2(out, es, ml, tmp, d["q"], wl["kcs"][layer], wl["vcs"][layer], w["Hkv"], wl["scale"],
+                                   d["bt"], d["cl"], w["bs"], w["ctx"], None, w["kv"])
+
+    def step(i, ev=None):
+        layer = i % layers
+        cache_ops.reshape_and_cache(d["key"], d["value"], wl["kcs"][layer], wl["vcs"][layer], d["slots"], w["kv"])
+        if ev is not None:
+            ev[0].record()
+        attention(layer)
+        if ev is not None:
+            ev[1].record()
+
+    # ---- device-resident timing ----
+    for i in range(warmup):
+        step(i)
+    barrier()
+    attn_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    t_beg, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler = ClockSampler(clocks_index) if clocks_index is not None else None
+    launches0 = lib.b200_kv_launch_count()
+    if sampler:
+        sampler.start()
+    barrier()
+    t_beg.record()
+    for i in range(steps):
+        step(i, attn_ev[i])
+    t_end.record()
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    launches = lib.b200_kv_launch_count() - launches0
+    res = dict(total_ms=t_beg.elapsed_time(t_end), attn_ms=sum(a.elapsed_time(b) for a, b in attn_ev) / steps,
+               launches=int(launches), clocks=clocks, steps=steps)
+    if not e2e:
+        return res
+
+    # ---- end to end through the composed decode step, host buffers ----
+    from vllm_splitwise_b200.decode_metadata import DeviceDecodeState
+    from vllm_splitwise_b200.decode_step import DecodeStepRunner, PipelinedDecodeStep
+    from vllm_splitwise_b200.utils import rotary_cos_sin_cache
+    dt = getattr(torch, w["dtype"])
+    ctx, bs = w["ctx"], w["bs"]
+    ncol = wl["table"].shape[1]
+    max_ctx = ctx + total_e2e_steps + 1
+    state = DeviceDecodeState(S, ncol, bs, device, max_batch=S)
+    state.block_tables.copy_(wl["table"])
+    state.set_batch(list(range(S)))
+    cos_sin = rotary_cos_sin_cache(D, max_ctx + 8, 10000.0, dt, device)
+    runner = DecodeStepRunner(state, Hq, w["Hkv"], D, wl["scale"], dt, w["kv"], cos_sin, True, None)
+    kv_caches = list(zip(wl["kcs"], wl["vcs"]))
+    width = (Hq + 2 * w["Hkv"]) * D
+    qkv_rows = torch.empty(S, width, dtype=dt).uniform_(-wl["scale"], wl["scale"])
+    h2d_bytes = qkv_rows.numel() * qkv_rows.element_size()
+    d2h_bytes = S * Hq * D * qkv_rows.element_size()
+    first_ctx = ctx  # context length of the first TIMED step of each e2e loop
+
+    # (a) one graph per layer cache: H2D -> metadata -> RoPE + cache write -> attention -> D2H; sync after every replay
+    caps = [runner.capture(S, [kv_caches[l]], max_ctx) for l in range(layers)]
+    for c in caps:
+        c.qkv_host[0].copy_(qkv_rows)
+    state.seq_lens.fill_(first_ctx - 1 - warmup)  # the step advances it before use: first timed context == ctx
+    torch.cuda.synchronize()
+    for i in range(warmup):
+        caps[i % layers].replay()
+        caps[i % layers].synchronize()
+    barrier()
+    e_beg, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e_beg.record()
+    for i in range(steps):
+        c = caps[i % layers]
+        c.replay()
+        c.synchronize()  # the caller consumes the step's result on the host
+    e_end.record()
+    barrier()
+    res["e2e_sync_ms"] = e_beg.elapsed_time(e_end)
+    assert int(state.seq_lens[0].item()) == first_ctx - 1 + steps
+
+    # (b) pipelined: copies of neighbouring steps overlap the kernels, two steps in flight
+    pipe = PipelinedDecodeStep(runner, S, kv_caches, max_ctx, depth=2)
+    for s in pipe.slots:
+        s.qkv_host.copy_(qkv_rows)
+    state.seq_lens.fill_(first_ctx - 1 - warmup)
+    torch.cuda.synchronize()
+    for i in range(warmup):
+        pipe.submit(i, i % layers)
+        pipe.result(i)
+    barrier()
+    t0 = time.perf_counter()
+    e_beg.record()
+    for i in range(steps):
+        pipe.submit(warmup + i, (warmup + i) % layers)
+        if i > 0:
+            pipe.result(warmup + i - 1)  # the host consumes every step's output, one step behind the submission
+    pipe.result(warmup + steps - 1)
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    e_end.record()
+    barrier()
+    # device-side span of the pipelined loop; the host-side wall clock is reported next to it
+    res["e2e_pipe_ms"] = max(e_beg.elapsed_time(e_end), wall_ms)
+    res["e2e_bytes"] = sum(step_bytes(w, first_ctx + i) for i in range(steps))
+    res["h2d_bytes"], res["d2h_bytes"] = h2d_bytes, d2h_bytes
+    return res
+
+
+def summarize(w, version, layers, res, world, peak, peak_src, name=None):
+    """JSON block of one measured workload (times in `res` are already the max over ranks)."""
+    steps = res["steps"]
+    job_bytes = step_bytes(w) * steps * world
+    value = job_bytes / (res["total_ms"] * 1e-3) / 1e9
+    achieved = attention_bytes(w) / (res["attn_ms"] * 1e-3) / 1e9
+    traffic, traffic_src = NCU_TRAFFIC.get(name, (None, None)) if version == "v1" else (None, None)
+    block = {
+        "value": round(value, 2), "unit": UNIT, "ms_per_step": round(res["total_ms"] / steps, 5), "steps": steps,
+        "config": workload_config(w, version, layers, world),
+        "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
+                     "frac": round(achieved / peak, 4), "traffic": traffic, "traffic_source": traffic_src,
+                     "kernel": kernel_name(w), "kernel_ms": round(res["attn_ms"], 5),
+                     "algorithmic_bytes_per_launch": attention_bytes(w), "peak_source": peak_src,
+                     "frac_of_8TBps_spec": round(achieved / 8000.0, 4)},
+        "gpu_launches": res["launches"],
+    }
+    if "e2e_pipe_ms" in res:
+        e2e_val = res["e2e_bytes"] * world / (res["e2e_pipe_ms"] * 1e-3) / 1e9
+        sync_val = res["e2e_bytes"] * world / (res["e2e_sync_ms"] * 1e-3) / 1e9
+        block["e2e"] = {"value": round(e2e_val, 2), "unit": UNIT, "h2d_bytes_per_step": res["h2d_bytes"],
+                        "d2h_bytes_per_step": res["d2h_bytes"], "ms_per_step": round(res["e2e_pipe_ms"] / steps, 5),
+                        "frac_of_device_value": round(e2e_val / value, 4),
+                        "through": "decode_step.PipelinedDecodeStep: per step H2D of the packed qkv rows (pinned) -> "
+                                   "device-side metadata -> RoPE + cache write -> paged attention -> D2H of the output; "
+                                   "two steps in flight, the host waits for every result",
+                        "sync_each_step": {"value": round(sync_val, 2),
+                                           "ms_per_step": round(res["e2e_sync_ms"] / steps, 5),
+                                           "frac_of_device_value": round(sync_val / value, 4),
+                                           "through": "DecodeStepRunner.capture: ONE CUDA graph per step (H2D, 3 kernels, "
+                                                      "D2H), host synchronise after every replay"}}
+    return block
 
 
 # ---------------------------------------------------------------------------------------------
@@ -316,13 +497,83 @@ def run_reference(args, w):
     line = {"impl": "reference", "metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt / args.steps * 1e3, 3),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": w["dtype"], "data": "synthetic",
-            "config": {"workload": w["desc"], "version": args.version, "sample": sample},
+            # the same config object as the b200 arm prints (the bounded CPU sample is described in cpu_baseline)
+            "config": workload_config(w, args.version, args.layers, max(1, args.gpus)),
             "cpu_baseline": {"value": round(value, 4), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
                              "sample": sample},
             "e2e": {"value": round(value, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
     return 0
+
+
+# ---------------------------------------------------------------------------------------------
+# N >= 2 extras
+# ---------------------------------------------------------------------------------------------
+def extra_c3_strong(args, rank, world, device, barrier, peak, peak_src, steps):
+    """The FIXED C3 problem (S=256, 64 q / 8 kv heads, ctx 4096, bf16) split by KV head over the `world` ranks
+    (sharding.shard_heads = the reference's partition, vllm/config.py:288-296), no data-path collective; and the
+    unsharded problem on one GPU in the same run, for the strong-scaling efficiency T1 / (N * TN)."""
+    from vllm_splitwise_b200.sharding import shard_heads
+    full = WORKLOADS["c3"]
+    sh = shard_heads(full["Hq"], full["Hkv"], world, rank)
+    shard = dict(full, Hq=sh.num_q, Hkv=sh.num_kv,
+                 desc=f"C3 Llama-2-70B GQA, KV heads sharded over tp={world}: {sh.num_q} q / {sh.num_kv} kv heads per GPU, "
+                      f"head 128, block 16, batch 256, ctx 4096, bf16")
+    r = measure_workload(shard, "v1", steps, args.warmup, args.layers, device, 1000 + rank, barrier)
+    keys = ["total_ms", "attn_ms", "e2e_sync_ms", "e2e_pipe_ms"]
+    for k, v in zip(keys, max_over_ranks([r[k] for k in keys], device, world)):
+        r[k] = v
+    one = measure_workload(full, "v1", steps, args.warmup, args.layers, device, 2000 + rank, barrier)
+    for k, v in zip(keys, max_over_ranks([one[k] for k in keys], device, world)):
+        one[k] = v
+    if rank != 0:
+        return None
+    # whole-job numbers: the N shards together are one C3 layer-call
+    block = summarize(shard, "v1", args.layers, r, world, peak, peak_src)
+    block["config"]["workload"] = shard["desc"]
+    block["scaling"] = "strong"
+    block["unsharded_on_one_gpu"] = {"ms_per_step": round(one["total_ms"] / steps, 5),
+                                     "e2e_ms_per_step": round(one["e2e_pipe_ms"] / steps, 5),
+                                     "value": round(step_bytes(full) * steps / (one["total_ms"] * 1e-3) / 1e9, 2),
+                                     "note": "the same C3 problem, all 64 q / 8 kv heads on one GPU, measured by every "
+                                             "rank in this run (max over ranks)"}
+    block["efficiency_vs_one_gpu"] = {"device": round(one["total_ms"] / (world * r["total_ms"]), 4),
+                                      "e2e": round(one["e2e_pipe_ms"] / (world * r["e2e_pipe_ms"]), 4),
+                                      "formula": "T(1 GPU, unsharded) / (N * T(N GPUs, sharded)), max over ranks"}
+    return block
+
+
+def extra_kv_transfer(args, rank, world, device):
+    """C5: prompt ranks 0..N/2-1 -> token ranks N/2..N-1 through KVCacheCommManager over CUDA IPC."""
+    import torch.distributed as dist
+    from tools import kv_transfer_bench
+    boot = dist.new_group(backend="gloo")
+    lines = kv_transfer_bench.run(rank, world, device, boot, prompts=8, iters=4, warmup=2)
+    if rank != 0:
+        return None
+    out = {"config": lines[0]["config"] if lines else None, "unit": "GB/s per GPU pair",
+           "nvlink_nominal_GBps": kv_transfer_bench.NVLINK_NOMINAL_GBS,
+           "nvlink_measured_peer_copy_GBps": kv_transfer_bench.NVLINK_MEASURED_GBS, "cases": {}}
+    for l in lines:
+        out["cases"][f"{l['pattern']}.{l['mode']}"] = {
+            "value": l["value"], "best": l["best_GBps"], "aggregate": l["aggregate_GBps"],
+            "frac_of_900": l["frac_of_nvlink_nominal_900"], "frac_of_770_measured": l["frac_of_nvlink_measured_770"],
+            "bit_exact": l["bit_exact"], "prompts_in_flight": l["prompts_in_flight"], "ms": l["ms_mean"],
+            "time_to_signal_ms": l.get("time_to_signal_ms"), "max_ctas": l.get("max_ctas"),
+            "runs_per_prompt": l["runs_per_prompt"]}
+    out["bit_exact"] = all(l["bit_exact"] for l in lines)
+    return out
+
+
+def extra_allreduce(args, rank, world, device):
+    import torch.distributed as dist
+    from tools import allreduce_bench
+    lines = allreduce_bench.run(rank, world, device, dist.group.WORLD, iters=100)
+    if rank != 0:
+        return None
+    return {"unit": "us per call, max over ranks", "cases": {l["case"]: {k: v for k, v in l.items() if k != "case"} for l in lines},
+            "bit_exact": all(l["bit_exact_all_ranks"] for l in lines)}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -342,122 +593,71 @@ def run_b200(args, w):
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
 
-    from vllm_splitwise_b200 import _lib
-    from vllm_splitwise_b200._C import cache_ops, ops
-    from vllm_splitwise_b200.paged_attn import PagedAttentionImpl
-    lib = _lib.load()
-
-    wl = build_device_workload(w, args.layers, device, seed=rank)
-    d, h = wl["dev"], wl["host"]
-    S, Hq, D = w["S"], w["Hq"], w["D"]
-    P = math.ceil(w["ctx"] / 512)
-    out = torch.empty_like(d["q"])
-    if args.version == "v2":
-        tmp = torch.empty(S, Hq, P, D, dtype=out.dtype, device=device)
-        es = torch.empty(S, Hq, P, dtype=torch.float32, device=device)
-        ml = torch.empty_like(es)
-
-    def attention(layer):
-        if args.version == "v1":
-            ops.paged_attention_v1(out, d["q"], wl["kcs"][layer], wl["vcs"][layer], w["Hkv"], wl["scale"], d["bt"],
-                                   d["cl"], w["bs"], w["ctx"], None, w["kv"])
-        else:
-            ops.paged_attention_v2(out, es, ml, tmp, d["q"], wl["kcs"][layer], wl["vcs"][layer], w["Hkv"], wl["scale"],
-                                   d["bt"], d["cl"], w["bs"], w["ctx"], None, w["kv"])
-
-    def step(i, ev=None):
-        layer = i % args.layers
-        cache_ops.reshape_and_cache(d["key"], d["value"], wl["kcs"][layer], wl["vcs"][layer], d["slots"], w["kv"])
-        if ev is not None:
-            ev[0].record()
-        attention(layer)
-        if ev is not None:
-            ev[1].record()
-
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident timing ----
-    for i in range(args.warmup):
-        step(i)
-    barrier()
-    attn_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    t_beg, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sampler = ClockSampler(local_rank)
-    launches0 = lib.b200_kv_launch_count()
-    sampler.start()
-    barrier()
-    t_beg.record()
-    for i in range(args.steps):
-        step(i, attn_ev[i])
-    t_end.record()
-    barrier()
-    clocks = sampler.stop()
-    launches = lib.b200_kv_launch_count() - launches0
-    total_ms = t_beg.elapsed_time(t_end)
-    attn_ms = sum(a.elapsed_time(b) for a, b in attn_ev) / args.steps
+    peak, peak_src = measured_peak()
+    t_wall0 = time.perf_counter()
+    keys = ["total_ms", "attn_ms", "e2e_sync_ms", "e2e_pipe_ms"]
+    res = measure_workload(w, args.version, args.steps, args.warmup, args.layers, device, rank, barrier,
+                           clocks_index=local_rank)
+    for k, v in zip(keys, max_over_ranks([res[k] for k in keys], device, world)):
+        res[k] = v
+    head = summarize(w, args.version, args.layers, res, world, peak, peak_src, name=args.workload)
 
-    # ---- end to end through the op wrapper, host buffers ----
-    meta_host_bytes = sum(h[k].numel() * h[k].element_size() for k in ("q", "key", "value", "bt", "cl", "slots"))
-    out_bytes = h["out"].numel() * h["out"].element_size()
+    extra, extra_errors = {}, {}
+    if not args.no_extra:
+        def guarded(name, fn):
+            """An extra block must never take the headline down with it: a failure is recorded, not raised."""
+            try:
+                out = fn()
+                if out is not None:
+                    extra[name] = out
+            except Exception as e:  # noqa: BLE001
+                import traceback
+                extra_errors[name] = f"{type(e).__name__}: {e}"
+                traceback.print_exc(file=sys.stderr)
+            torch.cuda.empty_cache()
 
-    def e2e_step(i):
-        layer = i % args.layers
-        q = h["q"].to(device, non_blocking=True)
-        key = h["key"].to(device, non_blocking=True)
-        value = h["value"].to(device, non_blocking=True)
-        meta = Meta(h["slots"].to(device, non_blocking=True), h["bt"].to(device, non_blocking=True),
-                    h["cl"].to(device, non_blocking=True), w["ctx"], w["kv"])
-        PagedAttentionImpl.reshape_and_cache(key, value, wl["kcs"][layer], wl["vcs"][layer], meta)
-        o = PagedAttentionImpl.forward_decode(q, wl["kcs"][layer], wl["vcs"][layer], meta, w["Hkv"], wl["scale"], None)
-        h["out"].copy_(o, non_blocking=True)
-        torch.cuda.current_stream().synchronize()  # the caller consumes the step's result on the host
+        if world == 1:
+            for key, wname, version in EXTRA_N1:
+                if wname == args.workload and version == args.version:
+                    continue
 
-    for i in range(args.warmup):
-        e2e_step(i)
-    barrier()
-    e_beg, e_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e_beg.record()
-    for i in range(args.steps):
-        e2e_step(i)
-    e_end.record()
-    barrier()
-    e2e_ms = e_beg.elapsed_time(e_end)
-
-    # ---- max over ranks ----
-    total_ms, e2e_ms, attn_ms = max_over_ranks([total_ms, e2e_ms, attn_ms], device, world)
+                def one(wname=wname, version=version, key=key):
+                    ww = WORKLOADS[wname]
+                    r = measure_workload(ww, version, args.extra_steps, args.warmup, args.layers, device, 100 + len(extra),
+                                         barrier)
+                    return summarize(ww, version, args.layers, r, 1, peak, peak_src, name=wname)
+                guarded(key, one)
+        else:
+            guarded("c3_strong", lambda: extra_c3_strong(args, rank, world, device, barrier, peak, peak_src, args.extra_steps))
+            if world % 2 == 0:
+                guarded("kv_transfer", lambda: extra_kv_transfer(args, rank, world, device))
+            guarded("allreduce", lambda: extra_allreduce(args, rank, world, device))
 
     if rank == 0:
-        peak, peak_src = measured_peak()
-        job_bytes = step_bytes(w) * args.steps * world
-        value = job_bytes / (total_ms * 1e-3) / 1e9
-        e2e_val = job_bytes / (e2e_ms * 1e-3) / 1e9
-        achieved = attention_bytes(w) / (attn_ms * 1e-3) / 1e9
         line = {
-            "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": round(total_ms / args.steps, 5), "higher_is_better": True,
+            "metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": w["dtype"] if w["kv"] == "auto" else f"{w['dtype']}+fp8_e5m2_kv",
             "data": "synthetic",
-            "config": {"workload": w["desc"] + (" per GPU (KV-head shard of an N-times-wider model)" if world > 1 else ""),
-                       "version": args.version, "layers_cycled": args.layers,
-                       "l2": "inputs larger than L2: each layer cache is %.2f GB, distinct physical blocks, %d layers cycled"
-                             % (attention_bytes(w) / 1e9, args.layers),
-                       "step": "reshape_and_cache + paged_attention_%s for one layer" % args.version,
-                       "decode_tokens_per_s_per_layer": round(w["S"] * world / (total_ms / args.steps * 1e-3), 1)},
-            "clocks": clocks,
-            "e2e": {"value": round(e2e_val, 2), "unit": UNIT, "h2d_bytes_per_step": meta_host_bytes,
-                    "d2h_bytes_per_step": out_bytes, "ms_per_step": round(e2e_ms / args.steps, 5)},
-            "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s",
-                         "frac": round(achieved / peak, 4), "traffic": args.traffic if args.traffic is not None else NCU_TRAFFIC.get(args.workload),
-                         "kernel": kernel_name(w), "kernel_ms": round(attn_ms, 5),
-                         "algorithmic_bytes_per_launch": attention_bytes(w), "peak_source": peak_src,
-                         "frac_of_8TBps_spec": round(achieved / 8000.0, 4)},
+            "config": head["config"],
+            "decode_tokens_per_s_per_layer": round(w["S"] * world / (head["ms_per_step"] * 1e-3), 1),
+            "clocks": res["clocks"],
+            "e2e": head["e2e"],
+            "gpu_launches": head["gpu_launches"],
+            "roofline": head["roofline"],
         }
+        if extra:
+            line["extra"] = extra
+        if extra_errors:
+            line["extra_errors"] = extra_errors
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(w)
+        line["wall_s"] = round(time.perf_counter() - t_wall0, 1)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -595,8 +795,8 @@ def main():
     ap.add_argument("--workload", choices=sorted(WORKLOADS) + ["n1"], default="c2")
     ap.add_argument("--version", choices=["v1", "v2"], default="v1")
     ap.add_argument("--layers", type=int, default=3, help="distinct layer caches cycled by consecutive steps")
-    ap.add_argument("--traffic", type=float, default=None,
-                    help="ncu dram bytes per attention launch, from profiles/ (null unless given)")
+    ap.add_argument("--extra-steps", type=int, default=50, help="timed steps of every `extra` workload")
+    ap.add_argument("--no-extra", action="store_true", help="headline workload only")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup

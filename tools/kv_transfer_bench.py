@@ -57,18 +57,39 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from vllm_splitwise_b200.comm_utils import KVCacheCommManager
-    from vllm_splitwise_b200.utils import coalesce_blocks, kv_cache_shapes
-
     rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
-    assert world % 2 == 0, "needs an even number of ranks"
-    npw = world // 2
-    is_prompt = rank < npw
-    peer = (rank + npw) % world
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     boot = dist.new_group(backend="gloo")
+    results = run(rank, world, dev, boot, prompts=args.prompts, layers=args.layers, kv_heads=args.kv_heads,
+                  head_size=args.head_size, block_size=args.block_size, prompt_tokens=args.prompt_tokens,
+                  iters=args.iters, warmup=args.warmup, max_ctas=args.max_ctas, modes=args.modes.split(","),
+                  patterns=args.patterns.split(","), nccl_max_prompts=args.nccl_max_prompts, echo=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    return 0 if all(r["bit_exact"] for r in results) else 1
+
+
+def run(rank, world, dev, boot, prompts=8, layers=40, kv_heads=10, head_size=128, block_size=16, prompt_tokens=2048,
+        iters=5, warmup=2, max_ctas=0, modes=("bulk", "per_layer", "ref_api", "nccl"),
+        patterns=("contiguous", "fragmented"), nccl_max_prompts=2, echo=False):
+    """The C5 measurement as a function (bench.py calls it for `extra.kv_transfer`): torch.distributed must be
+    initialised with the NCCL backend, `boot` is a gloo group for the one-time handle exchange.  Returns the
+    result lines (every rank gets the list; the numbers are the max over ranks)."""
+    import argparse as _argparse
+    import torch
+    import torch.distributed as dist
+    from vllm_splitwise_b200.comm_utils import KVCacheCommManager
+    from vllm_splitwise_b200.utils import coalesce_blocks, kv_cache_shapes
+    args = _argparse.Namespace(prompts=prompts, layers=layers, kv_heads=kv_heads, head_size=head_size,
+                               block_size=block_size, prompt_tokens=prompt_tokens, iters=iters, warmup=warmup,
+                               max_ctas=max_ctas, modes=",".join(modes), patterns=",".join(patterns),
+                               nccl_max_prompts=nccl_max_prompts)
+    assert world % 2 == 0, "needs an even number of ranks"
+    npw = world // 2
+    is_prompt = rank < npw
+    peer = (rank + npw) % world
 
     L, H, D, bs = args.layers, args.kv_heads, args.head_size, args.block_size
     blocks_per_prompt = (args.prompt_tokens + bs - 1) // bs
@@ -211,12 +232,11 @@ def main():
                     "config": {"workload": f"C5 Llama-2-13B tp=4 shard: {L} layers, {H} kv heads, head {D}, block {bs}, fp16, "
                                            f"{args.prompt_tokens}-token prompts, {npw} prompt -> {npw} token GPUs"}}
             results.append(line)
-            if rank == 0:
+            if rank == 0 and echo:
                 print(json.dumps(line), flush=True)
     dist.barrier()
     mgr.destroy_comm()
-    dist.destroy_process_group()
-    return 0 if all(r["bit_exact"] for r in results) else 1
+    return results
 
 
 if __name__ == "__main__":

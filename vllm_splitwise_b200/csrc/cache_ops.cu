@@ -27,6 +27,10 @@ void set_last_cuda_error(cudaError_t e, const char* where) {
 }
 
 thread_local bool tl_pdl_launch = false;
+bool pdl_disabled() {
+  static const bool off = getenv("B200_NO_PDL") != nullptr;
+  return off;
+}
 
 static std::atomic<unsigned long long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }

@@ -78,6 +78,7 @@ int num_sms(int device);
 // predecessor is still running.  Both instructions are no-ops for a kernel launched the ordinary way.
 // tl_pdl_launch: set by b200_decode_step around its 2nd and 3rd launch; the attention kernel always uses it.
 extern thread_local bool tl_pdl_launch;
+bool pdl_disabled();  // B200_NO_PDL=1: every launch is an ordinary one (A/B knob)
 struct PdlScope {
   bool prev;
   explicit PdlScope(bool on) : prev(tl_pdl_launch) { tl_pdl_launch = on; }
@@ -98,7 +99,7 @@ inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, 
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = pdl ? 1 : 0;
+  cfg.numAttrs = (pdl && !pdl_disabled()) ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 #endif

@@ -121,3 +121,84 @@ class DecodeStepRunner:
         stream.synchronize()
         torch.cuda.current_stream(self.device).wait_stream(stream)
         return CapturedDecodeStep(graph, stream, qkv_host, qkv, out, out_host, batch)
+
+
+class PipelinedDecodeStep:
+    """The same composed step with the copy engines overlapped: step i's packed qkv rows travel host -> device on
+    one copy stream and step i's output device -> host on another while the kernels of neighbouring steps run,
+    `depth` steps in flight (double buffering by default).  Per step the host issues two async copies and one
+    kernel-only graph launch and waits for the result of an EARLIER step, never for the one it just submitted.
+
+        p = PipelinedDecodeStep(runner, batch, kv_caches, max_context_len)
+        p.slot(n).qkv_host[...] = step n's qkv rows;  p.submit(n, layer);  ...;  out = p.result(n - 1)
+
+    Ordering per slot s = n % depth:  H2D(n) after the kernels of step n - depth (they read qkv[s]);
+    kernels(n) after H2D(n) and after D2H(n - depth) (they overwrite out[s]);  D2H(n) after kernels(n).
+    The kernels of consecutive steps stay in issue order on one compute stream: they share the decode state."""
+
+    class _Slot:
+        pass
+
+    def __init__(self, runner: DecodeStepRunner, batch: int, kv_caches: Sequence[Tuple[torch.Tensor, torch.Tensor]],
+                 max_context_len: int, depth: int = 2, out_blocks: Optional[int] = None) -> None:
+        self.runner, self.batch, self.depth = runner, batch, depth
+        dev = runner.device
+        self.compute, self.h2d, self.d2h = torch.cuda.Stream(dev), torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        width = runner.q_size + 2 * runner.kv_size
+        scratch = runner.v2_scratch(batch, max_context_len)
+        self.slots = []
+        for _ in range(depth):
+            s = self._Slot()
+            s.qkv_host = torch.zeros(batch, width, dtype=runner.dtype).pin_memory()
+            s.out_host = torch.zeros(batch, runner.num_heads, runner.head_size, dtype=runner.dtype).pin_memory()
+            s.qkv = torch.zeros(batch, width, dtype=runner.dtype, device=dev)
+            s.out = torch.zeros(batch, runner.num_heads, runner.head_size, dtype=runner.dtype, device=dev)
+            s.ev_in, s.ev_done, s.ev_out = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
+            s.graphs = []
+            self.slots.append(s)
+        rows = runner.state.batch_rows[:batch]
+        self.compute.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(self.compute):
+            saved = rows.clone()
+            rows.fill_(-1)  # warm-up as padding entries: nothing advances, no cache write (see capture())
+            for s in self.slots:
+                for kc, vc in kv_caches:
+                    runner.layer_step(s.qkv, s.out, kc, vc, batch, max_context_len, True, out_blocks, scratch)
+            rows.copy_(saved)
+            for s in self.slots:
+                for kc, vc in kv_caches:
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=self.compute):
+                        runner.layer_step(s.qkv, s.out, kc, vc, batch, max_context_len, True, out_blocks, scratch)
+                    s.graphs.append(g)
+        self.compute.synchronize()
+        for s in self.slots:  # "already happened" for the first use of every slot
+            s.ev_done.record(self.compute)
+            s.ev_out.record(self.d2h)
+        torch.cuda.current_stream(dev).wait_stream(self.compute)
+
+    def slot(self, n: int):
+        return self.slots[n % self.depth]
+
+    def submit(self, n: int, layer: int = 0) -> None:
+        s = self.slots[n % self.depth]
+        with torch.cuda.stream(self.h2d):
+            self.h2d.wait_event(s.ev_done)
+            s.qkv.copy_(s.qkv_host, non_blocking=True)
+            s.ev_in.record(self.h2d)
+        with torch.cuda.stream(self.compute):
+            self.compute.wait_event(s.ev_in)
+            self.compute.wait_event(s.ev_out)
+            s.graphs[layer].replay()
+            s.ev_done.record(self.compute)
+        with torch.cuda.stream(self.d2h):
+            self.d2h.wait_event(s.ev_done)
+            s.out_host.copy_(s.out, non_blocking=True)
+            s.ev_out.record(self.d2h)
+
+    def result(self, n: int) -> torch.Tensor:
+        """Block until step n's output is in pinned host memory and return it (valid until step n + depth is
+        submitted)."""
+        s = self.slots[n % self.depth]
+        s.ev_out.synchronize()
+        return s.out_host

@@ -97,3 +97,12 @@ def create_kv_caches_with_random(num_blocks: int, block_size: int, num_layers: i
     keys = [_random_cache(kshape, dtype, as_fp8, bound, device) for _ in range(num_layers)]
     values = [_random_cache(vshape, dtype, as_fp8, bound, device) for _ in range(num_layers)]
     return keys, values
+
+
+def rotary_cos_sin_cache(rot_dim: int, max_position: int, base: float, dtype: torch.dtype, device="cpu") -> torch.Tensor:
+    """[max_position, rot_dim]: rot_dim/2 cosines then rot_dim/2 sines of position * base^(-2i/rot_dim) -- the
+    table `rotary_embedding` indexes by position (reference RotaryEmbedding._compute_cos_sin_cache,
+    vllm/model_executor/layers/rotary_embedding.py:67-93, cast to the model dtype as in :63-65)."""
+    inv_freq = base ** (-torch.arange(0, rot_dim, 2, dtype=torch.float, device=device) / rot_dim)
+    angles = torch.outer(torch.arange(max_position, dtype=torch.float, device=device), inv_freq)
+    return torch.cat((angles.cos(), angles.sin()), dim=-1).to(dtype)
