@@ -29,8 +29,11 @@ def peak():
         return 6650.0
 
 
+NCU_MODE = False  # --ncu: one warm-up, no graph replays, no reference kernels (keeps the ncu launch list short)
+
+
 def timeit(fn, iters, nbuf):
-    for i in range(3):
+    for i in range(1 if NCU_MODE else 3):
         fn(i % nbuf)
     torch.cuda.synchronize()
     beg, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -45,6 +48,8 @@ def timeit(fn, iters, nbuf):
 def timeit_graph(fn, nbuf, calls=24, replays=20):
     """GPU time per call with the CPU out of the way: `calls` calls captured into one CUDA graph (the decode
     path is graph-captured in the reference, model_runner.py:826-834), replayed `replays` times."""
+    if NCU_MODE:
+        return None
     side = torch.cuda.Stream()
     side.wait_stream(torch.cuda.current_stream())
     with torch.cuda.stream(side):
@@ -256,11 +261,14 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=50)
     ap.add_argument("--only", default="")
+    ap.add_argument("--ncu", action="store_true", help="short launch list for an ncu capture: our kernels only")
     args = ap.parse_args()
     assert torch.cuda.is_available()
     from vllm_splitwise_b200._C import cache_ops as ours
     from _util import load_ref_cuda
-    ref = load_ref_cuda()
+    global NCU_MODE
+    NCU_MODE = args.ncu
+    ref = None if args.ncu else load_ref_cuda()
     only = set(filter(None, args.only.split(",")))
 
     def want(n):
