@@ -368,6 +368,16 @@ B200_API int b200_kv_put_blocks(const int64_t* src_ptrs, const int64_t* dst_ptrs
                        const int32_t* runs, int32_t num_runs, int64_t block_bytes,
                        int32_t max_ctas, b200_stream_t stream);
 
+/* Process-wide put configuration.  variant: 0 = SIMT (every warp moves 4 KiB chunks with ld.global / st.global),
+ * 1 = bulk (one thread per CTA drives cp.async.bulk global -> shared ring -> peer global), < 0 = keep;
+ * default_ctas: CTAs a put launch uses when max_ctas <= 0 (the transfer overlaps prefill compute, so it is a
+ * budget of SMs, not "all of them"), <= 0 = keep.  Initial values: B200_KV_PUT_VARIANT / B200_KV_PUT_CTAS or
+ * the measured defaults (profiles/r05_kv_put_sweep*.jsonl).  No reference counterpart: MSCCL++'s proxy uses the
+ * copy engine (comm_utils.py:173-197). */
+B200_API int b200_kv_put_configure(int32_t variant, int32_t default_ctas);
+/* The configuration in force (either pointer may be NULL). */
+B200_API int b200_kv_put_config(int32_t* variant, int32_t* default_ctas);
+
 /* Run lists longer than one launch's parameter table (several hundred runs: many fragmented prompts put in
  * one go).  b200_kv_put_table_build (host only, no CUDA call) turns runs [num_runs][2] into a table of
  * 3*num_runs+1 int32 -- starts, lengths, exclusive tile prefix -- that the caller copies to the device ONCE

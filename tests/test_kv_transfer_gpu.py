@@ -297,3 +297,58 @@ def test_two_process_ipc_transfer_bit_exact():
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
     lines = [json.loads(l) for l in res.stdout.splitlines() if l.startswith("{")]
     assert len(lines) == 8 and all(l["bit_exact"] for l in lines)
+
+
+@pytest.fixture
+def put_config():
+    """Set / restore the process-wide put configuration (b200_kv_put_configure)."""
+    import ctypes
+    from vllm_splitwise_b200 import _lib
+    lib = _lib.load()
+    v, c = ctypes.c_int32(), ctypes.c_int32()
+    assert lib.b200_kv_put_config(ctypes.byref(v), ctypes.byref(c)) == 0
+    yield lib
+    assert lib.b200_kv_put_configure(v.value, c.value) == 0
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("ctas", [1, 5, 32, 0])
+@pytest.mark.parametrize("layers_per_launch", [1, 3])
+def test_put_variants_cta_budgets_and_layer_batches(put_config, variant, ctas, layers_per_launch):
+    """Both put kernels (SIMT warp chunks / cp.async.bulk ring), any CTA budget, layers merged into one launch:
+    the same bytes arrive.  Block size 40 960 B (two 20 KiB tiles, ten 4 KiB chunks), mixed run lengths, and a
+    second prompt whose run list is longer than one parameter table (device-table kernels)."""
+    from vllm_splitwise_b200.comm_utils import KVCacheCommManager
+    from vllm_splitwise_b200.utils import coalesce_blocks
+    assert put_config.b200_kv_put_configure(variant, 0) == 0
+    assert put_config.b200_kv_put_configure(7, 0) == -4   # unknown variant: B200_ERR_ARG, configuration unchanged
+    random.seed(5)
+    dev = torch.device("cuda:0")
+    L, NB, hkv, d, bs = 7, 1400, 10, 128, 16
+    src = _caches(L, NB, hkv, d, bs, torch.half, dev, 9)
+    dst = [(torch.zeros_like(k), torch.zeros_like(v)) for k, v in src]
+    before = [(k.clone(), v.clone()) for k, v in dst]
+    a = list(range(3, 60)) + random.sample(range(70, 300), 90)          # mixed runs
+    b = list(range(301, NB, 2))                                         # 550 single-block runs (> 440)
+    m = KVCacheCommManager(rank=0, world_size=2, num_prompt_workers=1)
+    m.setup_comm(L, src, peer_kv_cache=dst, max_ctas=ctas, layers_per_launch=layers_per_launch)
+    lib = m.kvcache_comm._lib
+    n0 = lib.b200_kv_launch_count()
+    ra, rb = tuple(map(tuple, coalesce_blocks(a))), tuple(map(tuple, coalesce_blocks(b)))
+    for layer in range(L):
+        m.put_runs(0, layer, ra)
+    m.signal_and_flush(0)
+    launches_a = lib.b200_kv_launch_count() - n0 - 1
+    assert launches_a == -(-L // layers_per_launch)
+    for layer in range(L - 1):                  # layer L-1 of prompt b is NOT sent
+        for s, n in rb:
+            m.put(1, layer, s, n)
+    m.signal_and_flush(1)
+    m.wait(0)
+    m.wait(1)
+    torch.cuda.synchronize()
+    assert not m.kvcache_comm.timed_out()
+    want = {l: sorted(a + b) for l in range(L - 1)}
+    want[L - 1] = sorted(a)
+    _check(src, dst, before, want)
+    m.destroy_comm()

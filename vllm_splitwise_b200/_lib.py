@@ -132,6 +132,8 @@ SIGNATURES = {
     "b200_kv_enable_peer_access": (c_int32, [c_int32, c_int32]),
     "b200_kv_put_blocks": (c_int32, [c_void_p, c_void_p, c_int32, POINTER(c_int32), c_int32,
                                      c_int64, c_int32, c_void_p]),
+    "b200_kv_put_configure": (c_int32, [c_int32, c_int32]),
+    "b200_kv_put_config": (c_int32, [POINTER(c_int32), POINTER(c_int32)]),
     "b200_kv_put_table_build": (c_int32, [POINTER(c_int32), c_int32, c_int64, c_void_p, POINTER(c_int32),
                                           POINTER(c_int64)]),
     "b200_kv_put_blocks_table": (c_int32, [c_void_p, c_void_p, c_int32, c_void_p, c_int32, c_int32, c_int64, c_int64,

@@ -95,7 +95,7 @@ class KVCacheCommunicator:
                  src_table: Optional[torch.Tensor], dst_table: Optional[torch.Tensor],
                  remote_flags: Optional[int], local_flags: torch.Tensor, my_rank: int, remote_rank: int,
                  max_ctas: int = 0, wait_max_spins: int = 100000000, defer_puts: bool = True,
-                 comm_stream: Optional["torch.cuda.Stream"] = None) -> None:
+                 comm_stream: Optional["torch.cuda.Stream"] = None, layers_per_launch: int = 1) -> None:
         self.block_size = block_size
         self.num_layers = num_layers
         self.device = device
@@ -120,7 +120,17 @@ class KVCacheCommunicator:
         self.defer_puts = defer_puts
         self._pending_layer = -1
         self._pending_runs: List[Tuple[int, int]] = []
+        # layers_per_launch > 1: consecutive layers that put the SAME run list (what the backends do: one block
+        # list per batch, every layer) are merged into one launch of up to that many layers.  A launch then moves
+        # tens of MB instead of ~10 MB, so neither the host's launch rate nor the gaps between kernels limit the
+        # link; the price is that a layer's blocks leave up to layers_per_launch - 1 layers later.
+        self.layers_per_launch = max(1, int(layers_per_launch))
+        self._batch_first, self._batch_count, self._batch_runs = -1, 0, ()
         self._tables: dict = {}
+        self._src_base = src_table.data_ptr() if src_table is not None else 0
+        self._dst_base = dst_table.data_ptr() if dst_table is not None else 0
+        self._dev_index = device.index if device.index is not None else torch.cuda.current_device()
+        self._join = torch.cuda.Event() if comm_stream is not None else None
         # optional side stream: transfers then overlap the prefill compute that follows on the main stream
         # (the reference's host proxy copies asynchronously too); signal rides the same side stream.
         self.comm_stream = comm_stream
@@ -137,13 +147,42 @@ class KVCacheCommunicator:
             self._fence.record(torch.cuda.current_stream(self.device))
             self.comm_stream.wait_event(self._fence)
 
-    def flush(self) -> None:
-        """Launch the deferred puts (one kernel for every run collected for the pending layer)."""
-        if self._pending_runs:
-            layer, runs = self._pending_layer, self._pending_runs
-            self._pending_layer, self._pending_runs = -1, []
+    def join_current_stream(self) -> None:
+        """Side stream only: the caller's current stream waits for everything issued to the comm stream so far."""
+        if self.comm_stream is not None:
+            self._join.record(self.comm_stream)
+            torch.cuda.current_stream(self.device).wait_event(self._join)
+
+    def _close_layer(self) -> None:
+        """The runs collected for the pending layer are complete: merge them into the batch of consecutive
+        layers with the same run list, launching the batch when it is full or cannot be extended."""
+        if not self._pending_runs:
+            return
+        layer, runs = self._pending_layer, tuple(self._pending_runs)
+        self._pending_layer, self._pending_runs = -1, []
+        self._add_layer(layer, runs)
+
+    def _add_layer(self, layer: int, runs: tuple) -> None:
+        if self._batch_count and layer == self._batch_first + self._batch_count and \
+                (runs is self._batch_runs or runs == self._batch_runs):
+            self._batch_count += 1
+        else:
+            self._launch_batch()
+            self._batch_first, self._batch_count, self._batch_runs = layer, 1, runs
+        if self._batch_count >= self.layers_per_launch:
+            self._launch_batch()
+
+    def _launch_batch(self) -> None:
+        if self._batch_count:
+            first, count, runs = self._batch_first, self._batch_count, self._batch_runs
+            self._batch_count = 0
             self._order_after_current()
-            self._put(2 * layer, 2, tuple(runs))
+            self._put(2 * first, 2 * count, runs)
+
+    def flush(self) -> None:
+        """Launch the deferred puts (the pending layer's runs and any batch of merged layers)."""
+        self._close_layer()
+        self._launch_batch()
 
     def _check_sem(self, sem_id: int) -> None:
         if not 0 <= sem_id < MAX_SLOT_IDS:
@@ -178,18 +217,26 @@ class KVCacheCommunicator:
         key = runs if isinstance(runs, tuple) else tuple(map(tuple, runs))
         if len(key) == 0:
             return
-        with torch.cuda.device(self.device):
+        stream = self.comm_stream.cuda_stream if self.comm_stream is not None else \
+            torch.cuda.current_stream(self.device).cuda_stream
+        # this is the per-layer hot call of a prefill worker: switch devices only when the caller sits on another one
+        switch = torch.cuda.current_device() != self._dev_index
+        if switch:
+            prev = torch.cuda.current_device()
+            torch.cuda.set_device(self._dev_index)
+        try:
             if len(key) > self.PARAM_TABLE_RUNS:
                 dev, n, tv, tpb, _ = self._device_table(key)
-                st = self._lib.b200_kv_put_blocks_table(self.src_table.data_ptr() + 8 * first_buf,
-                                                        self.dst_table.data_ptr() + 8 * first_buf, num_bufs,
-                                                        dev.data_ptr(), n, tv, tpb, self.block_size, self.max_ctas,
-                                                        self._stream())
+                st = self._lib.b200_kv_put_blocks_table(self._src_base + 8 * first_buf, self._dst_base + 8 * first_buf,
+                                                        num_bufs, dev.data_ptr(), n, tv, tpb, self.block_size,
+                                                        self.max_ctas, stream)
             else:
                 arr, n = _runs_array(key)
-                st = self._lib.b200_kv_put_blocks(self.src_table.data_ptr() + 8 * first_buf,
-                                                  self.dst_table.data_ptr() + 8 * first_buf, num_bufs, arr, n,
-                                                  self.block_size, self.max_ctas, self._stream())
+                st = self._lib.b200_kv_put_blocks(self._src_base + 8 * first_buf, self._dst_base + 8 * first_buf,
+                                                  num_bufs, arr, n, self.block_size, self.max_ctas, stream)
+        finally:
+            if switch:
+                torch.cuda.set_device(prev)
         _lib.check(st, "kv put")
 
     # ---- reference surface -------------------------------------------------------------
@@ -216,7 +263,7 @@ class KVCacheCommunicator:
             self._order_after_current()
             self._put(2 * layer_id, 2, ((int(block_start), int(num_blocks)),))
             return
-        self.flush()
+        self._close_layer()
         self._pending_layer = layer_id
         self._pending_runs.append((block_start, num_blocks))
 
@@ -244,11 +291,12 @@ class KVCacheCommunicator:
 
     # ---- batched extensions ------------------------------------------------------------
     def put_runs(self, sem_id: int, layer_id: int, runs: Sequence[Tuple[int, int]]) -> None:
-        """All coalesced runs of one layer (K and V) in one launch."""
+        """All coalesced runs of one layer (K and V) in one launch (merged with the neighbouring layers' identical
+        run lists when layers_per_launch > 1; pass the same tuple object every layer to make that check free)."""
         self._check_sem(sem_id)
-        self.flush()
-        self._order_after_current()
-        self._put(2 * layer_id, 2, runs)
+        if self._pending_runs:
+            self._close_layer()
+        self._add_layer(layer_id, runs if isinstance(runs, tuple) else tuple(map(tuple, runs)))
 
     def put_layers(self, sem_id: int, first_layer: int, num_layers: int, runs: Sequence[Tuple[int, int]]) -> None:
         """The same runs for a range of layers (K and V) in one launch."""
@@ -343,7 +391,7 @@ class KVCacheCommManager:
     def setup_comm(self, num_layers: int, kv_cache: List[Tuple[torch.Tensor, torch.Tensor]],
                    peer_kv_cache: Optional[List[Tuple[torch.Tensor, torch.Tensor]]] = None,
                    peer_flags: Optional[torch.Tensor] = None, max_ctas: int = 0, defer_puts: bool = True,
-                   use_comm_stream: bool = False) -> None:
+                   use_comm_stream: bool = False, layers_per_launch: int = 1) -> None:
         device = kv_cache[0][0].device if self.device is None else self.device
         self.device = device
         k0 = kv_cache[0][0]
@@ -382,12 +430,17 @@ class KVCacheCommManager:
         self.kvcache_comm = KVCacheCommunicator(block_size, num_layers, device, src_table, dst_table, remote_flags,
                                                 local_flags, self.rank, self.corr_worker_rank, max_ctas=max_ctas,
                                                 defer_puts=defer_puts,
-                                                comm_stream=torch.cuda.Stream(device) if use_comm_stream else None)
+                                                comm_stream=torch.cuda.Stream(device) if use_comm_stream else None,
+                                                layers_per_launch=layers_per_launch)
         self.put = self.kvcache_comm.put  # the hot call of the prefill loop: one Python frame, not two
 
     def flush(self) -> None:
         """Launch any deferred puts now (optional: call after a layer's put loop for the earliest start)."""
         self.kvcache_comm.flush()
+
+    def join_current_stream(self) -> None:
+        """Side stream only: the caller's stream waits for every put / signal issued so far."""
+        self.kvcache_comm.join_current_stream()
 
     def destroy_comm(self) -> None:
         if self.kvcache_comm is not None:

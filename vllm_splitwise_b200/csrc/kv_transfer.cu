@@ -7,6 +7,8 @@
 // mapping -- no host hop, one launch for any number of (layer, K|V) buffers and block runs --
 // and a system-scope release/acquire flag replaces the semaphore.
 #include <algorithm>
+#include <atomic>
+#include <stdlib.h>
 #include <cuda.h>
 
 #include "common.cuh"
@@ -15,98 +17,211 @@ namespace b200 {
 namespace {
 
 constexpr int kMaxRuns = 440;        // (block_start, num_blocks) runs per launch (kernel params)
-constexpr int kPutThreads = 256;
-constexpr int kTileVecs = 2048;      // 16-byte vectors per tile = 32 KiB
+constexpr int kPutThreads = 512;     // SIMT variant: 16 warps per CTA, each moving its own 4 KiB chunks
+constexpr int kChunkVecs = 256;      // SIMT variant: 16-byte vectors per warp chunk (32 lanes x 8 loads in flight)
+constexpr int kTileVecs = 2048;      // bulk variant: 16-byte vectors per tile = 32 KiB (one ring stage)
+constexpr int kBulkStages = 6;       // bulk variant: 6 x 32 KiB ring per CTA, up to 5 loads in flight
+constexpr int kBulkThreads = 32;
+constexpr int kBulkMaxRuns = 1360;   // bulk variant: run table that still fits beside the ring
 
 struct PutTable {
   int start[kMaxRuns];
   int len[kMaxRuns];
   int num_runs;
   int num_bufs;
-  int tile_vecs;              // 16-byte vectors per tile (host: divides a block evenly when it can)
+  int tile_vecs;              // bulk variant: 16-byte vectors per tile (host: divides a block evenly when it can)
   long long block_bytes;
   const long long* src_ptrs;  // device arrays [num_bufs]
   const long long* dst_ptrs;
 };
 static_assert(sizeof(PutTable) <= 4000, "kernel parameter space");
 
-// CTAs take tiles round-robin; a tile lies inside one (buffer, run).  Each thread keeps up to 8 independent
-// 16-byte loads from local HBM in flight and then issues the stores to the peer mapping.
-__device__ __forceinline__ void put_tiles(const int* start, const int* len, const int* run_tile0, int num_runs,
-                                          int num_bufs, int tv, long long block_bytes, const long long* src_ptrs,
-                                          const long long* dst_ptrs) {
-  const long long tpb = run_tile0[num_runs];
-  const long long total = tpb * num_bufs;
-  for (long long tile = blockIdx.x; tile < total; tile += gridDim.x) {
-    const int buf = (int)(tile / tpb);
-    const int rt = (int)(tile - (long long)buf * tpb);
-    int lo = 0, hi = num_runs - 1;  // last run with run_tile0[r] <= rt
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (run_tile0[mid] <= rt) lo = mid; else hi = mid - 1;
-    }
-    const long long run_vecs = (long long)len[lo] * block_bytes / 16;
-    const long long v0 = (long long)(rt - run_tile0[lo]) * tv;
-    const long long v1 = min(run_vecs, v0 + tv);
-    const long long byte0 = (long long)start[lo] * block_bytes;
+// Stage the run list in shared memory and build the exclusive prefix of work units per run (unit = `unit_vecs`
+// 16-byte vectors; the last unit of a run may be short).  s_tab = [start[n] | len[n] | unit0[n + 1]].
+__device__ __forceinline__ void stage_runs(int* s_tab, const int* g_start, const int* g_len, int n, long long block_vecs,
+                                           int unit_vecs) {
+  __shared__ int s_part[32];
+  int* s_start = s_tab;
+  int* s_len = s_tab + n;
+  int* s_unit0 = s_tab + 2 * n;
+  const int nthr = blockDim.x, per = (n + nthr - 1) / nthr;
+  const int lo = min(n, (int)threadIdx.x * per), hi = min(n, lo + per);
+  int sum = 0;
+  for (int i = lo; i < hi; ++i) {
+    const int st = g_start[i], ln = g_len[i];
+    s_start[i] = st;
+    s_len[i] = ln;
+    sum += (int)(((long long)ln * block_vecs + unit_vecs - 1) / unit_vecs);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int incl = sum;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += v;
+  }
+  if (lane == 31) s_part[warp] = incl;
+  __syncthreads();
+  int base = 0;
+  for (int w = 0; w < warp; ++w) base += s_part[w];
+  int run = base + incl - sum;
+  for (int i = lo; i < hi; ++i) {
+    s_unit0[i] = run;
+    run += (int)(((long long)s_len[i] * block_vecs + unit_vecs - 1) / unit_vecs);
+  }
+  if ((int)threadIdx.x == nthr - 1) s_unit0[n] = base + incl;
+  __syncthreads();
+}
+
+// unit `u` of one buffer -> (run, first vector, end vector) ; unit0 is the exclusive prefix built by stage_runs
+__device__ __forceinline__ int find_run(const int* unit0, int n, int u) {
+  int lo = 0, hi = n - 1;  // last run with unit0[r] <= u
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (unit0[mid] <= u) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+// ---- SIMT variant -------------------------------------------------------------------------------------------
+// Work = num_bufs x (sum of run lengths) blocks cut into 4 KiB chunks.  Every WARP takes chunks on its own
+// (neighbouring warps take neighbouring chunks): 8 independent 16-byte loads per lane from local HBM, then the 8
+// stores into the peer mapping, no CTA-wide barrier in the loop -- so a handful of CTAs keeps megabytes in flight.
+__device__ __forceinline__ void put_chunks(const int* s_tab, int n, int num_bufs, long long block_bytes,
+                                           const long long* src_ptrs, const long long* dst_ptrs) {
+  const int* start = s_tab;
+  const int* len = s_tab + n;
+  const int* unit0 = s_tab + 2 * n;
+  const long long cpb = unit0[n];
+  const long long total = cpb * num_bufs;
+  const int warps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (long long c = (long long)blockIdx.x * warps + warp; c < total; c += (long long)gridDim.x * warps) {
+    const int buf = (int)(c / cpb);
+    const int rc = (int)(c - (long long)buf * cpb);
+    const int r = find_run(unit0, n, rc);
+    const long long run_vecs = (long long)len[r] * block_bytes / 16;
+    const long long v0 = (long long)(rc - unit0[r]) * kChunkVecs;
+    const long long v1 = min(run_vecs, v0 + kChunkVecs);
+    const long long byte0 = (long long)start[r] * block_bytes;
     const uint4* src = reinterpret_cast<const uint4*>(src_ptrs[buf] + byte0);
     uint4* dst = reinterpret_cast<uint4*>(dst_ptrs[buf] + byte0);
-    for (long long i = v0 + threadIdx.x; i < v1; i += 8 * kPutThreads) {
-      uint4 r[8];
+    uint4 v[8];
 #pragma unroll
-      for (int k = 0; k < 8; ++k)
-        if (i + k * kPutThreads < v1) r[k] = ld_nc_v4(src + i + k * kPutThreads);
+    for (int k = 0; k < 8; ++k)
+      if (v0 + lane + 32 * k < v1) v[k] = ld_nc_v4(src + v0 + lane + 32 * k);
 #pragma unroll
-      for (int k = 0; k < 8; ++k)
-        if (i + k * kPutThreads < v1) st_na_v4(dst + i + k * kPutThreads, r[k]);
-    }
+    for (int k = 0; k < 8; ++k)
+      if (v0 + lane + 32 * k < v1) st_na_v4(dst + v0 + lane + 32 * k, v[k]);
   }
 }
 
-// Work = num_bufs x (sum of run lengths) blocks, cut into tiles of `tile_vecs` 16-byte vectors
-// (<= 32 KiB).  CTAs take tiles round-robin; a tile lies inside one (buffer, run).  Each thread keeps up
-// to 8 independent 16-byte loads from local HBM in flight and then issues the stores to the peer mapping.
 __global__ void __launch_bounds__(kPutThreads) kv_put_blocks_kernel(const __grid_constant__ PutTable t) {
-  __shared__ int run_tile0[kMaxRuns + 1];  // exclusive prefix of tiles per run
-  __shared__ int warp_sum[kPutThreads / 32];
-  const int tv = t.tile_vecs;
-  {
-    // block-wide exclusive scan of tiles per run: thread i owns runs 2i and 2i+1 (kMaxRuns <= 2 * threads)
-    static_assert(kMaxRuns <= 2 * kPutThreads, "two runs per thread");
-    const int r0 = 2 * threadIdx.x, r1 = r0 + 1;
-    const int c0 = r0 < t.num_runs ? (int)(((long long)t.len[r0] * t.block_bytes / 16 + tv - 1) / tv) : 0;
-    const int c1 = r1 < t.num_runs ? (int)(((long long)t.len[r1] * t.block_bytes / 16 + tv - 1) / tv) : 0;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int incl = c0 + c1;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const int n = __shfl_up_sync(0xffffffffu, incl, d);
-      if (lane >= d) incl += n;
-    }
-    if (lane == 31) warp_sum[warp] = incl;
-    __syncthreads();
-    int base = 0;
-    for (int w = 0; w < warp; ++w) base += warp_sum[w];
-    const int excl = base + incl - (c0 + c1);
-    if (r0 < t.num_runs) run_tile0[r0] = excl;
-    if (r1 < t.num_runs) run_tile0[r1] = excl + c0;
-    if (threadIdx.x == kPutThreads - 1) run_tile0[t.num_runs] = base + incl;
-    __syncthreads();
-  }
-  put_tiles(t.start, t.len, run_tile0, t.num_runs, t.num_bufs, tv, t.block_bytes, t.src_ptrs, t.dst_ptrs);
+  extern __shared__ __align__(16) int s_tab[];
+  stage_runs(s_tab, t.start, t.len, t.num_runs, t.block_bytes / 16, kChunkVecs);
+  put_chunks(s_tab, t.num_runs, t.num_bufs, t.block_bytes, t.src_ptrs, t.dst_ptrs);
 }
 
-// Same copy for run lists that do not fit the kernel-parameter table: starts, lengths and the exclusive tile
-// prefix live in DEVICE memory (built once per run list by b200_kv_put_table_build and reused for every
-// layer -- the backends put the same block list 2 x num_layers times); each CTA stages them in shared memory.
-// tab = [start[n] | len[n] | tile0[n + 1]] int32.
+// Same copy for run lists that do not fit the kernel-parameter table: starts and lengths live in DEVICE memory
+// (built once per run list by b200_kv_put_table_build and reused for every layer -- the backends put the same
+// block list 2 x num_layers times).  tab = [start[n] | len[n] | host-side tile prefix (unused here)] int32.
 __global__ void __launch_bounds__(kPutThreads) kv_put_blocks_table_kernel(
+    const int* __restrict__ tab, int num_runs, int num_bufs, long long block_bytes,
+    const long long* __restrict__ src_ptrs, const long long* __restrict__ dst_ptrs) {
+  extern __shared__ __align__(16) int s_tab[];
+  stage_runs(s_tab, tab, tab + num_runs, num_runs, block_bytes / 16, kChunkVecs);
+  put_chunks(s_tab, num_runs, num_bufs, block_bytes, src_ptrs, dst_ptrs);
+}
+
+// ---- bulk-copy variant ----------------------------------------------------------------------------------------
+// One thread per CTA drives the TMA engine: tiles (<= 32 KiB, inside one (buffer, run)) travel global -> shared
+// memory ring (cp.async.bulk + mbarrier) -> peer global memory (cp.async.bulk.global.shared::cta), up to
+// kBulkStages - 1 loads in flight per CTA.  No registers hold data and no warp spins on loads, so an SM that runs
+// one of these CTAs keeps its issue slots for the prefill kernels the transfer overlaps.
+__device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
+
+struct BulkShared {
+  uint64_t full[kBulkStages];
+  unsigned long long dst[kBulkStages];
+  uint32_t bytes[kBulkStages];
+};
+
+__device__ __forceinline__ void put_tiles_bulk(uint8_t* ring, BulkShared* sh, const int* s_tab, int n, int num_bufs, int tv,
+                                               long long block_bytes, const long long* src_ptrs,
+                                               const long long* dst_ptrs) {
+  const int* start = s_tab;
+  const int* len = s_tab + n;
+  const int* unit0 = s_tab + 2 * n;
+  const long long tpb = unit0[n];
+  const long long total = tpb * num_bufs;
+  if (threadIdx.x != 0 || blockIdx.x >= total) return;
+  const long long n_my = (total - blockIdx.x + gridDim.x - 1) / gridDim.x;
+  const uint64_t policy = l2_policy_evict_first();
+  auto issue_load = [&](long long k) {  // k-th tile of this CTA into stage k % kBulkStages
+    const long long tile = blockIdx.x + k * gridDim.x;
+    const int buf = (int)(tile / tpb);
+    const int rt = (int)(tile - (long long)buf * tpb);
+    const int r = find_run(unit0, n, rt);
+    const long long run_vecs = (long long)len[r] * block_bytes / 16;
+    const long long v0 = (long long)(rt - unit0[r]) * tv;
+    const long long v1 = min(run_vecs, v0 + tv);
+    const long long byte0 = (long long)start[r] * block_bytes + v0 * 16;
+    const uint32_t bytes = (uint32_t)((v1 - v0) * 16);
+    const int s = (int)(k % kBulkStages);
+    sh->dst[s] = (unsigned long long)(dst_ptrs[buf] + byte0);
+    sh->bytes[s] = bytes;
+    mbar_arrive_expect_tx(&sh->full[s], bytes);
+    bulk_g2s(ring + (size_t)s * kTileVecs * 16, reinterpret_cast<const void*>(src_ptrs[buf] + byte0), bytes, &sh->full[s],
+             policy);
+  };
+  const long long pro = n_my < kBulkStages ? n_my : kBulkStages;
+  for (long long k = 0; k < pro; ++k) issue_load(k);
+  for (long long k = 0; k < n_my; ++k) {
+    const int s = (int)(k % kBulkStages);
+    mbar_wait(&sh->full[s], (uint32_t)((k / kBulkStages) & 1));
+    bulk_s2g(reinterpret_cast<void*>(sh->dst[s]), ring + (size_t)s * kTileVecs * 16, sh->bytes[s]);
+    bulk_commit();
+    // the stage of tile k-1 is free once its store has read shared memory (all groups but the newest are done reading)
+    if (k >= 1 && k - 1 + kBulkStages < n_my) {
+      bulk_wait_read<1>();
+      issue_load(k - 1 + kBulkStages);
+    }
+  }
+  bulk_wait_all<0>();  // the writes are performed before the grid ends (the signal kernel follows in stream order)
+}
+
+__device__ __forceinline__ BulkShared* bulk_setup(uint8_t* smem) {
+  BulkShared* sh = reinterpret_cast<BulkShared*>(smem + (size_t)kBulkStages * kTileVecs * 16);
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kBulkStages; ++s) mbar_init(&sh->full[s], 1);
+    mbar_fence_init();
+  }
+  return sh;
+}
+
+__global__ void __launch_bounds__(kBulkThreads) kv_put_blocks_bulk_kernel(const __grid_constant__ PutTable t) {
+  extern __shared__ __align__(128) uint8_t bulk_smem[];
+  BulkShared* sh = bulk_setup(bulk_smem);
+  int* s_tab = reinterpret_cast<int*>(sh + 1);
+  stage_runs(s_tab, t.start, t.len, t.num_runs, t.block_bytes / 16, t.tile_vecs);
+  put_tiles_bulk(bulk_smem, sh, s_tab, t.num_runs, t.num_bufs, t.tile_vecs, t.block_bytes, t.src_ptrs, t.dst_ptrs);
+}
+
+__global__ void __launch_bounds__(kBulkThreads) kv_put_blocks_table_bulk_kernel(
     const int* __restrict__ tab, int num_runs, int num_bufs, int tile_vecs, long long block_bytes,
     const long long* __restrict__ src_ptrs, const long long* __restrict__ dst_ptrs) {
-  extern __shared__ int s_tab[];
-  for (int i = threadIdx.x; i < 3 * num_runs + 1; i += blockDim.x) s_tab[i] = tab[i];
-  __syncthreads();
-  put_tiles(s_tab, s_tab + num_runs, s_tab + 2 * num_runs, num_runs, num_bufs, tile_vecs, block_bytes, src_ptrs, dst_ptrs);
+  extern __shared__ __align__(128) uint8_t bulk_smem[];
+  BulkShared* sh = bulk_setup(bulk_smem);
+  int* s_tab = reinterpret_cast<int*>(sh + 1);
+  stage_runs(s_tab, tab, tab + num_runs, num_runs, block_bytes / 16, tile_vecs);
+  put_tiles_bulk(bulk_smem, sh, s_tab, num_runs, num_bufs, tile_vecs, block_bytes, src_ptrs, dst_ptrs);
 }
 
 __global__ void kv_signal_kernel(unsigned long long* flag, unsigned long long value) {
@@ -139,12 +254,52 @@ __global__ void kv_wait_kernel(const unsigned long long* flag, unsigned long lon
 
 using namespace b200;
 
-// Tile = the largest even split of one block that stays <= 32 KiB (a 40 KiB block -> two 20 KiB tiles, not
-// 32 + 8), so single-block runs of a fragmented block list load the CTAs evenly.
+// Bulk-variant tile = the largest even split of one block that stays <= 32 KiB (a 40 KiB block -> two 20 KiB tiles,
+// not 32 + 8), so single-block runs of a fragmented block list load the CTAs evenly.
 static int put_tile_vecs(int64_t block_bytes) {
   const long long block_vecs = block_bytes / 16;
   const long long pieces = (block_vecs + kTileVecs - 1) / kTileVecs;
   return (int)((block_vecs + pieces - 1) / pieces);
+}
+
+// Process-wide put configuration (b200_kv_put_configure; initial values from B200_KV_PUT_VARIANT / B200_KV_PUT_CTAS).
+// variant 0 = SIMT (ld.global / st.global per warp chunk), 1 = bulk (TMA through a shared-memory ring).
+// Defaults from the CTA sweep on 2 x B200 (profiles/r05_kv_put_sweep.jsonl).
+static std::atomic<int> g_put_variant{-1}, g_put_ctas{-1};
+static int put_variant() {
+  int v = g_put_variant.load(std::memory_order_relaxed);
+  if (v < 0) {
+    const char* e = getenv("B200_KV_PUT_VARIANT");
+    v = e ? atoi(e) : 0;
+    g_put_variant.store(v, std::memory_order_relaxed);
+  }
+  return v;
+}
+static int put_default_ctas() {
+  int v = g_put_ctas.load(std::memory_order_relaxed);
+  if (v < 0) {
+    const char* e = getenv("B200_KV_PUT_CTAS");
+    v = e ? atoi(e) : 32;
+    if (v <= 0) v = 32;
+    g_put_ctas.store(v, std::memory_order_relaxed);
+  }
+  return v;
+}
+static size_t bulk_smem_bytes(int num_runs) {
+  return (size_t)kBulkStages * kTileVecs * 16 + sizeof(BulkShared) + ((size_t)3 * num_runs + 1) * sizeof(int);
+}
+template <typename K>
+static cudaError_t allow_smem(K kernel, size_t bytes, size_t* granted /* [64] per device */) {
+  if (bytes <= 48 * 1024) return cudaSuccess;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  dev &= 63;
+  if (granted[dev] >= bytes) return cudaSuccess;
+  const size_t want = 225 * 1024;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)want);
+  if (e == cudaSuccess) granted[dev] = want;
+  return e;
 }
 
 extern "C" {
@@ -204,37 +359,61 @@ B200_API int b200_kv_enable_peer_access(int32_t dev, int32_t peer_dev) {
   return B200_OK;
 }
 
+B200_API int b200_kv_put_configure(int32_t variant, int32_t default_ctas) {
+  if (variant >= 0) {
+    if (variant > 1) return B200_ERR_ARG;
+    g_put_variant.store(variant, std::memory_order_relaxed);
+  }
+  if (default_ctas > 0) g_put_ctas.store(default_ctas, std::memory_order_relaxed);
+  return B200_OK;
+}
+
+B200_API int b200_kv_put_config(int32_t* variant, int32_t* default_ctas) {
+  if (variant) *variant = put_variant();
+  if (default_ctas) *default_ctas = put_default_ctas();
+  return B200_OK;
+}
+
 B200_API int b200_kv_put_blocks(const int64_t* src_ptrs, const int64_t* dst_ptrs, int32_t num_bufs, const int32_t* runs,
                        int32_t num_runs, int64_t block_bytes, int32_t max_ctas, b200_stream_t stream_) {
   if (num_bufs == 0 || num_runs == 0) return B200_OK;
   if (!src_ptrs || !dst_ptrs || !runs || num_bufs < 0 || num_runs < 0 || block_bytes <= 0) return B200_ERR_ARG;
   if (block_bytes % 16 != 0) return B200_ERR_ALIGN;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (max_ctas <= 0) max_ctas = 2 * num_sms(-1);
-  // Tile = the largest even split of one block that stays <= 32 KiB (a 40 KiB block -> two 20 KiB tiles, not
-  // 32 + 8), so single-block runs of a fragmented block list load the CTAs evenly.
+  if (max_ctas <= 0) max_ctas = put_default_ctas();
+  const bool bulk = put_variant() == 1;
   const long long block_vecs = block_bytes / 16;
-  const int tile_vecs = put_tile_vecs(block_bytes);
+  const int unit_vecs = bulk ? put_tile_vecs(block_bytes) : kChunkVecs;
+  static size_t granted[64] = {0};
   for (int r0 = 0; r0 < num_runs; r0 += kMaxRuns) {
     PutTable t;
     t.num_runs = std::min(kMaxRuns, num_runs - r0);
-    long long tiles = 0;
+    long long units = 0;
     for (int r = 0; r < t.num_runs; ++r) {
       t.start[r] = runs[2 * (r0 + r)];
       t.len[r] = runs[2 * (r0 + r) + 1];
       if (t.start[r] < 0 || t.len[r] < 0) return B200_ERR_ARG;
-      tiles += ((long long)t.len[r] * block_vecs + tile_vecs - 1) / tile_vecs;
+      units += ((long long)t.len[r] * block_vecs + unit_vecs - 1) / unit_vecs;
     }
-    if (tiles * num_bufs > INT32_MAX) return B200_ERR_ARG;
-    t.tile_vecs = tile_vecs;
+    if (units * num_bufs > INT32_MAX) return B200_ERR_ARG;
+    t.tile_vecs = unit_vecs;
     t.num_bufs = num_bufs;
     t.block_bytes = block_bytes;
     t.src_ptrs = reinterpret_cast<const long long*>(src_ptrs);
     t.dst_ptrs = reinterpret_cast<const long long*>(dst_ptrs);
-    tiles *= num_bufs;
-    if (tiles == 0) continue;
-    const int grid = (int)std::min<long long>(tiles, max_ctas);
-    kv_put_blocks_kernel<<<grid, kPutThreads, 0, stream>>>(t);
+    units *= num_bufs;
+    if (units == 0) continue;
+    if (bulk) {
+      const size_t smem = bulk_smem_bytes(t.num_runs);
+      B200_CUDA_TRY(allow_smem(kv_put_blocks_bulk_kernel, smem, granted));
+      const int grid = (int)std::min<long long>(units, max_ctas);
+      kv_put_blocks_bulk_kernel<<<grid, kBulkThreads, smem, stream>>>(t);
+    } else {
+      const size_t smem = ((size_t)3 * t.num_runs + 1) * sizeof(int);
+      const long long want = (units + kPutThreads / 32 - 1) / (kPutThreads / 32);
+      const int grid = (int)std::min<long long>(want, max_ctas);
+      kv_put_blocks_kernel<<<grid, kPutThreads, smem, stream>>>(t);
+    }
     B200_LAUNCH_CHECK();
   }
   return B200_OK;
@@ -269,23 +448,29 @@ B200_API int b200_kv_put_blocks_table(const int64_t* src_ptrs, const int64_t* ds
       block_bytes <= 0)
     return B200_ERR_ARG;
   if (block_bytes % 16 != 0) return B200_ERR_ALIGN;
+  if (tile_vecs != put_tile_vecs(block_bytes)) return B200_ERR_ARG;  // the table was built for another block size
   if (tiles_per_buf * num_bufs > INT32_MAX) return B200_ERR_ARG;
-  const size_t smem = ((size_t)3 * num_runs + 1) * sizeof(int);
-  if (smem > 200 * 1024) return B200_ERR_ARG;
+  const size_t tab_bytes = ((size_t)3 * num_runs + 1) * sizeof(int);
+  if (tab_bytes > 200 * 1024) return B200_ERR_ARG;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  if (max_ctas <= 0) max_ctas = 2 * num_sms(-1);
-  static size_t attr_set[64] = {0};
-  int dev = 0;
-  B200_CUDA_TRY(cudaGetDevice(&dev));
-  dev &= 63;
-  if (smem > 48 * 1024 && attr_set[dev] < smem) {
-    B200_CUDA_TRY(cudaFuncSetAttribute(kv_put_blocks_table_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    attr_set[dev] = 200 * 1024;
+  if (max_ctas <= 0) max_ctas = put_default_ctas();
+  const long long* sp = reinterpret_cast<const long long*>(src_ptrs);
+  const long long* dp = reinterpret_cast<const long long*>(dst_ptrs);
+  static size_t granted_bulk[64] = {0}, granted_simt[64] = {0};
+  if (put_variant() == 1 && num_runs <= kBulkMaxRuns) {
+    const size_t smem = bulk_smem_bytes(num_runs);
+    B200_CUDA_TRY(allow_smem(kv_put_blocks_table_bulk_kernel, smem, granted_bulk));
+    const int grid = (int)std::min<long long>(tiles_per_buf * num_bufs, max_ctas);
+    kv_put_blocks_table_bulk_kernel<<<grid, kBulkThreads, smem, stream>>>(dev_table, num_runs, num_bufs, tile_vecs,
+                                                                         block_bytes, sp, dp);
+  } else {
+    B200_CUDA_TRY(allow_smem(kv_put_blocks_table_kernel, tab_bytes, granted_simt));
+    // chunks per buffer <= (tile_vecs / kChunkVecs + 1) per tile: size the grid from the tile count
+    const long long chunks = tiles_per_buf * ((tile_vecs + kChunkVecs - 1) / kChunkVecs) * num_bufs;
+    const long long want = (chunks + kPutThreads / 32 - 1) / (kPutThreads / 32);
+    const int grid = (int)std::min<long long>(want, max_ctas);
+    kv_put_blocks_table_kernel<<<grid, kPutThreads, tab_bytes, stream>>>(dev_table, num_runs, num_bufs, block_bytes, sp, dp);
   }
-  const int grid = (int)std::min<long long>(tiles_per_buf * num_bufs, max_ctas);
-  kv_put_blocks_table_kernel<<<grid, kPutThreads, smem, stream>>>(
-      dev_table, num_runs, num_bufs, tile_vecs, block_bytes, reinterpret_cast<const long long*>(src_ptrs),
-      reinterpret_cast<const long long*>(dst_ptrs));
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
