@@ -166,7 +166,7 @@ def test_bf16_query_outside_f16_range_with_fp8_cache(ops, num_heads, how):
 
 def _split_case(seed, ctx_len=4096, num_heads=(8, 1), num_seqs=2):
     return make_attention_inputs(num_seqs=num_seqs, num_heads=num_heads, head_size=128, block_size=16, dtype=torch.half,
-                                 num_blocks=num_seqs * (ctx_len // 16), context_lens=[ctx_len] * num_seqs,
+                                 num_blocks=num_seqs * ((ctx_len + 15) // 16), context_lens=[ctx_len] * num_seqs,
                                  distinct_blocks=True, seed=seed)
 
 

@@ -181,6 +181,9 @@ def bench_swap(iters, ours, ref):
             it = iters if kind == "d2d" else max(5, iters // 5)
             b.zero_()
             ms = timeit(lambda i: ours.swap_blocks(a, b, mapping), it, 1)
+            # D2D: the eager call is bound by the host side of the op (a 256-entry dict crosses the binding per call);
+            # the replayed graph shows the gather kernel itself
+            gms = timeit_graph(lambda i: ours.swap_blocks(a, b, mapping), 1) if kind == "d2d" else None
             mine = b.clone() if kind != "d2h" else b.clone()
             ref_ms, exact = None, None
             if ref is not None:
@@ -188,8 +191,8 @@ def bench_swap(iters, ours, ref):
                 ref_ms = timeit(lambda i: ref.cache_ops.swap_blocks(a, b, mapping), it, 1)
                 exact = bool(torch.equal(mine, b))
             emit(f"swap_blocks_{kind}_{pattern}", f"{n} blocks x 128 KiB, one layer's V, fp16", nbytes, ms, ref_ms, exact,
-                 note="bytes = read + write" if kind == "d2d" else "bytes = one direction over PCIe (pinned host)",
-                 bound=bound)
+                 note="bytes = read + write; ms = eager op calls (host-bound), graph_replay_ms = the gather kernel"
+                 if kind == "d2d" else "bytes = one direction over PCIe (pinned host)", bound=bound, graph_ms=gms)
 
 
 def bench_convert(iters, ours, ref):

@@ -241,6 +241,25 @@ __global__ void __launch_bounds__(256) reshape_and_cache_tile_kernel(
   if (s_fast) {
     const int ngroups = TOK / G;
     constexpr int WPE = 8 / (int)sizeof(CT);  // cache elements per 8-byte word
+    constexpr int VPE = 16 / (int)sizeof(CT); // cache elements per 16-byte vector
+    if ((G % VPE) == 0 && (block_size % VPE) == 0) {
+      // a group's row is whole 16-byte vectors (block_size 16/32; fp32 also 8): one st.v4 per 16 bytes
+      for (int i = threadIdx.x; i < head_size * ngroups; i += blockDim.x) {
+        const int g = i / head_size, d = i - g * head_size;
+        const int tl = g * G;
+        CT* row = value_cache + s_base[tl] + (int64_t)d * block_size + s_off[tl];
+        const T* col = vt + tl * pitch + d;
+#pragma unroll
+        for (int w = 0; w < TOK / VPE; ++w) {
+          if (w * VPE < G) {
+            alignas(16) CT tmp[VPE];
+#pragma unroll
+            for (int e = 0; e < VPE; ++e) tmp[e] = cache_cvt<T, CT, FP8>(col[(w * VPE + e) * pitch]);
+            *reinterpret_cast<uint4*>(row + w * VPE) = *reinterpret_cast<const uint4*>(tmp);
+          }
+        }
+      }
+    } else
     for (int i = threadIdx.x; i < head_size * ngroups; i += blockDim.x) {
       const int g = i / head_size, d = i - g * head_size;
       const int tl = g * G;
@@ -401,6 +420,10 @@ static int launch_copy(const int64_t* src_bases, const int64_t* dst_bases, int n
 // ------------------------------------------------------------------------------------------
 // 16 elements per thread per step: 16-byte vectors on both sides when the host proved alignment; the
 // tail (numel % 16) and unaligned tensors take the scalar loop of the same kernel.
+// U groups per thread per step: all of a step's loads are issued before the first conversion, so a thread keeps
+// U x 32 (to fp8) / U x 16 (from fp8) bytes in flight -- one group per step left the kernel latency-bound
+// (profiles/r05_cache_ops_ncu.txt: from_fp8 at 0.70 of the copy peak with 57 % of the warps resident).
+constexpr int kCvtUnroll = 4;
 template <typename T, bool VEC>
 __global__ void __launch_bounds__(256) to_fp8_kernel(const T* __restrict__ src, uint8_t* __restrict__ dst, int64_t n) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -408,13 +431,20 @@ __global__ void __launch_bounds__(256) to_fp8_kernel(const T* __restrict__ src, 
   int64_t done = 0;
   if constexpr (VEC) {
     const int64_t groups = n / 16;
-    for (int64_t g = tid; g < groups; g += stride) {
-      alignas(16) T in[16];
-      load_elems<T, 16, true>(src + g * 16, in);
-      alignas(16) uint8_t out[16];
+    for (int64_t g0 = tid; g0 < groups; g0 += kCvtUnroll * stride) {
+      alignas(16) T in[kCvtUnroll][16];
 #pragma unroll
-      for (int e = 0; e < 16; ++e) out[e] = to_e5m2<T>(in[e]);
-      st_na_v4(dst + g * 16, *reinterpret_cast<const uint4*>(out));
+      for (int u = 0; u < kCvtUnroll; ++u)
+        if (g0 + u * stride < groups) load_elems<T, 16, true>(src + (g0 + u * stride) * 16, in[u]);
+#pragma unroll
+      for (int u = 0; u < kCvtUnroll; ++u) {
+        if (g0 + u * stride < groups) {
+          alignas(16) uint8_t out[16];
+#pragma unroll
+          for (int e = 0; e < 16; ++e) out[e] = to_e5m2<T>(in[u][e]);
+          st_na_v4(dst + (g0 + u * stride) * 16, *reinterpret_cast<const uint4*>(out));
+        }
+      }
     }
     done = groups * 16;
   }
@@ -428,14 +458,23 @@ __global__ void __launch_bounds__(256) from_fp8_kernel(const uint8_t* __restrict
   if constexpr (VEC) {
     constexpr int PER = 16 / (int)sizeof(T);
     const int64_t groups = n / 16;
-    for (int64_t g = tid; g < groups; g += stride) {
-      const uint4 raw = ld_nc_v4(src + g * 16);
-      const uint8_t* in = reinterpret_cast<const uint8_t*>(&raw);
-      alignas(16) T out[16];
+    for (int64_t g0 = tid; g0 < groups; g0 += kCvtUnroll * stride) {
+      uint4 raw[kCvtUnroll];
 #pragma unroll
-      for (int e = 0; e < 16; ++e) out[e] = from_e5m2<T>(in[e]);
+      for (int u = 0; u < kCvtUnroll; ++u)
+        if (g0 + u * stride < groups) raw[u] = ld_nc_v4(src + (g0 + u * stride) * 16);
 #pragma unroll
-      for (int v = 0; v < 16 / PER; ++v) st_na_v4(dst + g * 16 + v * PER, *reinterpret_cast<const uint4*>(out + v * PER));
+      for (int u = 0; u < kCvtUnroll; ++u) {
+        if (g0 + u * stride < groups) {
+          const uint8_t* in = reinterpret_cast<const uint8_t*>(&raw[u]);
+          alignas(16) T out[16];
+#pragma unroll
+          for (int e = 0; e < 16; ++e) out[e] = from_e5m2<T>(in[e]);
+#pragma unroll
+          for (int v = 0; v < 16 / PER; ++v)
+            st_na_v4(dst + (g0 + u * stride) * 16 + v * PER, *reinterpret_cast<const uint4*>(out + v * PER));
+        }
+      }
     }
     done = groups * 16;
   }

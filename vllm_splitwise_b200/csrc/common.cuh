@@ -24,6 +24,7 @@ void count_launch();
     cudaError_t e__ = (expr);                          \
     if (e__ != cudaSuccess) {                          \
       ::b200::set_last_cuda_error(e__, #expr);         \
+      (void)cudaGetLastError(); /* not sticky for the next call's launch check */ \
       return B200_ERR_CUDA;                            \
     }                                                  \
   } while (0)

@@ -115,7 +115,7 @@ int dispatch_simt(const b200_paged_attn_args_t* a, const AttnParams& p, int gt, 
 template <typename T>
 int launch_reduce_t(const b200_paged_attn_args_t* a, int max_parts, int partition_tokens, cudaStream_t stream) {
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(a->num_heads, a->num_seqs);
+  cfg.gridDim = dim3(a->num_seqs, a->num_heads);
   cfg.blockDim = dim3(128);
   cfg.dynamicSmemBytes = (size_t)max_parts * sizeof(float);
   cfg.stream = stream;
@@ -146,8 +146,7 @@ int launch_reduce(const b200_paged_attn_args_t* a, int max_parts, int partition_
 int pick_smem_budget(const b200_paged_attn_args_t* a, const TilePlan& t, int* ctas_per_sm) {
   const int stage = 2 * a->head_size * a->block_size * dtype_size(a->cache_dtype);
   const int fixed = t.mma ? 0 : t.gt * a->head_size * 4 + kConsumerWarps * t.gt * a->block_size * 4;
-  const int tail = fixed + kConsumerWarps * t.gt * a->head_size * 4 + kConsumerWarps * t.gt * 8 + 16 + kItemQueue * 16 +
-                   2 * kMaxStages * 8 + 2 * kItemQueue * 8;
+  const int tail = attn_smem_tail(fixed, t.gt, a->head_size, dtype_size(a->query_dtype));
   // two resident CTAs per SM when each still gets a ring of at least 4 stages, else one.  (Three CTAs with
   // 12-stage rings fit for 1-byte caches but measured 2 % slower on C4: profiles/README.md.)
   int want = 2;

@@ -26,6 +26,7 @@
 #pragma once
 
 #include <float.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -57,6 +58,8 @@ struct AttnParams {
   int always_partials;   // 1: v2 signature (every item writes tmp_out/exp_sums/max_logits)
   int nstages;           // ring depth; always a multiple of nconsumers
   int nconsumers;        // consumer warps that take blocks (<= kConsumerWarps)
+  int lookahead;         // 1: small items -- the producer draws and prefetches the metadata of two items ahead
+  int q_bulk;            // 1: the query rows of an item reach the consumers through shared memory (bulk copy)
   long long total_items; // max_num_partitions * num_seqs * tiles_per_seq
   long long q_stride;
   long long kv_block_stride;
@@ -105,6 +108,13 @@ __device__ __forceinline__ ItemInfo decode_item(const AttnParams& p, long long i
   return it;
 }
 
+// bulk copy without an eviction hint (query rows: re-read by the sequence's other partitions)
+__device__ __forceinline__ void bulk_g2s_plain(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
 __device__ __forceinline__ void consumer_bar() {  // the 4 consumer warps only; the producer never joins
   asm volatile("bar.sync 1, %0;" ::"n"(kConsumerThreads) : "memory");
 }
@@ -124,7 +134,8 @@ struct RingPos {
 template <typename CT>
 __device__ __forceinline__ void attn_produce_item(const AttnParams& p, const ItemInfo& it, RingPos& pos, int lane,
                                                   unsigned char* stages, int stage_bytes, int kbytes,
-                                                  uint64_t* full_bar, uint64_t* empty_bar, uint64_t pol) {
+                                                  uint64_t* full_bar, uint64_t* empty_bar, uint64_t pol,
+                                                  bool have_first = false, int phys_first = 0) {
   const int nst = p.nstages;
   const int G = nst < 32 ? nst : 32;
   const int* table = p.block_tables + (long long)it.seq * p.max_num_blocks_per_seq + it.b0;
@@ -132,7 +143,8 @@ __device__ __forceinline__ void attn_produce_item(const AttnParams& p, const Ite
   const unsigned char* vbase = static_cast<const unsigned char*>(p.v_cache) + (long long)it.kvh * p.kv_head_stride * (long long)sizeof(CT);
   const long long blk_bytes = p.kv_block_stride * (long long)sizeof(CT);
   const int nblk = it.nblk;
-  int phys_next = (lane < G && lane < nblk) ? table[lane] : 0;
+  // have_first: the first group's block numbers were fetched while the previous item was streaming
+  int phys_next = have_first ? phys_first : ((lane < G && lane < nblk) ? table[lane] : 0);
   for (int n0 = 0; n0 < nblk; n0 += G) {
     const int phys = phys_next;
     const int nn = n0 + G + lane;
@@ -269,6 +281,8 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_kernel(const __grid_c
   uint64_t* empty_bar = full_bar + kMaxStages;
   uint64_t* iq_full = empty_bar + kMaxStages;
   uint64_t* iq_empty = iq_full + kItemQueue;
+  constexpr int QB = GT * D * (int)sizeof(T);  // query rows of one item
+  unsigned char* q_stage = reinterpret_cast<unsigned char*>(iq_empty + kItemQueue);  // [kItemQueue][QB]
 
   if (tid == 0) {
     for (int s = 0; s < nst; ++s) {
@@ -296,32 +310,89 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_kernel(const __grid_c
     // Work items are drawn from a device-wide counter (the first one is blockIdx.x), so CTAs on slower SMs
     // simply take fewer; every item id is handed to the consumer warps through a small shared-memory queue.
     RingPos pos{0, 0};
-    long long item = blockIdx.x;
-    for (int k = 0;; ++k) {
+    const T* qbase = static_cast<const T*>(p.q);
+    // hand item `item` (context length ctx) to the consumers: id, context length and -- q_bulk -- its query rows
+    auto enqueue = [&](int k, long long item, bool done, const ItemInfo& it) {
       const int qs = k % kItemQueue;
-      const bool done = item >= p.total_items;
-      ItemInfo it;
-      if (!done) it = decode_item<GT, BS>(p, item);
       if (lane == 0) {
         if (k >= kItemQueue) mbar_wait(&iq_empty[qs], ((k / kItemQueue) - 1) & 1);
         item_q[qs] = item;
         ctx_q[qs] = done ? 0 : it.ctx;
-        mbar_arrive(&iq_full[qs]);
+        if (!done && p.q_bulk && it.nblk > 0) {
+          const uint32_t bytes = (uint32_t)(it.ng * D * (int)sizeof(T));
+          mbar_arrive_expect_tx(&iq_full[qs], bytes);
+          bulk_g2s_plain(q_stage + qs * QB, qbase + (long long)it.seq * p.q_stride + (long long)it.head0 * D, bytes,
+                         &iq_full[qs]);
+        } else {
+          mbar_arrive(&iq_full[qs]);
+        }
       }
-      if (done) break;
-      if (it.nblk > 0)
-        attn_produce_item<CT>(p, it, pos, lane, stages, Impl::kStageBytes, Impl::kKBytes, full_bar, empty_bar, pol);
-      if (p.sched == nullptr) {  // no counter slot left for this launch (see attach_sched): static round-robin
-        item += gridDim.x;
-        continue;
-      }
+    };
+    // draw the id of the next item from the device-wide counter (static round-robin without one)
+    auto draw_issue = [&](long long prev) -> unsigned int {  // returns lane 0's raw ticket (other lanes: 0)
       unsigned int raw = 0;
-      if (lane == 0) {
+      if (p.sched != nullptr && lane == 0) {
         raw = atomicAdd(p.sched, 1u);
         if ((long long)raw == p.total_items - 1) *p.sched = 0u;  // the last draw of the launch: leave the counter at zero
       }
-      raw = __shfl_sync(0xffffffffu, raw, 0);
-      item = (long long)raw + gridDim.x;
+      (void)prev;
+      return raw;
+    };
+    auto draw_finish = [&](unsigned int raw, long long prev) -> long long {
+      if (p.sched == nullptr) return prev + gridDim.x;
+      return (long long)__shfl_sync(0xffffffffu, raw, 0) + gridDim.x;
+    };
+    if (!p.lookahead) {
+      long long item = blockIdx.x;
+      for (int k = 0;; ++k) {
+        const bool done = item >= p.total_items;
+        ItemInfo it;
+        if (!done) it = decode_item<GT, BS>(p, item);
+        enqueue(k, item, done, it);
+        if (done) break;
+        if (it.nblk > 0)
+          attn_produce_item<CT>(p, it, pos, lane, stages, Impl::kStageBytes, Impl::kKBytes, full_bar, empty_bar, pol);
+        item = draw_finish(draw_issue(item), item);
+      }
+      return;
+    }
+    // Small items (a partition of a few dozen blocks streams in a few microseconds): the three dependent
+    // global-memory round trips between two items -- ticket, context length, first block-table group -- would
+    // drain the ring at every item boundary.  So the producer works two items ahead: while item k streams, the
+    // ticket of item k+2 is in flight and the context length / block numbers of item k+1 have already landed.
+    const int G = p.nstages < 32 ? p.nstages : 32;
+    const int per_part = p.num_seqs * p.tiles_per_seq;
+    auto prefetch = [&](long long item, int& ctx, int& phys) {  // loads only: nothing here waits
+      ctx = 0;
+      phys = 0;
+      if (item >= p.total_items) return;
+      const int part = (int)(item / per_part);
+      const int seq = (int)(item - (long long)part * per_part) / p.tiles_per_seq;
+      ctx = p.context_lens[seq];
+      const int b = part * p.partition_blocks + lane;
+      if (lane < G && b < p.max_num_blocks_per_seq) phys = p.block_tables[(long long)seq * p.max_num_blocks_per_seq + b];
+    };
+    long long cur = blockIdx.x, nxt;
+    int ctx_cur, phys_cur, ctx_nxt, phys_nxt;
+    prefetch(cur, ctx_cur, phys_cur);
+    nxt = cur < p.total_items ? draw_finish(draw_issue(cur), cur) : cur;
+    prefetch(nxt, ctx_nxt, phys_nxt);
+    for (int k = 0;; ++k) {
+      const bool done = cur >= p.total_items;
+      ItemInfo it;
+      if (!done) it = decode_item<GT, BS>(p, cur, ctx_cur);
+      enqueue(k, cur, done, it);
+      if (done) break;
+      // every CTA draws exactly one ticket past the end, never more (the counter's reset relies on it)
+      const bool more = nxt < p.total_items;
+      const unsigned int raw = more ? draw_issue(nxt) : 0u;
+      if (it.nblk > 0)
+        attn_produce_item<CT>(p, it, pos, lane, stages, Impl::kStageBytes, Impl::kKBytes, full_bar, empty_bar, pol, true,
+                              phys_cur);
+      const long long nn = more ? draw_finish(raw, nxt) : nxt;
+      cur = nxt; ctx_cur = ctx_nxt; phys_cur = phys_nxt;
+      nxt = nn;
+      prefetch(nxt, ctx_nxt, phys_nxt);
     }
     return;
   }
@@ -343,10 +414,10 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_kernel(const __grid_c
     const long long item = item_q[qs];
     const int ctx_known = ctx_q[qs];
     __syncwarp();
-    if (lane == 0) mbar_arrive(&iq_empty[qs]);
     if (item >= p.total_items) break;
     const ItemInfo it = decode_item<GT, BS>(p, item, ctx_known);
     if (it.nblk == 0) {
+      if (lane == 0) mbar_arrive(&iq_empty[qs]);
       // nothing to read.  An empty context is softmax over nothing -> zeros (reference: exp_sum = 0, acc = 0);
       // under the v2 signature the reduce kernel writes them (it sees zero partitions).
       if (it.nblk_ctx == 0 && it.part == 0 && !p.always_partials) {
@@ -357,7 +428,12 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_kernel(const __grid_c
       continue;
     }
     Impl::init(st);
-    Impl::begin_item(st, p, it, fixed, warp, lane);
+    // the item's query rows [ng][D]: staged by the producer next to the queue entry, or read from global memory
+    const T* qrows = p.q_bulk ? reinterpret_cast<const T*>(q_stage + qs * QB)
+                              : static_cast<const T*>(p.q) + (long long)it.seq * p.q_stride + (long long)it.head0 * D;
+    Impl::begin_item(st, p, it, qrows, fixed, warp, lane);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&iq_empty[qs]);  // the queue entry (and its query rows) may be reused
     if (active) {
       const int gend = gbase + it.nblk;
       for (; my_gi < gend; my_gi += nwa) {
@@ -446,10 +522,9 @@ struct SimtImpl {
     }
   }
 
-  __device__ __forceinline__ static void begin_item(State& st, const AttnParams& p, const ItemInfo& it,
+  __device__ __forceinline__ static void begin_item(State& st, const AttnParams& p, const ItemInfo& it, const T* q,
                                                     unsigned char* fixed, int warp, int lane) {
     float* q_s = reinterpret_cast<float*>(fixed);
-    const T* q = static_cast<const T*>(p.q) + (long long)it.seq * p.q_stride + (long long)it.head0 * D;
     for (int i = warp * 32 + lane; i < GT * D; i += kConsumerThreads) q_s[i] = (i < it.ng * D) ? to_f32<T>(q[i]) : 0.f;
 #pragma unroll
     for (int g = 0; g < GT; ++g)
@@ -580,7 +655,7 @@ __global__ void __launch_bounds__(128) paged_attn_reduce_kernel(
     T* __restrict__ out, const float* __restrict__ exp_sums, const float* __restrict__ max_logits,
     const T* __restrict__ tmp_out, const int* __restrict__ context_lens, int head_size,
     int max_num_partitions, int partition_tokens) {
-  const int head = blockIdx.x, seq = blockIdx.y, num_heads = gridDim.x;
+  const int head = blockIdx.y, seq = blockIdx.x, num_heads = gridDim.y;  // sequences on x: no 65 535 limit
   const int ctx = context_lens[seq];
   const int np = (ctx + partition_tokens - 1) / partition_tokens;
   const long long sh = (long long)seq * num_heads + head;
@@ -624,12 +699,21 @@ __global__ void __launch_bounds__(128) paged_attn_reduce_kernel(
 
 // ---- host-side launch plumbing shared by both consumers ---------------------------------------------
 // Ring depth and shared-memory size for a consumer under a per-CTA budget.
-inline bool attn_smem_plan(int stage_bytes, int fixed_bytes, int gt, int head_size, int smem_budget, int* nstages,
-                           int* nconsumers, int* smem_bytes) {
-  const int tail = fixed_bytes + kConsumerWarps * gt * head_size * 4 + kConsumerWarps * gt * 2 * 4 + 16 +
-                   kItemQueue * 16 + 2 * kMaxStages * 8 + 2 * kItemQueue * 8;
+inline int attn_max_stages(int stage_bytes) {
+  // small stages (1-byte caches, short heads): a deeper ring rides out the per-item bubbles of short partitions
+  static const int env = getenv("B200_ATTN_MAX_STAGES") ? atoi(getenv("B200_ATTN_MAX_STAGES")) : 0;  // tuning knob
+  if (env >= 2 && env <= kMaxStages) return env;
+  return stage_bytes <= 4096 ? 24 : 16;
+}
+inline int attn_smem_tail(int fixed_bytes, int gt, int head_size, int q_elt_bytes) {
+  return fixed_bytes + kConsumerWarps * gt * head_size * 4 + kConsumerWarps * gt * 2 * 4 + 16 + kItemQueue * 16 +
+         2 * kMaxStages * 8 + 2 * kItemQueue * 8 + kItemQueue * gt * head_size * q_elt_bytes;
+}
+inline bool attn_smem_plan(int stage_bytes, int fixed_bytes, int gt, int head_size, int q_elt_bytes, int smem_budget,
+                           int* nstages, int* nconsumers, int* smem_bytes) {
+  const int tail = attn_smem_tail(fixed_bytes, gt, head_size, q_elt_bytes);
   int n = (smem_budget - tail) / stage_bytes;
-  if (n > 16) n = 16;
+  if (n > attn_max_stages(stage_bytes)) n = attn_max_stages(stage_bytes);
   // ring depth must be a multiple of the number of consuming warps (same warp per slot, see the kernel)
   const int nwa = n < kConsumerWarps ? n : kConsumerWarps;
   if (nwa > 0) n = n / nwa * nwa;
@@ -644,10 +728,18 @@ template <class Impl>
 int launch_attn(const AttnParams& p_in, int smem_budget, int sms, cudaStream_t stream) {
   AttnParams p = p_in;
   int nst = 0, nwa = 0, smem = 0;
-  if (!attn_smem_plan(Impl::kStageBytes, Impl::kFixedBytes, Impl::GT, Impl::D, smem_budget, &nst, &nwa, &smem))
+  if (!attn_smem_plan(Impl::kStageBytes, Impl::kFixedBytes, Impl::GT, Impl::D, (int)sizeof(typename Impl::T), smem_budget,
+                      &nst, &nwa, &smem))
     return B200_ERR_ARG;
   p.nstages = nst;
   p.nconsumers = nwa;
+  // query rows travel through shared memory when a bulk copy can fetch them (16-byte aligned rows)
+  static const bool no_q_bulk = getenv("B200_ATTN_NO_QBULK") != nullptr;      // A/B knobs
+  static const bool no_lookahead = getenv("B200_ATTN_NO_LOOKAHEAD") != nullptr;
+  p.q_bulk = !no_q_bulk && (reinterpret_cast<uintptr_t>(p.q) % 16 == 0) &&
+             ((p.q_stride * (long long)sizeof(typename Impl::T)) % 16 == 0) &&
+             ((Impl::D * (int)sizeof(typename Impl::T)) % 16 == 0);
+  p.lookahead = !no_lookahead && p.partition_blocks > 0 && p.partition_blocks <= 64;
   auto kern = paged_attn_kernel<Impl>;
   // per instantiation and per device (function attributes are per device): smem size -> resident CTAs per SM
   static int occ_smem[64] = {0}, occ_val[64] = {0};

@@ -149,13 +149,12 @@ struct MmaImpl {
       for (int j = 0; j < 2 * R; ++j) st.o[i][j] = 0.f;
   }
 
-  __device__ __forceinline__ static void begin_item(State& st, const AttnParams& p, const ItemInfo& it,
+  __device__ __forceinline__ static void begin_item(State& st, const AttnParams& p, const ItemInfo& it, const T* qrow,
                                                     unsigned char*, int, int lane) {
     const int g = lane >> 2, t = lane & 3;
     // Q fragments (A operand of S^T = Q.K^T).  k-slot -> d mapping inside a 16-wide k-step: natural for
     // 2-byte caches; for fp8 the thread's ldmatrix word holds d = 4t..4t+3, so slots (2t,2t+1) <- d (4t,4t+1)
     // and (2t+8,2t+9) <- d (4t+2,4t+3).
-    const T* qrow = static_cast<const T*>(p.q) + (long long)it.seq * p.q_stride + (long long)it.head0 * D;
     float qmul[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
