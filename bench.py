@@ -549,18 +549,23 @@ def extra_kv_transfer(args, rank, world, device):
     import torch.distributed as dist
     from tools import kv_transfer_bench
     boot = dist.new_group(backend="gloo")
-    lines = kv_transfer_bench.run(rank, world, device, boot, prompts=8, iters=4, warmup=2)
+    # library-default put kernel and CTA budget; per-layer launches and 4 layers merged per launch
+    lines = kv_transfer_bench.run(rank, world, device, boot, prompts=8, iters=4, warmup=2,
+                                  modes=("bulk", "per_layer", "ref_api", "paced", "nccl"), sweep=[(-1, 0, 1), (-1, 0, 4)])
     if rank != 0:
         return None
     out = {"config": lines[0]["config"] if lines else None, "unit": "GB/s per GPU pair",
            "nvlink_nominal_GBps": kv_transfer_bench.NVLINK_NOMINAL_GBS,
            "nvlink_measured_peer_copy_GBps": kv_transfer_bench.NVLINK_MEASURED_GBS, "cases": {}}
     for l in lines:
-        out["cases"][f"{l['pattern']}.{l['mode']}"] = {
+        key = f"{l['pattern']}.{l['mode']}" + (f".lpl{l['layers_per_launch']}" if "layers_per_launch" in l else "")
+        out["cases"][key] = {
             "value": l["value"], "best": l["best_GBps"], "aggregate": l["aggregate_GBps"],
             "frac_of_900": l["frac_of_nvlink_nominal_900"], "frac_of_770_measured": l["frac_of_nvlink_measured_770"],
             "bit_exact": l["bit_exact"], "prompts_in_flight": l["prompts_in_flight"], "ms": l["ms_mean"],
             "time_to_signal_ms": l.get("time_to_signal_ms"), "max_ctas": l.get("max_ctas"),
+            "put_variant": l.get("put_variant"), "layers_per_launch": l.get("layers_per_launch"),
+            "comm_stream": l.get("comm_stream"),
             "runs_per_prompt": l["runs_per_prompt"]}
     out["bit_exact"] = all(l["bit_exact"] for l in lines)
     return out

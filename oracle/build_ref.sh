@@ -32,10 +32,11 @@ build_cu cache_kernels.cu cache_kernels.o &
 P2=$!
 build_cu cuda_utils_kernels.cu cuda_utils_kernels.o
 build_cu pos_encoding_kernels.cu pos_encoding_kernels.o
+build_cu custom_all_reduce.cu custom_all_reduce.o
 g++ -fPIC $COMMON -c "$HERE/ref_build/ref_binding.cpp" -o "$OUT/ref_binding.o"
 wait $P1; wait $P2
 g++ -shared -o "$OUT/vllm_ref_C.so" "$OUT/attention_kernels.o" "$OUT/cache_kernels.o" \
-    "$OUT/cuda_utils_kernels.o" "$OUT/pos_encoding_kernels.o" "$OUT/ref_binding.o" \
+    "$OUT/cuda_utils_kernels.o" "$OUT/pos_encoding_kernels.o" "$OUT/custom_all_reduce.o" "$OUT/ref_binding.o" \
     -L"$TORCH_LIB" -Wl,-rpath,"$TORCH_LIB" -lc10 -lc10_cuda -ltorch_cpu -ltorch_cuda -ltorch -ltorch_python \
     -L/usr/local/cuda/lib64 -lcudart
 echo "[build_ref] built $OUT/vllm_ref_C.so"

@@ -4,7 +4,7 @@
 // tests and bench.py can run the reference's own paged_attention / cache ops next to ours on
 // identical inputs.  The kernels themselves are compiled straight from
 // /root/reference/csrc/{attention/attention_kernels.cu,cache_kernels.cu,cuda_utils_kernels.cu,
-// pos_encoding_kernels.cu}
+// pos_encoding_kernels.cu, custom_all_reduce.cu}
 // by oracle/build_ref.sh; nothing from the reference is copied into this repository.  The
 // prototypes below restate csrc/ops.h:5-34, csrc/cache.h:8-29 and csrc/cuda_utils.h.
 #include <torch/extension.h>
@@ -42,6 +42,18 @@ void batched_rotary_embedding(torch::Tensor& positions, torch::Tensor& query, to
                               torch::Tensor& cos_sin_cache, bool is_neox, int rot_dim,
                               torch::Tensor& cos_sin_cache_offsets);
 
+// csrc/ops.h:96-117 (compiled from csrc/custom_all_reduce.cu): the reference's P2P all-reduce, SURVEY 8f row N4
+using fptr_t = uint64_t;
+fptr_t init_custom_ar(torch::Tensor& meta, torch::Tensor& rank_data, const std::vector<std::string>& handles,
+                      const std::vector<int64_t>& offsets, int rank, bool full_nvlink);
+bool should_custom_ar(torch::Tensor& inp, int max_size, int world_size, bool full_nvlink);
+void all_reduce_reg(fptr_t _fa, torch::Tensor& inp, torch::Tensor& out);
+void all_reduce_unreg(fptr_t _fa, torch::Tensor& inp, torch::Tensor& reg_buffer, torch::Tensor& out);
+void dispose(fptr_t _fa);
+int meta_size();
+void register_buffer(fptr_t _fa, torch::Tensor& t, const std::vector<std::string>& handles,
+                     const std::vector<int64_t>& offsets);
+
 int get_device_attribute(int attribute, int device_id);
 int get_max_shared_memory_per_block_device_attribute(int device_id);
 
@@ -56,6 +68,14 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   cache_ops.def("copy_blocks", &copy_blocks);
   cache_ops.def("reshape_and_cache", &reshape_and_cache);
   cache_ops.def("convert_fp8_e5m2", &convert_fp8_e5m2);
+  pybind11::module custom_ar = m.def_submodule("custom_ar");
+  custom_ar.def("init_custom_ar", &init_custom_ar);
+  custom_ar.def("should_custom_ar", &should_custom_ar);
+  custom_ar.def("all_reduce_reg", &all_reduce_reg);
+  custom_ar.def("all_reduce_unreg", &all_reduce_unreg);
+  custom_ar.def("dispose", &dispose);
+  custom_ar.def("meta_size", &meta_size);
+  custom_ar.def("register_buffer", &register_buffer);
   pybind11::module cuda_utils = m.def_submodule("cuda_utils");
   cuda_utils.def("get_device_attribute", &get_device_attribute);
   cuda_utils.def("get_max_shared_memory_per_block_device_attribute",

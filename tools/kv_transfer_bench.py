@@ -278,8 +278,11 @@ def run(rank, world, dev, boot, prompts=8, layers=40, kv_heads=10, head_size=128
                         "config": {"workload": f"C5 Llama-2-13B tp=4 shard: {L} layers, {H} kv heads, head {D}, block {bs}, fp16, "
                                                f"{args.prompt_tokens}-token prompts, {npw} prompt -> {npw} token GPUs"}}
                 if mode != "nccl":
-                    line.update({"put_variant": {0: "simt", 1: "bulk"}.get(variant, "library default"),
-                                 "max_ctas": ctas if ctas > 0 else "library default",
+                    import ctypes
+                    cv, cc = ctypes.c_int32(), ctypes.c_int32()
+                    lib.b200_kv_put_config(ctypes.byref(cv), ctypes.byref(cc))   # what the library actually used
+                    line.update({"put_variant": {0: "simt", 1: "bulk"}[cv.value],
+                                 "max_ctas": ctas if ctas > 0 else cc.value,
                                  "layers_per_launch": comm.layers_per_launch, "comm_stream": comm.comm_stream is not None})
                 if mode == "paced":
                     tail = sum(tails) / len(tails)

@@ -58,7 +58,6 @@ struct AttnParams {
   int always_partials;   // 1: v2 signature (every item writes tmp_out/exp_sums/max_logits)
   int nstages;           // ring depth; always a multiple of nconsumers
   int nconsumers;        // consumer warps that take blocks (<= kConsumerWarps)
-  int lookahead;         // 1: small items -- the producer draws and prefetches the metadata of two items ahead
   int q_bulk;            // 1: the query rows of an item reach the consumers through shared memory (bulk copy)
   long long total_items; // max_num_partitions * num_seqs * tiles_per_seq
   long long q_stride;
@@ -134,8 +133,7 @@ struct RingPos {
 template <typename CT>
 __device__ __forceinline__ void attn_produce_item(const AttnParams& p, const ItemInfo& it, RingPos& pos, int lane,
                                                   unsigned char* stages, int stage_bytes, int kbytes,
-                                                  uint64_t* full_bar, uint64_t* empty_bar, uint64_t pol,
-                                                  bool have_first = false, int phys_first = 0) {
+                                                  uint64_t* full_bar, uint64_t* empty_bar, uint64_t pol) {
   const int nst = p.nstages;
   const int G = nst < 32 ? nst : 32;
   const int* table = p.block_tables + (long long)it.seq * p.max_num_blocks_per_seq + it.b0;
@@ -143,8 +141,7 @@ __device__ __forceinline__ void attn_produce_item(const AttnParams& p, const Ite
   const unsigned char* vbase = static_cast<const unsigned char*>(p.v_cache) + (long long)it.kvh * p.kv_head_stride * (long long)sizeof(CT);
   const long long blk_bytes = p.kv_block_stride * (long long)sizeof(CT);
   const int nblk = it.nblk;
-  // have_first: the first group's block numbers were fetched while the previous item was streaming
-  int phys_next = have_first ? phys_first : ((lane < G && lane < nblk) ? table[lane] : 0);
+  int phys_next = (lane < G && lane < nblk) ? table[lane] : 0;
   for (int n0 = 0; n0 < nblk; n0 += G) {
     const int phys = phys_next;
     const int nn = n0 + G + lane;
@@ -328,71 +325,29 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_kernel(const __grid_c
         }
       }
     };
-    // draw the id of the next item from the device-wide counter (static round-robin without one)
-    auto draw_issue = [&](long long prev) -> unsigned int {  // returns lane 0's raw ticket (other lanes: 0)
+    long long item = blockIdx.x;
+    for (int k = 0;; ++k) {
+      const bool done = item >= p.total_items;
+      ItemInfo it;
+      if (!done) it = decode_item<GT, BS>(p, item);
+      enqueue(k, item, done, it);
+      if (done) break;
+      if (it.nblk > 0)
+        attn_produce_item<CT>(p, it, pos, lane, stages, Impl::kStageBytes, Impl::kKBytes, full_bar, empty_bar, pol);
+      // (Measured, profiles/r05_attn_short_items.txt: drawing and prefetching two items ahead to hide the ticket /
+      // context-length / block-table round trips between short items made every short-item shape SLOWER -- the
+      // extra claimed item costs more at the tail than the bubbles it removes.)
+      if (p.sched == nullptr) {  // no counter slot left for this launch (see attach_sched): static round-robin
+        item += gridDim.x;
+        continue;
+      }
       unsigned int raw = 0;
-      if (p.sched != nullptr && lane == 0) {
+      if (lane == 0) {
         raw = atomicAdd(p.sched, 1u);
         if ((long long)raw == p.total_items - 1) *p.sched = 0u;  // the last draw of the launch: leave the counter at zero
       }
-      (void)prev;
-      return raw;
-    };
-    auto draw_finish = [&](unsigned int raw, long long prev) -> long long {
-      if (p.sched == nullptr) return prev + gridDim.x;
-      return (long long)__shfl_sync(0xffffffffu, raw, 0) + gridDim.x;
-    };
-    if (!p.lookahead) {
-      long long item = blockIdx.x;
-      for (int k = 0;; ++k) {
-        const bool done = item >= p.total_items;
-        ItemInfo it;
-        if (!done) it = decode_item<GT, BS>(p, item);
-        enqueue(k, item, done, it);
-        if (done) break;
-        if (it.nblk > 0)
-          attn_produce_item<CT>(p, it, pos, lane, stages, Impl::kStageBytes, Impl::kKBytes, full_bar, empty_bar, pol);
-        item = draw_finish(draw_issue(item), item);
-      }
-      return;
-    }
-    // Small items (a partition of a few dozen blocks streams in a few microseconds): the three dependent
-    // global-memory round trips between two items -- ticket, context length, first block-table group -- would
-    // drain the ring at every item boundary.  So the producer works two items ahead: while item k streams, the
-    // ticket of item k+2 is in flight and the context length / block numbers of item k+1 have already landed.
-    const int G = p.nstages < 32 ? p.nstages : 32;
-    const int per_part = p.num_seqs * p.tiles_per_seq;
-    auto prefetch = [&](long long item, int& ctx, int& phys) {  // loads only: nothing here waits
-      ctx = 0;
-      phys = 0;
-      if (item >= p.total_items) return;
-      const int part = (int)(item / per_part);
-      const int seq = (int)(item - (long long)part * per_part) / p.tiles_per_seq;
-      ctx = p.context_lens[seq];
-      const int b = part * p.partition_blocks + lane;
-      if (lane < G && b < p.max_num_blocks_per_seq) phys = p.block_tables[(long long)seq * p.max_num_blocks_per_seq + b];
-    };
-    long long cur = blockIdx.x, nxt;
-    int ctx_cur, phys_cur, ctx_nxt, phys_nxt;
-    prefetch(cur, ctx_cur, phys_cur);
-    nxt = cur < p.total_items ? draw_finish(draw_issue(cur), cur) : cur;
-    prefetch(nxt, ctx_nxt, phys_nxt);
-    for (int k = 0;; ++k) {
-      const bool done = cur >= p.total_items;
-      ItemInfo it;
-      if (!done) it = decode_item<GT, BS>(p, cur, ctx_cur);
-      enqueue(k, cur, done, it);
-      if (done) break;
-      // every CTA draws exactly one ticket past the end, never more (the counter's reset relies on it)
-      const bool more = nxt < p.total_items;
-      const unsigned int raw = more ? draw_issue(nxt) : 0u;
-      if (it.nblk > 0)
-        attn_produce_item<CT>(p, it, pos, lane, stages, Impl::kStageBytes, Impl::kKBytes, full_bar, empty_bar, pol, true,
-                              phys_cur);
-      const long long nn = more ? draw_finish(raw, nxt) : nxt;
-      cur = nxt; ctx_cur = ctx_nxt; phys_cur = phys_nxt;
-      nxt = nn;
-      prefetch(nxt, ctx_nxt, phys_nxt);
+      raw = __shfl_sync(0xffffffffu, raw, 0);
+      item = (long long)raw + gridDim.x;
     }
     return;
   }
@@ -700,10 +655,11 @@ __global__ void __launch_bounds__(128) paged_attn_reduce_kernel(
 // ---- host-side launch plumbing shared by both consumers ---------------------------------------------
 // Ring depth and shared-memory size for a consumer under a per-CTA budget.
 inline int attn_max_stages(int stage_bytes) {
-  // small stages (1-byte caches, short heads): a deeper ring rides out the per-item bubbles of short partitions
+  // (a 24-stage ring for 4 KiB stages measured no faster than 16 on any shape: profiles/r05_attn_short_items.txt)
   static const int env = getenv("B200_ATTN_MAX_STAGES") ? atoi(getenv("B200_ATTN_MAX_STAGES")) : 0;  // tuning knob
+  (void)stage_bytes;
   if (env >= 2 && env <= kMaxStages) return env;
-  return stage_bytes <= 4096 ? 24 : 16;
+  return 16;
 }
 inline int attn_smem_tail(int fixed_bytes, int gt, int head_size, int q_elt_bytes) {
   return fixed_bytes + kConsumerWarps * gt * head_size * 4 + kConsumerWarps * gt * 2 * 4 + 16 + kItemQueue * 16 +
@@ -734,12 +690,11 @@ int launch_attn(const AttnParams& p_in, int smem_budget, int sms, cudaStream_t s
   p.nstages = nst;
   p.nconsumers = nwa;
   // query rows travel through shared memory when a bulk copy can fetch them (16-byte aligned rows)
-  static const bool no_q_bulk = getenv("B200_ATTN_NO_QBULK") != nullptr;      // A/B knobs
-  static const bool no_lookahead = getenv("B200_ATTN_NO_LOOKAHEAD") != nullptr;
+  static const bool no_q_bulk = getenv("B200_ATTN_NO_QBULK") != nullptr;      // A/B knob
   p.q_bulk = !no_q_bulk && (reinterpret_cast<uintptr_t>(p.q) % 16 == 0) &&
              ((p.q_stride * (long long)sizeof(typename Impl::T)) % 16 == 0) &&
              ((Impl::D * (int)sizeof(typename Impl::T)) % 16 == 0);
-  p.lookahead = !no_lookahead && p.partition_blocks > 0 && p.partition_blocks <= 64;
+
   auto kern = paged_attn_kernel<Impl>;
   // per instantiation and per device (function attributes are per device): smem size -> resident CTAs per SM
   static int occ_smem[64] = {0}, occ_val[64] = {0};
