@@ -364,6 +364,11 @@ B200_API int b200_kv_enable_peer_access(int32_t dev, int32_t peer_dev);
  * (layer x {K,V}), built once at setup; runs: HOST [num_runs][2] = (block_start, num_blocks) as produced by the
  * reference's coalesce_blocks (vllm/utils.py:403-426).  One launch, max_ctas CTAs (0 = default).
  * Replaces nw_cache_out_kernel's put (kv_comm_kernels.cu:11-20); offsets are 64-bit. */
+/* OR this into a positive max_ctas: the caller guarantees that the source blocks of this put were complete when
+ * it was enqueued by something other than stream order behind the previous put (e.g. an event the stream waits
+ * for).  The put may then overlap the tail of the put before it (programmatic dependent launch); completion
+ * stays in stream order.  Without the flag a put starts reading only after everything before it has finished. */
+#define B200_KV_PUT_CHAINED (1 << 30)
 B200_API int b200_kv_put_blocks(const int64_t* src_ptrs, const int64_t* dst_ptrs, int32_t num_bufs,
                        const int32_t* runs, int32_t num_runs, int64_t block_bytes,
                        int32_t max_ctas, b200_stream_t stream);

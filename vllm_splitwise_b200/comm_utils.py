@@ -25,6 +25,7 @@ from . import _lib
 from .utils import MAX_SLOT_IDS
 
 HEAD_TYPES = [0, 1]  # 0 = keys, 1 = values (reference comm_utils.py:16)
+PUT_CHAINED = 1 << 30  # include/b200_kv.h B200_KV_PUT_CHAINED
 
 
 def pair_rank(rank: int, world_size: int, num_prompt_workers: int) -> int:
@@ -217,8 +218,12 @@ class KVCacheCommunicator:
         key = runs if isinstance(runs, tuple) else tuple(map(tuple, runs))
         if len(key) == 0:
             return
-        stream = self.comm_stream.cuda_stream if self.comm_stream is not None else \
-            torch.cuda.current_stream(self.device).cuda_stream
+        if self.comm_stream is not None:
+            # Side stream: every put is ordered behind the caller's cache writes by an event (_order_after_current),
+            # not by stream order behind the previous put, so consecutive puts may overlap (B200_KV_PUT_CHAINED).
+            stream, ctas = self.comm_stream.cuda_stream, max(0, self.max_ctas) | PUT_CHAINED
+        else:
+            stream, ctas = torch.cuda.current_stream(self.device).cuda_stream, self.max_ctas
         # this is the per-layer hot call of a prefill worker: switch devices only when the caller sits on another one
         switch = torch.cuda.current_device() != self._dev_index
         if switch:
@@ -229,11 +234,11 @@ class KVCacheCommunicator:
                 dev, n, tv, tpb, _ = self._device_table(key)
                 st = self._lib.b200_kv_put_blocks_table(self._src_base + 8 * first_buf, self._dst_base + 8 * first_buf,
                                                         num_bufs, dev.data_ptr(), n, tv, tpb, self.block_size,
-                                                        self.max_ctas, stream)
+                                                        ctas, stream)
             else:
                 arr, n = _runs_array(key)
                 st = self._lib.b200_kv_put_blocks(self._src_base + 8 * first_buf, self._dst_base + 8 * first_buf,
-                                                  num_bufs, arr, n, self.block_size, self.max_ctas, stream)
+                                                  num_bufs, arr, n, self.block_size, ctas, stream)
         finally:
             if switch:
                 torch.cuda.set_device(prev)

@@ -33,6 +33,7 @@ struct PutTable {
   long long block_bytes;
   const long long* src_ptrs;  // device arrays [num_bufs]
   const long long* dst_ptrs;
+  int chained;                // see put_begin / put_end
 };
 static_assert(sizeof(PutTable) <= 4000, "kernel parameter space");
 
@@ -83,6 +84,20 @@ __device__ __forceinline__ int find_run(const int* unit0, int n, int u) {
   return lo;
 }
 
+// Programmatic dependent launch between the puts of one communicator.  Every put lets its successor start at once
+// (launch_dependents).  A put launched as `chained` -- the caller guarantees that its source blocks were complete
+// when it was enqueued (side stream ordered by an event, comm_utils.py) -- streams immediately, overlapping the tail
+// of its predecessor and hiding its own ramp, and waits for the predecessor only before it EXITS: completion stays
+// transitive, so the signal kernel (an ordinary launch) still fires after every byte of every earlier put.  An
+// unchained put waits before it reads anything, like any dependent kernel.
+__device__ __forceinline__ void put_begin(int chained) {
+  griddep_launch_dependents();
+  if (!chained) griddep_wait();
+}
+__device__ __forceinline__ void put_end(int chained) {
+  if (chained) griddep_wait();
+}
+
 // ---- SIMT variant -------------------------------------------------------------------------------------------
 // Work = num_bufs x (sum of run lengths) blocks cut into 4 KiB chunks.  Every WARP takes chunks on its own
 // (neighbouring warps take neighbouring chunks): 8 independent 16-byte loads per lane from local HBM, then the 8
@@ -117,8 +132,10 @@ __device__ __forceinline__ void put_chunks(const int* s_tab, int n, int num_bufs
 
 __global__ void __launch_bounds__(kPutThreads) kv_put_blocks_kernel(const __grid_constant__ PutTable t) {
   extern __shared__ __align__(16) int s_tab[];
+  put_begin(t.chained);
   stage_runs(s_tab, t.start, t.len, t.num_runs, t.block_bytes / 16, kChunkVecs);
   put_chunks(s_tab, t.num_runs, t.num_bufs, t.block_bytes, t.src_ptrs, t.dst_ptrs);
+  put_end(t.chained);
 }
 
 // Same copy for run lists that do not fit the kernel-parameter table: starts and lengths live in DEVICE memory
@@ -126,10 +143,12 @@ __global__ void __launch_bounds__(kPutThreads) kv_put_blocks_kernel(const __grid
 // block list 2 x num_layers times).  tab = [start[n] | len[n] | host-side tile prefix (unused here)] int32.
 __global__ void __launch_bounds__(kPutThreads) kv_put_blocks_table_kernel(
     const int* __restrict__ tab, int num_runs, int num_bufs, long long block_bytes,
-    const long long* __restrict__ src_ptrs, const long long* __restrict__ dst_ptrs) {
+    const long long* __restrict__ src_ptrs, const long long* __restrict__ dst_ptrs, int chained) {
   extern __shared__ __align__(16) int s_tab[];
+  put_begin(chained);
   stage_runs(s_tab, tab, tab + num_runs, num_runs, block_bytes / 16, kChunkVecs);
   put_chunks(s_tab, num_runs, num_bufs, block_bytes, src_ptrs, dst_ptrs);
+  put_end(chained);
 }
 
 // ---- bulk-copy variant ----------------------------------------------------------------------------------------
@@ -210,18 +229,22 @@ __global__ void __launch_bounds__(kBulkThreads) kv_put_blocks_bulk_kernel(const 
   extern __shared__ __align__(128) uint8_t bulk_smem[];
   BulkShared* sh = bulk_setup(bulk_smem);
   int* s_tab = reinterpret_cast<int*>(sh + 1);
+  put_begin(t.chained);
   stage_runs(s_tab, t.start, t.len, t.num_runs, t.block_bytes / 16, t.tile_vecs);
   put_tiles_bulk(bulk_smem, sh, s_tab, t.num_runs, t.num_bufs, t.tile_vecs, t.block_bytes, t.src_ptrs, t.dst_ptrs);
+  put_end(t.chained);
 }
 
 __global__ void __launch_bounds__(kBulkThreads) kv_put_blocks_table_bulk_kernel(
     const int* __restrict__ tab, int num_runs, int num_bufs, int tile_vecs, long long block_bytes,
-    const long long* __restrict__ src_ptrs, const long long* __restrict__ dst_ptrs) {
+    const long long* __restrict__ src_ptrs, const long long* __restrict__ dst_ptrs, int chained) {
   extern __shared__ __align__(128) uint8_t bulk_smem[];
   BulkShared* sh = bulk_setup(bulk_smem);
   int* s_tab = reinterpret_cast<int*>(sh + 1);
+  put_begin(chained);
   stage_runs(s_tab, tab, tab + num_runs, num_runs, block_bytes / 16, tile_vecs);
   put_tiles_bulk(bulk_smem, sh, s_tab, num_runs, num_bufs, tile_vecs, block_bytes, src_ptrs, dst_ptrs);
+  put_end(chained);
 }
 
 __global__ void kv_signal_kernel(unsigned long long* flag, unsigned long long value) {
@@ -380,6 +403,8 @@ B200_API int b200_kv_put_blocks(const int64_t* src_ptrs, const int64_t* dst_ptrs
   if (!src_ptrs || !dst_ptrs || !runs || num_bufs < 0 || num_runs < 0 || block_bytes <= 0) return B200_ERR_ARG;
   if (block_bytes % 16 != 0) return B200_ERR_ALIGN;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int chained = (max_ctas > 0 && (max_ctas & B200_KV_PUT_CHAINED)) ? 1 : 0;
+  if (max_ctas > 0) max_ctas &= ~B200_KV_PUT_CHAINED;
   if (max_ctas <= 0) max_ctas = put_default_ctas();
   const bool bulk = put_variant() == 1;
   const long long block_vecs = block_bytes / 16;
@@ -401,18 +426,19 @@ B200_API int b200_kv_put_blocks(const int64_t* src_ptrs, const int64_t* dst_ptrs
     t.block_bytes = block_bytes;
     t.src_ptrs = reinterpret_cast<const long long*>(src_ptrs);
     t.dst_ptrs = reinterpret_cast<const long long*>(dst_ptrs);
+    t.chained = chained;
     units *= num_bufs;
     if (units == 0) continue;
     if (bulk) {
       const size_t smem = bulk_smem_bytes(t.num_runs);
       B200_CUDA_TRY(allow_smem(kv_put_blocks_bulk_kernel, smem, granted));
       const int grid = (int)std::min<long long>(units, max_ctas);
-      kv_put_blocks_bulk_kernel<<<grid, kBulkThreads, smem, stream>>>(t);
+      B200_CUDA_TRY(launch_kernel(kv_put_blocks_bulk_kernel, dim3(grid), dim3(kBulkThreads), smem, stream, true, t));
     } else {
       const size_t smem = ((size_t)3 * t.num_runs + 1) * sizeof(int);
       const long long want = (units + kPutThreads / 32 - 1) / (kPutThreads / 32);
       const int grid = (int)std::min<long long>(want, max_ctas);
-      kv_put_blocks_kernel<<<grid, kPutThreads, smem, stream>>>(t);
+      B200_CUDA_TRY(launch_kernel(kv_put_blocks_kernel, dim3(grid), dim3(kPutThreads), smem, stream, true, t));
     }
     B200_LAUNCH_CHECK();
   }
@@ -453,6 +479,8 @@ B200_API int b200_kv_put_blocks_table(const int64_t* src_ptrs, const int64_t* ds
   const size_t tab_bytes = ((size_t)3 * num_runs + 1) * sizeof(int);
   if (tab_bytes > 200 * 1024) return B200_ERR_ARG;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int chained = (max_ctas > 0 && (max_ctas & B200_KV_PUT_CHAINED)) ? 1 : 0;
+  if (max_ctas > 0) max_ctas &= ~B200_KV_PUT_CHAINED;
   if (max_ctas <= 0) max_ctas = put_default_ctas();
   const long long* sp = reinterpret_cast<const long long*>(src_ptrs);
   const long long* dp = reinterpret_cast<const long long*>(dst_ptrs);
@@ -461,15 +489,16 @@ B200_API int b200_kv_put_blocks_table(const int64_t* src_ptrs, const int64_t* ds
     const size_t smem = bulk_smem_bytes(num_runs);
     B200_CUDA_TRY(allow_smem(kv_put_blocks_table_bulk_kernel, smem, granted_bulk));
     const int grid = (int)std::min<long long>(tiles_per_buf * num_bufs, max_ctas);
-    kv_put_blocks_table_bulk_kernel<<<grid, kBulkThreads, smem, stream>>>(dev_table, num_runs, num_bufs, tile_vecs,
-                                                                         block_bytes, sp, dp);
+    B200_CUDA_TRY(launch_kernel(kv_put_blocks_table_bulk_kernel, dim3(grid), dim3(kBulkThreads), smem, stream, true,
+                                dev_table, num_runs, num_bufs, tile_vecs, (long long)block_bytes, sp, dp, chained));
   } else {
     B200_CUDA_TRY(allow_smem(kv_put_blocks_table_kernel, tab_bytes, granted_simt));
     // chunks per buffer <= (tile_vecs / kChunkVecs + 1) per tile: size the grid from the tile count
     const long long chunks = tiles_per_buf * ((tile_vecs + kChunkVecs - 1) / kChunkVecs) * num_bufs;
     const long long want = (chunks + kPutThreads / 32 - 1) / (kPutThreads / 32);
     const int grid = (int)std::min<long long>(want, max_ctas);
-    kv_put_blocks_table_kernel<<<grid, kPutThreads, tab_bytes, stream>>>(dev_table, num_runs, num_bufs, block_bytes, sp, dp);
+    B200_CUDA_TRY(launch_kernel(kv_put_blocks_table_kernel, dim3(grid), dim3(kPutThreads), tab_bytes, stream, true, dev_table,
+                                num_runs, num_bufs, (long long)block_bytes, sp, dp, chained));
   }
   B200_LAUNCH_CHECK();
   return B200_OK;

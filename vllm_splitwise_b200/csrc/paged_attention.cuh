@@ -59,6 +59,7 @@ struct AttnParams {
   int nstages;           // ring depth; always a multiple of nconsumers
   int nconsumers;        // consumer warps that take blocks (<= kConsumerWarps)
   int q_bulk;            // 1: the query rows of an item reach the consumers through shared memory (bulk copy)
+  int quad;              // 1: v2 signature on the tensor-core consumer -- every consumer warp owns a whole item
   long long total_items; // max_num_partitions * num_seqs * tiles_per_seq
   long long q_stride;
   long long kv_block_stride;
@@ -249,6 +250,168 @@ __device__ __forceinline__ void attn_reduce_in_kernel(const AttnParams& p, const
   }
 }
 
+// ---- quad mode (v2 signature, tensor-core consumer) ----------------------------------------------
+// Under the v2 signature every item is one 512-token partition: 32 blocks shared by four warps is 8 blocks per
+// warp, then a cross-warp merge through shared memory and two CTA-wide barriers -- measured, that per-item
+// epilogue left C4 through the v2 signature at 0.67 of the copy peak against 0.95 for the unsplit v1 call
+// (profiles/r05_attn_short_items.txt).  Here the unit of work is a QUAD of four consecutive items and every
+// consumer warp owns one of them outright: its own query fragments, all of its partition's blocks, and the
+// partial written straight from its registers (Impl::store_partial) -- no merge, no barrier between items.
+// The producer interleaves the four block streams (virtual block v -> warp v % 4, round v / 4), so ring slot
+// ownership is unchanged (global block index modulo 4); rounds a shorter item does not have are passed through the
+// ring as empty slots.  Query rows are staged in the (otherwise unused) merge buffer, two quads deep.
+constexpr int kQuadQueue = 2;
+
+template <int BS>
+__device__ __forceinline__ int quad_item_blocks(const AttnParams& p, long long item, int ctx) {
+  if (ctx < 0) return 0;
+  const int part = (int)(item / ((long long)p.num_seqs * p.tiles_per_seq));
+  const int nblk_ctx = (ctx + BS - 1) / BS;
+  const int b0 = part * p.partition_blocks;
+  return max(0, min(nblk_ctx, b0 + p.partition_blocks) - b0);
+}
+
+template <class Impl>
+__device__ __forceinline__ void attn_quad_mode(const AttnParams& p, unsigned char* stages, unsigned char* q_stage,
+                                               long long* quad_q, int* ctx8, uint64_t* full_bar, uint64_t* empty_bar,
+                                               uint64_t* iq_full, uint64_t* iq_empty, int warp, int lane) {
+  using T = typename Impl::T;
+  using CT = typename Impl::CT;
+  constexpr int D = Impl::D, BS = Impl::BS, GT = Impl::GT;
+  constexpr int NW = kConsumerWarps;
+  constexpr int QB = GT * D * (int)sizeof(T);
+  static_assert(NW == 4 && sizeof(T) == 2, "quad mode: four consumer warps, query staging aliases the merge buffer");
+  const int nst = p.nstages;
+  const long long total_quads = (p.total_items + 3) >> 2;
+
+  if (warp == NW) {
+    // ================= producer =================
+    const uint64_t pol = l2_policy_evict_first();
+    const int G = nst < 32 ? nst : 32;  // a multiple of 4 (nstages is)
+    const int w = lane & 3;             // the consumer warp this lane feeds: virtual block n0 + lane, n0 % 4 == 0
+    const int kbytes = Impl::kKBytes;
+    const long long blk_bytes = p.kv_block_stride * (long long)sizeof(CT);
+    int slot0 = 0, fill0 = 0;
+    long long quad = blockIdx.x;
+    for (int k = 0;; ++k) {
+      const int qs = k % kQuadQueue;
+      const bool done = quad >= total_quads;
+      const long long item = 4 * quad + w;
+      const bool valid = !done && item < p.total_items;
+      ItemInfo it;
+      it.nblk = 0; it.ctx = -1; it.seq = 0; it.kvh = 0; it.b0 = 0; it.ng = 0; it.head0 = 0;
+      if (valid) it = decode_item<GT, BS>(p, item);
+      const int my_n = valid ? it.nblk : 0;
+      int rounds = my_n;
+      rounds = max(rounds, __shfl_xor_sync(0xffffffffu, rounds, 1));
+      rounds = max(rounds, __shfl_xor_sync(0xffffffffu, rounds, 2));
+      // ---- queue entry: quad id, the four context lengths, the four query tiles ----
+      if (lane == 0 && k >= kQuadQueue) mbar_wait(&iq_empty[qs], ((k / kQuadQueue) - 1) & 1);
+      __syncwarp();
+      if (lane < 4) ctx8[qs * 4 + lane] = valid ? it.ctx : -1;
+      if (lane == 0) quad_q[qs] = done ? -1 : quad;
+      uint32_t qbytes = (lane < 4 && my_n > 0 && p.q_bulk) ? (uint32_t)(it.ng * D * (int)sizeof(T)) : 0u;
+      uint32_t qtot = qbytes + __shfl_xor_sync(0xffffffffu, qbytes, 1);
+      qtot += __shfl_xor_sync(0xffffffffu, qtot, 2);
+      __syncwarp();
+      if (lane == 0) {
+        if (qtot) mbar_arrive_expect_tx(&iq_full[qs], qtot);
+        else mbar_arrive(&iq_full[qs]);
+      }
+      __syncwarp();
+      if (qbytes)
+        bulk_g2s_plain(q_stage + (qs * 4 + lane) * QB,
+                       static_cast<const T*>(p.q) + (long long)it.seq * p.q_stride + (long long)it.head0 * D, qbytes,
+                       &iq_full[qs]);
+      if (done) break;
+      // ---- the four block streams, interleaved ----
+      const int* table = p.block_tables + (long long)it.seq * p.max_num_blocks_per_seq + it.b0;
+      const unsigned char* kbase = static_cast<const unsigned char*>(p.k_cache) + (long long)it.kvh * p.kv_head_stride * (long long)sizeof(CT);
+      const unsigned char* vbase = static_cast<const unsigned char*>(p.v_cache) + (long long)it.kvh * p.kv_head_stride * (long long)sizeof(CT);
+      const int nvirt = 4 * rounds;
+      int phys_next = (lane < G && (lane >> 2) < my_n) ? table[lane >> 2] : 0;
+      for (int n0 = 0; n0 < nvirt; n0 += G) {
+        const int r = (n0 + lane) >> 2;
+        const bool virt = lane < G && n0 + lane < nvirt;
+        const bool real = virt && r < my_n;
+        const int phys = phys_next;
+        const int rn = (n0 + G + lane) >> 2;
+        phys_next = (lane < G && rn < my_n) ? table[rn] : 0;  // in flight while this group is issued
+        int slot = slot0 + lane, fill = fill0;
+        if (slot >= nst) { slot -= nst; ++fill; }
+        bool pending = virt;
+        const long long off = (long long)phys * blk_bytes;
+        unsigned char* dst = stages + (size_t)slot * Impl::kStageBytes;
+        while (__any_sync(0xffffffffu, pending)) {
+          if (pending && (fill == 0 || mbar_try_wait(&empty_bar[slot], (fill - 1) & 1))) {
+            if (real) {
+              mbar_arrive_expect_tx(&full_bar[slot], 2 * kbytes);
+              bulk_g2s(dst, kbase + off, kbytes, &full_bar[slot], pol);
+              bulk_g2s(dst + kbytes, vbase + off, kbytes, &full_bar[slot], pol);
+            } else {
+              mbar_arrive(&full_bar[slot]);  // a round this warp's item does not have: an empty slot
+            }
+            pending = false;
+          }
+        }
+        const int cnt = min(G, nvirt - n0);
+        slot0 += cnt;
+        if (slot0 >= nst) { slot0 -= nst; ++fill0; }
+      }
+      if (p.sched == nullptr) {
+        quad += gridDim.x;
+        continue;
+      }
+      unsigned int raw = 0;
+      if (lane == 0) {
+        raw = atomicAdd(p.sched, 1u);
+        if ((long long)raw == total_quads - 1) *p.sched = 0u;  // the last draw of the launch: leave the counter at zero
+      }
+      raw = __shfl_sync(0xffffffffu, raw, 0);
+      quad = (long long)raw + gridDim.x;
+    }
+    return;
+  }
+
+  // ================= consumers: warp w owns item 4 * quad + w =================
+  int slot = warp;
+  uint32_t parity = 0;
+  typename Impl::State st;
+  for (int k = 0;; ++k) {
+    const int qs = k % kQuadQueue;
+    mbar_wait(&iq_full[qs], (k / kQuadQueue) & 1);
+    const long long quad = quad_q[qs];
+    if (quad < 0) break;
+    int rounds = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) rounds = max(rounds, quad_item_blocks<BS>(p, 4 * quad + j, ctx8[qs * 4 + j]));
+    const long long item = 4 * quad + warp;
+    const int ctx = ctx8[qs * 4 + warp];
+    ItemInfo it;
+    it.nblk = 0;
+    if (ctx >= 0) it = decode_item<GT, BS>(p, item, ctx);
+    const int my_n = ctx >= 0 ? it.nblk : 0;
+    if (my_n > 0) {
+      Impl::init(st);
+      const T* qrows = p.q_bulk ? reinterpret_cast<const T*>(q_stage + (qs * 4 + warp) * QB)
+                                : static_cast<const T*>(p.q) + (long long)it.seq * p.q_stride + (long long)it.head0 * D;
+      Impl::begin_item(st, p, it, qrows, nullptr, warp, lane);
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&iq_empty[qs]);  // every warp arrives, with or without an item
+    for (int r = 0; r < rounds; ++r) {
+      unsigned char* ks = stages + (size_t)slot * Impl::kStageBytes;
+      mbar_wait(&full_bar[slot], parity);
+      if (r < my_n) Impl::block(st, p, it, ks, ks + Impl::kKBytes, it.b0 + r, nullptr, warp, lane);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty_bar[slot]);
+      slot += NW;
+      if (slot >= nst) { slot -= nst; parity ^= 1u; }
+    }
+    if (my_n > 0) Impl::store_partial(st, p, it, lane);
+  }
+}
+
 // ---- the persistent kernel ------------------------------------------------------------------
 // Impl supplies the consumer: types T (query/out) and CT (cache), tile constants D, BS, GT,
 // kKBytes/kStageBytes, kFixedBytes of private shared memory, a per-thread State and
@@ -296,6 +459,14 @@ __global__ void __launch_bounds__(kAttnThreads) paged_attn_kernel(const __grid_c
   // Everything above overlaps the tail of the previous kernel of the stream when this launch is a programmatic
   // dependent (it always is: launch_attn); nothing below may run before that kernel's memory is visible.
   griddep_wait();
+
+  if constexpr (Impl::kQuad) {
+    if (p.quad) {  // query staging (2 quads x 4 warps) aliases the merge buffer; ids and context lengths the item queue
+      attn_quad_mode<Impl>(p, stages, reinterpret_cast<unsigned char*>(red_acc), item_q,
+                           reinterpret_cast<int*>(item_q + kQuadQueue), full_bar, empty_bar, iq_full, iq_empty, warp, lane);
+      return;
+    }
+  }
 
   if (warp == NW) {
     // ================= producer =================
@@ -466,6 +637,8 @@ struct SimtImpl {
     float m_run[GT], l_run[GT], alibi[GT];
     float acc[GT][VIT];
   };
+  static constexpr bool kQuad = false;  // the SIMT consumer shares its query tile between the warps
+  __device__ __forceinline__ static void store_partial(State&, const AttnParams&, const ItemInfo&, int) {}
 
   __device__ __forceinline__ static void init(State& st) {
 #pragma unroll
@@ -709,8 +882,11 @@ int launch_attn(const AttnParams& p_in, int smem_budget, int sms, cudaStream_t s
     occ_val[dev] = occ;
     occ_smem[dev] = smem;
   }
+  static const bool no_quad = getenv("B200_ATTN_NO_QUAD") != nullptr;  // A/B knob
+  p.quad = Impl::kQuad && !no_quad && p.always_partials && nwa == kConsumerWarps && p.partition_blocks > 0;
+  const long long units = p.quad ? (p.total_items + 3) / 4 : p.total_items;
   long long grid = (long long)occ_val[dev] * sms;
-  if (grid > p.total_items) grid = p.total_items;
+  if (grid > units) grid = units;
   B200_CUDA_TRY(launch_kernel(kern, dim3((unsigned)grid), dim3(kAttnThreads), (size_t)smem, stream, /*pdl=*/true, p));
   B200_LAUNCH_CHECK();
   return B200_OK;

@@ -337,6 +337,33 @@ struct MmaImpl {
     }
   }
 
+  // One warp processed a whole partition by itself (quad mode): normalise its state and write the partition's
+  // partial straight from registers in the reference's tmp_out / exp_sums / max_logits format -- the same formula as
+  // attn_merge_store with a single contributor.
+  static constexpr bool kQuad = true;
+  __device__ __forceinline__ static void store_partial(State& st, const AttnParams& p, const ItemInfo& it, int lane) {
+    const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      float l = st.l_run[r];
+      l += __shfl_xor_sync(0xffffffffu, l, 1);
+      l += __shfl_xor_sync(0xffffffffu, l, 2);
+      const int h = g + 8 * r;
+      if (h < it.ng) {
+        const float inv = __fdividef(1.f, l + 1e-6f);
+        const long long pi = ((long long)it.seq * p.num_heads + it.head0 + h) * p.max_num_partitions + it.part;
+        T* row = static_cast<T*>(p.tmp_out) + pi * D;
+#pragma unroll
+        for (int i = 0; i < NT; ++i)
+          *reinterpret_cast<uint32_t*>(row + i * 8 + 2 * t) = pack2<T>(st.o[i][2 * r] * inv, st.o[i][2 * r + 1] * inv);
+        if (t == 0) {
+          p.exp_sums[pi] = l;
+          p.max_logits[pi] = st.m_run[r] * kLn2;
+        }
+      }
+    }
+  }
+
   __device__ __forceinline__ static void end_item(State& st, const ItemInfo& it, float* red_acc, float* red_ml,
                                                   int warp, int lane) {
     const int g = lane >> 2, t = lane & 3;
