@@ -38,5 +38,5 @@ wait $P1; wait $P2
 g++ -shared -o "$OUT/vllm_ref_C.so" "$OUT/attention_kernels.o" "$OUT/cache_kernels.o" \
     "$OUT/cuda_utils_kernels.o" "$OUT/pos_encoding_kernels.o" "$OUT/custom_all_reduce.o" "$OUT/ref_binding.o" \
     -L"$TORCH_LIB" -Wl,-rpath,"$TORCH_LIB" -lc10 -lc10_cuda -ltorch_cpu -ltorch_cuda -ltorch -ltorch_python \
-    -L/usr/local/cuda/lib64 -lcudart
+    -L/usr/local/cuda/lib64 -lcudart -L/usr/local/cuda/lib64/stubs -lcuda  # custom_all_reduce.cuh calls the driver API
 echo "[build_ref] built $OUT/vllm_ref_C.so"

@@ -45,7 +45,12 @@ def load_ref_cuda():
             return None
         spec = importlib.util.spec_from_file_location("vllm_ref_C", path)
         mod = importlib.util.module_from_spec(spec)
-        spec.loader.exec_module(mod)
+        try:
+            spec.loader.exec_module(mod)
+        except ImportError:   # no CUDA driver on this machine (the module links libcuda for the reference all-reduce)
+            if torch.cuda.is_available():
+                raise
+            return None
         _ref_mod = mod
     return _ref_mod
 

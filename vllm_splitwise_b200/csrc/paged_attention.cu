@@ -244,7 +244,10 @@ int plan_v1_split(const b200_paged_attn_args_t* a, int tiles_per_seq, int slots,
   // percent (partials + per-item epilogue).  So split only to fill the machine, never to balance it.
   if (base_items * 4 >= (long long)slots * 3) return 1;
   const int min_pb = 8;
-  int np = (int)std::min<long long>((slots + base_items - 1) / base_items, kMaxSplit);
+  // The largest partition count whose items still run in ONE wave (items <= resident CTAs): one item more than
+  // that and a second, nearly empty wave doubles the call (measured, profiles/r05_attn_quad.txt: the reference
+  // benchmark shape, 64 base items on 296 CTAs, takes 35.7 us with 4 partitions and 48.3 us with 5).
+  int np = (int)std::min<long long>(std::max<long long>(1, slots / base_items), kMaxSplit);
   np = std::min(np, std::max(1, max_blocks / min_pb));
   int best_np = 1, best_pb = 0;
   for (; np > 1; --np) {

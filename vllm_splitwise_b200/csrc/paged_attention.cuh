@@ -883,9 +883,12 @@ int launch_attn(const AttnParams& p_in, int smem_budget, int sms, cudaStream_t s
     occ_smem[dev] = smem;
   }
   static const bool no_quad = getenv("B200_ATTN_NO_QUAD") != nullptr;  // A/B knob
-  p.quad = Impl::kQuad && !no_quad && p.always_partials && nwa == kConsumerWarps && p.partition_blocks > 0;
-  const long long units = p.quad ? (p.total_items + 3) / 4 : p.total_items;
   long long grid = (long long)occ_val[dev] * sms;
+  // quad mode needs enough quads to keep every resident CTA busy (measured, profiles/r05_attn_quad.txt: with 128
+  // quads for 296 CTAs the reference benchmark shape loses 7 %, with 512 quads C3 tp=8 gains 13 %)
+  p.quad = Impl::kQuad && !no_quad && p.always_partials && nwa == kConsumerWarps && p.partition_blocks > 0 &&
+           (p.total_items + 3) / 4 >= grid * 3 / 2;
+  const long long units = p.quad ? (p.total_items + 3) / 4 : p.total_items;
   if (grid > units) grid = units;
   B200_CUDA_TRY(launch_kernel(kern, dim3((unsigned)grid), dim3(kAttnThreads), (size_t)smem, stream, /*pdl=*/true, p));
   B200_LAUNCH_CHECK();
