@@ -31,7 +31,10 @@ namespace tc {
 constexpr int kD = 128;        // head size of this kernel
 constexpr int kBM = 128;       // query rows per CTA = UMMA M
 constexpr int kBN = 128;       // KV tokens per tile = UMMA N of Q.K^T
-constexpr int kStages = 2;
+// K and V ring depth.  ncu (profiles/r05_ctx_tc_stalls.txt): with two stages the V loaders spend 80 % of a tile period
+// between issuing a tile and seeing it land (L2 latency under load ~2 us), i.e. the kernel was bound by the bytes it
+// could keep in flight (one K + one V tile per SM); three stages is what 227 KiB of shared memory holds next to Q.
+constexpr int kStages = 3;
 constexpr int kTileBytes = kBN * kD * 2;  // 32 KiB: one Q, K or V tile
 constexpr int kSoftmaxThreads = 256, kKLoaderThreads = 64, kVLoaderThreads = 128;
 constexpr int kMmaWarp = kSoftmaxThreads / 32;
@@ -39,7 +42,7 @@ constexpr int kMmaWarp = kSoftmaxThreads / 32;
 // launched with 128 registers per thread; setmaxnreg moves registers from the loader groups to the softmax groups.
 constexpr int kThreads = 512;
 constexpr int kRegsSoftmax = 168, kRegsOther = 88;  // (2*168 + 2*88) * 128 threads = 64 Ki registers
-constexpr int kSmemBytes = (1 + 2 * kStages) * kTileBytes + 256 + 3 * 2 * 128 * 4;
+constexpr int kSmemBytes = (1 + 2 * kStages) * kTileBytes + 256 + 2 * 2 * 128 * 4;
 
 // ---- tcgen05 wrappers --------------------------------------------------------------------------
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -110,6 +113,14 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
+// cp.async.wait_group with a run-time bound (0 .. kStages - 1 groups may stay in flight)
+__device__ __forceinline__ void cp_async_wait_upto(int n) {
+  if (n <= 0) cp_async_wait<0>();
+  else if (n == 1) cp_async_wait<1>();
+  else cp_async_wait<2>();
+}
+static_assert(kStages <= 3, "cp_async_wait_upto covers up to two groups in flight");
+
 struct Barriers {
   uint64_t q_full;
   uint64_t k_full[kStages], k_empty[kStages], v_full[kStages], v_empty[kStages];
@@ -117,9 +128,8 @@ struct Barriers {
   uint32_t tmem_base;
 };
 struct Exchange {        // between the two threads of a query row
-  float m[2][2][128];    // [tile parity][column half][row] tile maximum
-  float l[2][128];       // [column half][row] partial denominators
-};
+  float m[2][2][128];    // [tile parity][column half][row] tile maximum; after the last tile the free parity slot carries
+};                       // the partial denominators
 
 // granule index -> (row, d-octet) for sources laid out [row][D]: a warp covers 8 rows x 4 octets, i.e. 64-byte
 // global segments and four conflict-free 128-byte shared-memory lines
@@ -355,9 +365,9 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       l_run += (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
     }
 
-    xch->l[half][row] = l_run;
+    xch->m[n_tiles & 1][half][row] = l_run;  // the slot the last tile did not use
     asm volatile("bar.sync %0, 64;" ::"r"(2 + (warp & 3)) : "memory");
-    const float inv = 1.f / (l_run + xch->l[half ^ 1][row]);
+    const float inv = 1.f / (l_run + xch->m[n_tiles & 1][half ^ 1][row]);
     mbar_wait(&bar->o_full, (n_tiles - 1) & 1);
     tc_fence_after();
     MT* orow = static_cast<MT*>(p.o) + (start + qrow) * p.o_ts + (int64_t)head * p.o_hs + 64 * half;
@@ -388,8 +398,8 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       const uint32_t q_addr = smem_u32(q_s);
       mbar_wait(&bar->q_full, 0);
       auto issue_qk = [&](int i) {  // S_i = Q.K_i^T into S buffer i%3
-        const int st = i & 1;
-        mbar_wait(&bar->k_full[st], (i >> 1) & 1);
+        const int st = i % kStages;
+        mbar_wait(&bar->k_full[st], (i / kStages) & 1);
         tc_fence_after();
         const uint32_t k_addr = smem_u32(k_s + st * TILE_UNITS);
 #pragma unroll
@@ -404,8 +414,8 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       if (n_tiles > 1) issue_qk(1);
       for (int j = 0; j < n_tiles; ++j) {
         {  // O += P_j.V_j (first: it is on the softmax warps' critical path)
-          const int st = j & 1, sb = j % 3;
-          mbar_wait(&bar->v_full[st], (j >> 1) & 1);
+          const int st = j % kStages, sb = j % 3;
+          mbar_wait(&bar->v_full[st], (j / kStages) & 1);
           mbar_wait(&bar->p_full[sb], (j / 3) & 1);  // implies the softmax threads have seen O_{j-1} (and rescaled it)
           tc_fence_after();
           const uint32_t v_addr = smem_u32(v_s + st * TILE_UNITS);
@@ -449,17 +459,17 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
     cp_async_wait<1>();
     fence_proxy_async_smem();
     mbar_arrive(&bar->q_full);
-    if (n_tiles > 1) {
-      issue_k(1, 1);
+    for (int t = 1; t < kStages && t < n_tiles; ++t) {
+      issue_k(t, t);
       cp_async_commit();
     }
     for (int i = 0; i < n_tiles; ++i) {
-      if (i + 1 < n_tiles) cp_async_wait<1>(); else cp_async_wait<0>();
+      cp_async_wait_upto(min(kStages - 1, n_tiles - 1 - i));  // tiles issued after tile i may still be in flight
       fence_proxy_async_smem();
-      mbar_arrive(&bar->k_full[i & 1]);
-      if (i + 2 < n_tiles) {
-        mbar_wait(&bar->k_empty[i & 1], (i >> 1) & 1);
-        issue_k(i + 2, i & 1);
+      mbar_arrive(&bar->k_full[i % kStages]);
+      if (i + kStages < n_tiles) {
+        mbar_wait(&bar->k_empty[i % kStages], (i / kStages) & 1);
+        issue_k(i + kStages, i % kStages);
         cp_async_commit();
       }
     }
@@ -481,28 +491,26 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
         load_rows<MT, kVLoaderThreads, true>(Vs, vn + (int64_t)n0 * p.v_ts, p.v_ts, q_len - n0, lt);
       }
     };
-    issue_v(0, 0);
-    cp_async_commit();
-    if (n_tiles > 1) {
-      issue_v(1, 1);
+    for (int t = 0; t < kStages && t < n_tiles; ++t) {
+      issue_v(t, t);
       cp_async_commit();
     }
     for (int i = 0; i < n_tiles; ++i) {
-      if (i + 1 < n_tiles) cp_async_wait<1>(); else cp_async_wait<0>();
+      cp_async_wait_upto(min(kStages - 1, n_tiles - 1 - i));
       if (i < n_ctx_tiles && i * kBN + kBN > ctx_len && ((ctx_len - i * kBN) & 7)) {
         // the token octet that straddles ctx_len: slots past the end are stale cache memory (may be NaN / Inf)
         asm volatile("bar.sync 1, %0;" ::"n"(kVLoaderThreads) : "memory");  // every V loader's copies of tile i landed
         const int tgb = (ctx_len - i * kBN) >> 3, rem = (ctx_len - i * kBN) & 7;
         for (int d = lt; d < kD; d += kVLoaderThreads) {
-          MT* gp = reinterpret_cast<MT*>(&v_s[(i & 1) * TILE_UNITS + tgb * kD + d]);
+          MT* gp = reinterpret_cast<MT*>(&v_s[(i % kStages) * TILE_UNITS + tgb * kD + d]);
           for (int x = rem; x < 8; ++x) gp[x] = MT(0.f);
         }
       }
       fence_proxy_async_smem();
-      mbar_arrive(&bar->v_full[i & 1]);
-      if (i + 2 < n_tiles) {
-        mbar_wait(&bar->v_empty[i & 1], (i >> 1) & 1);
-        issue_v(i + 2, i & 1);
+      mbar_arrive(&bar->v_full[i % kStages]);
+      if (i + kStages < n_tiles) {
+        mbar_wait(&bar->v_empty[i % kStages], (i / kStages) & 1);
+        issue_v(i + kStages, i % kStages);
         cp_async_commit();
       }
     }
