@@ -124,7 +124,7 @@ static_assert(kStages <= 3, "cp_async_wait_upto covers up to two groups in fligh
 struct Barriers {
   uint64_t q_full;
   uint64_t k_full[kStages], k_empty[kStages], v_full[kStages], v_empty[kStages];
-  uint64_t s_full[3], p_full[3], o_full;
+  uint64_t s_full[3], p_full[3], o_full[4];
   uint32_t tmem_base;
 };
 struct Exchange {        // between the two threads of a query row
@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       mbar_init(&bar->s_full[s], 1);
       mbar_init(&bar->p_full[s], kSoftmaxThreads);
     }
-    mbar_init(&bar->o_full, 1);
+    for (int s = 0; s < 4; ++s) mbar_init(&bar->o_full[s], 1);
     mbar_fence_init();
   }
   if (warp == kMmaWarp) tmem_alloc_512(&bar->tmem_base);
@@ -278,6 +278,14 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
     // maximum has grown by more than 2^8, so that the O accumulator in TMEM is rescaled rarely (exact either way:
     // numerator and denominator carry the same reference point).
     float m_used = -INFINITY, l_run = 0.f;
+    // Completion of P_t.V_t is signalled on o_full[t % 4].  The softmax threads need it only when they rescale O
+    // (rare) and at the very end, but an mbarrier phase must be observed before the one after it on the same barrier
+    // can complete -- so tile t is observed, in order, at the latest before these threads release tile t + 4
+    // (by then it completed long ago: no stall), or right away when a rescale needs O.
+    int o_next = 0;  // first tile whose P.V completion these threads have not observed yet
+    auto observe_o_upto = [&](int last) {  // tiles o_next .. last
+      for (; o_next <= last; ++o_next) mbar_wait(&bar->o_full[o_next & 3], (o_next >> 2) & 1);
+    };
 
     for (int i = 0; i < n_tiles; ++i) {
       const int sb = i % 3, st = i & 1;  // S/P buffer, exchange-slot parity
@@ -320,17 +328,15 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       xch->m[st][half][row] = mx;
       asm volatile("bar.sync %0, 64;" ::"r"(2 + (warp & 3)) : "memory");  // the two warps that share these 32 rows
       mx = fmaxf(mx, xch->m[st][half ^ 1][row]);
-      // O is touched by these threads only when the reference point moves.  The completion of P_{i-1}.V_{i-1}
-      // (o_full: one phase per tile) is awaited up front in that case and otherwise at the end of the tile, where
-      // it costs nothing -- waiting for every phase in order is what keeps the parity tracking exact.
-      bool o_seen = i == 0;
+      // O is touched by these threads only when the reference point moves: then P_{i-1}.V_{i-1} must have completed
+      // (observe_o_upto); otherwise its completion is observed up to four tiles late (ncu, r05: waiting for it at the
+      // end of every tile was 16 % of the softmax warps' time).
       if (__any_sync(0xffffffffu, mx > m_used + 8.f)) {
         const float m_new = fmaxf(m_used, mx);
         const float alpha = ex2_approx(m_used - m_new);
         if (i > 0) {
-          mbar_wait(&bar->o_full, (i - 1) & 1);
+          observe_o_upto(i - 1);
           tc_fence_after();
-          o_seen = true;
 #pragma unroll
           for (int c = 0; c < 2; ++c) {
             uint32_t r[32];
@@ -359,7 +365,7 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
         tmem_st16(s_addr + 32 * half + 16 * c, pk);  // P (2 elements per column) over the consumed S columns
       }
       tmem_st_wait();
-      if (!o_seen) mbar_wait(&bar->o_full, (i - 1) & 1);
+      observe_o_upto(i - 4);
       tc_fence_before();
       mbar_arrive(&bar->p_full[sb]);
       l_run += (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
@@ -368,7 +374,7 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
     xch->m[n_tiles & 1][half][row] = l_run;  // the slot the last tile did not use
     asm volatile("bar.sync %0, 64;" ::"r"(2 + (warp & 3)) : "memory");
     const float inv = 1.f / (l_run + xch->m[n_tiles & 1][half ^ 1][row]);
-    mbar_wait(&bar->o_full, (n_tiles - 1) & 1);
+    observe_o_upto(n_tiles - 1);
     tc_fence_after();
     MT* orow = static_cast<MT*>(p.o) + (start + qrow) * p.o_ts + (int64_t)head * p.o_hs + 64 * half;
 #pragma unroll
@@ -409,9 +415,11 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
         tc_commit(&bar->k_empty[st]);
         tc_commit(&bar->s_full[i % 3]);
       };
-      // Q.K^T runs two tiles ahead of P.V (three S buffers): S_{j+1} is ready when the softmax warps finish tile j
+      // Q.K^T runs three tiles ahead of P.V (three S buffers; a buffer is free again, in pipe order, as soon as the
+      // P.V that reads it has been issued): S_{j+1} and S_{j+2} are ready when the softmax warps finish tile j
       issue_qk(0);
       if (n_tiles > 1) issue_qk(1);
+      if (n_tiles > 2) issue_qk(2);
       for (int j = 0; j < n_tiles; ++j) {
         {  // O += P_j.V_j (first: it is on the softmax warps' critical path)
           const int st = j % kStages, sb = j % 3;
@@ -429,9 +437,10 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
             mma_ts(tmem + 384, tmem + sb * 128 + kt * 8, b, is_ctx ? idesc_k : idesc_mn, (j | kt) > 0);
           }
           tc_commit(&bar->v_empty[st]);
-          tc_commit(&bar->o_full);
+          tc_commit(&bar->o_full[j & 3]);
         }
-        if (j + 2 < n_tiles) issue_qk(j + 2);
+        // S buffer j % 3 is free again in pipe order (P_j.V_j was just issued and tcgen05.mma's execute in order)
+        if (j + 3 < n_tiles) issue_qk(j + 3);
       }
     }
     __syncwarp();
