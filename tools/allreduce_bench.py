@@ -37,9 +37,16 @@ class ReferenceAllreduce:
         ar.register_buffer(self.ptr, self.buffer, handles, offsets)
 
     def _ipc_meta(self, t):
-        data = t.untyped_storage()._share_cuda_()
+        # (handle of the allocation's base, offset of t in it) -- cudaIpcGetMemHandle through the library's own export
+        # helper; torch's storage._share_cuda_() handle is not a bare cudaIpcMemHandle_t any more (the reference's
+        # cudaIpcOpenMemHandle rejects it with "invalid argument" on torch 2.11).
+        import ctypes
+        from vllm_splitwise_b200 import _lib
+        handle = (ctypes.c_ubyte * _lib.IPC_HANDLE_BYTES)()
+        off, size = ctypes.c_int64(), ctypes.c_int64()
+        _lib.check(_lib.load().b200_kv_ipc_export(t.data_ptr(), handle, ctypes.byref(off), ctypes.byref(size)), "ipc export")
         everyone = [None] * self.world
-        dist.all_gather_object(everyone, (data[1], data[3]), group=self.group)
+        dist.all_gather_object(everyone, (bytes(handle), off.value), group=self.group)
         return [e[0] for e in everyone], [e[1] for e in everyone]
 
     def all_reduce(self, x, out):
