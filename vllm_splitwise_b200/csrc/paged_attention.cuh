@@ -293,6 +293,13 @@ __device__ __forceinline__ void attn_quad_mode(const AttnParams& p, unsigned cha
     const long long blk_bytes = p.kv_block_stride * (long long)sizeof(CT);
     int slot0 = 0, fill0 = 0;
     long long quad = blockIdx.x;
+    const int per_part = p.num_seqs * p.tiles_per_seq;
+    // The next quad is drawn while the last two groups of the current one are being issued, and its context lengths
+    // and first block numbers are fetched behind that: the three dependent global round trips (ticket, context
+    // length, block table) would otherwise drain the ring at every quad boundary.  Drawing only ~2 ring depths early
+    // keeps the work a CTA has claimed but not started small (a whole item ahead measured slower, see the item mode).
+    int ctx_pref = -1, phys_pref = 0;
+    bool have_pref = false;
     for (int k = 0;; ++k) {
       const int qs = k % kQuadQueue;
       const bool done = quad >= total_quads;
@@ -300,7 +307,7 @@ __device__ __forceinline__ void attn_quad_mode(const AttnParams& p, unsigned cha
       const bool valid = !done && item < p.total_items;
       ItemInfo it;
       it.nblk = 0; it.ctx = -1; it.seq = 0; it.kvh = 0; it.b0 = 0; it.ng = 0; it.head0 = 0;
-      if (valid) it = decode_item<GT, BS>(p, item);
+      if (valid) it = decode_item<GT, BS>(p, item, have_pref ? ctx_pref : -1);
       const int my_n = valid ? it.nblk : 0;
       int rounds = my_n;
       rounds = max(rounds, __shfl_xor_sync(0xffffffffu, rounds, 1));
@@ -329,8 +336,36 @@ __device__ __forceinline__ void attn_quad_mode(const AttnParams& p, unsigned cha
       const unsigned char* kbase = static_cast<const unsigned char*>(p.k_cache) + (long long)it.kvh * p.kv_head_stride * (long long)sizeof(CT);
       const unsigned char* vbase = static_cast<const unsigned char*>(p.v_cache) + (long long)it.kvh * p.kv_head_stride * (long long)sizeof(CT);
       const int nvirt = 4 * rounds;
-      int phys_next = (lane < G && (lane >> 2) < my_n) ? table[lane >> 2] : 0;
+      int phys_next = have_pref ? phys_pref : ((lane < G && (lane >> 2) < my_n) ? table[lane >> 2] : 0);
+      // next quad: 0 = not drawn, 1 = ticket in flight, 2 = id known and prefetch issued
+      int stage_next = 0;
+      unsigned int raw = 0;
+      long long next_quad = 0;
+      int ctx_next = -1, phys_n = 0;
+      auto draw = [&]() {
+        if (p.sched != nullptr && lane == 0) {
+          raw = atomicAdd(p.sched, 1u);
+          if ((long long)raw == total_quads - 1) *p.sched = 0u;  // the last draw of the launch: leave the counter at zero
+        }
+        stage_next = 1;
+      };
+      auto prefetch = [&]() {
+        next_quad = p.sched == nullptr ? quad + gridDim.x : (long long)__shfl_sync(0xffffffffu, raw, 0) + gridDim.x;
+        const long long ni = 4 * next_quad + w;
+        ctx_next = -1;
+        phys_n = 0;
+        if (next_quad < total_quads && ni < p.total_items) {
+          const int part = (int)(ni / per_part);
+          const int seq = (int)(ni - (long long)part * per_part) / p.tiles_per_seq;
+          ctx_next = p.context_lens[seq];
+          const int b = part * p.partition_blocks + (lane >> 2);
+          if (lane < G && b < p.max_num_blocks_per_seq) phys_n = p.block_tables[(long long)seq * p.max_num_blocks_per_seq + b];
+        }
+        stage_next = 2;
+      };
       for (int n0 = 0; n0 < nvirt; n0 += G) {
+        if (stage_next == 1) prefetch();
+        else if (stage_next == 0 && n0 + 2 * G >= nvirt) draw();
         const int r = (n0 + lane) >> 2;
         const bool virt = lane < G && n0 + lane < nvirt;
         const bool real = virt && r < my_n;
@@ -358,17 +393,12 @@ __device__ __forceinline__ void attn_quad_mode(const AttnParams& p, unsigned cha
         slot0 += cnt;
         if (slot0 >= nst) { slot0 -= nst; ++fill0; }
       }
-      if (p.sched == nullptr) {
-        quad += gridDim.x;
-        continue;
-      }
-      unsigned int raw = 0;
-      if (lane == 0) {
-        raw = atomicAdd(p.sched, 1u);
-        if ((long long)raw == total_quads - 1) *p.sched = 0u;  // the last draw of the launch: leave the counter at zero
-      }
-      raw = __shfl_sync(0xffffffffu, raw, 0);
-      quad = (long long)raw + gridDim.x;
+      if (stage_next == 0) draw();
+      if (stage_next == 1) prefetch();
+      quad = next_quad;
+      ctx_pref = ctx_next;
+      phys_pref = phys_n;
+      have_pref = ctx_next >= 0;
     }
     return;
   }
