@@ -74,6 +74,18 @@ __device__ __forceinline__ CT cache_cvt(T v) {
   if constexpr (FP8) return to_e5m2<T>(v);
   else return v;
 }
+// N (even) source elements -> N cache elements; fp8 goes two elements per conversion instruction
+template <typename T, typename CT, bool FP8, int N>
+__device__ __forceinline__ void cache_cvt_vec(const T* src, CT* dst /* 2-byte aligned */) {
+  if constexpr (FP8) {
+    static_assert(N % 2 == 0, "pairs");
+#pragma unroll
+    for (int e = 0; e < N; e += 2) *reinterpret_cast<uint16_t*>(dst + e) = to_e5m2_x2<T>(src[e], src[e + 1]);
+  } else {
+#pragma unroll
+    for (int e = 0; e < N; ++e) dst[e] = src[e];
+  }
+}
 
 // Token-major kernel (decode-sized calls): one CTA per token.  K: every (head, d/x chunk) is x contiguous
 // source elements and x contiguous destination elements (16 bytes in the cache), so it moves as one
@@ -230,8 +242,7 @@ __global__ void __launch_bounds__(256) reshape_and_cache_tile_kernel(
     if (blk >= num_blocks) continue;
     const int off = static_cast<int>(slot - blk * block_size);
     alignas(16) CT tmp[X];
-#pragma unroll
-    for (int e = 0; e < X; ++e) tmp[e] = cache_cvt<T, CT, FP8>(src[e]);
+    cache_cvt_vec<T, CT, FP8, X>(src, tmp);
     *reinterpret_cast<uint4*>(key_cache + (blk * num_heads + h) * head_elems + ((int64_t)c * block_size + off) * X) =
         *reinterpret_cast<const uint4*>(tmp);
   }
@@ -242,20 +253,34 @@ __global__ void __launch_bounds__(256) reshape_and_cache_tile_kernel(
     const int ngroups = TOK / G;
     constexpr int WPE = 8 / (int)sizeof(CT);  // cache elements per 8-byte word
     constexpr int VPE = 16 / (int)sizeof(CT); // cache elements per 16-byte vector
-    if ((G % VPE) == 0 && (block_size % VPE) == 0) {
-      // a group's row is whole 16-byte vectors (block_size 16/32; fp32 also 8): one st.v4 per 16 bytes
-      for (int i = threadIdx.x; i < head_size * ngroups; i += blockDim.x) {
-        const int g = i / head_size, d = i - g * head_size;
+    constexpr int RD = 8 / (int)sizeof(T);    // cache rows per thread: one 8-byte shared-memory read per token
+    if ((G % VPE) == 0 && (block_size % VPE) == 0 && (head_size % RD) == 0) {
+      // A group's row is whole 16-byte vectors (block_size 16/32; fp32 also 8).  A thread takes RD adjacent rows d:
+      // per token ONE 8-byte read of the shared tile (lanes read adjacent 8-byte words: conflict-free) instead of RD
+      // element reads, fp8 conversions two elements per instruction, one st.v4 per 16 output bytes.  (ncu, r05: the
+      // fp8 variant of this kernel was issue-bound -- 70 % issue-active, 17 instructions per element.)
+      const int dgroups = head_size / RD;
+      for (int i = threadIdx.x; i < dgroups * ngroups; i += blockDim.x) {
+        const int g = i / dgroups, d0 = (i - g * dgroups) * RD;
         const int tl = g * G;
-        CT* row = value_cache + s_base[tl] + (int64_t)d * block_size + s_off[tl];
-        const T* col = vt + tl * pitch + d;
+        CT* row0 = value_cache + s_base[tl] + (int64_t)d0 * block_size + s_off[tl];
+        const T* col = vt + tl * pitch + d0;
 #pragma unroll
         for (int w = 0; w < TOK / VPE; ++w) {
           if (w * VPE < G) {
-            alignas(16) CT tmp[VPE];
+            alignas(8) T vals[VPE][RD];
 #pragma unroll
-            for (int e = 0; e < VPE; ++e) tmp[e] = cache_cvt<T, CT, FP8>(col[(w * VPE + e) * pitch]);
-            *reinterpret_cast<uint4*>(row + w * VPE) = *reinterpret_cast<const uint4*>(tmp);
+            for (int e = 0; e < VPE; ++e)
+              *reinterpret_cast<uint2*>(vals[e]) = *reinterpret_cast<const uint2*>(col + (w * VPE + e) * pitch);
+#pragma unroll
+            for (int rr = 0; rr < RD; ++rr) {
+              alignas(16) T line[VPE];
+#pragma unroll
+              for (int e = 0; e < VPE; ++e) line[e] = vals[e][rr];
+              alignas(16) CT tmp[VPE];
+              cache_cvt_vec<T, CT, FP8, VPE>(line, tmp);
+              *reinterpret_cast<uint4*>(row0 + (int64_t)rr * block_size + w * VPE) = *reinterpret_cast<const uint4*>(tmp);
+            }
           }
         }
       }
@@ -441,7 +466,7 @@ __global__ void __launch_bounds__(256) to_fp8_kernel(const T* __restrict__ src, 
         if (g0 + u * stride < groups) {
           alignas(16) uint8_t out[16];
 #pragma unroll
-          for (int e = 0; e < 16; ++e) out[e] = to_e5m2<T>(in[u][e]);
+          for (int e = 0; e < 16; e += 2) *reinterpret_cast<uint16_t*>(out + e) = to_e5m2_x2<T>(in[u][e], in[u][e + 1]);
           st_na_v4(dst + (g0 + u * stride) * 16, *reinterpret_cast<const uint4*>(out));
         }
       }

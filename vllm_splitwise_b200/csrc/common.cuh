@@ -277,6 +277,25 @@ template <> __device__ __forceinline__ uint8_t to_e5m2<__half>(__half v) {
 template <> __device__ __forceinline__ uint8_t to_e5m2<__nv_bfloat16>(__nv_bfloat16 v) {
   return (uint8_t)__nv_cvt_bfloat16raw_to_fp8(static_cast<__nv_bfloat16_raw>(v), __NV_SATFINITE, __NV_E5M2);
 }
+// Two elements per conversion instruction (cvt.rn.satfinite.e5m2x2.*): the same rounding as the single-element
+// intrinsics above (those issue the very same instruction with a zero partner), half the instructions.
+// Result: low byte = a, high byte = b.
+template <typename T> __device__ __forceinline__ uint16_t to_e5m2_x2(T a, T b);
+template <> __device__ __forceinline__ uint16_t to_e5m2_x2<float>(float a, float b) {
+  return (uint16_t)__nv_cvt_float2_to_fp8x2(make_float2(a, b), __NV_SATFINITE, __NV_E5M2);
+}
+template <> __device__ __forceinline__ uint16_t to_e5m2_x2<__half>(__half a, __half b) {
+  __half2_raw r;
+  r.x = static_cast<__half_raw>(a).x;
+  r.y = static_cast<__half_raw>(b).x;
+  return (uint16_t)__nv_cvt_halfraw2_to_fp8x2(r, __NV_SATFINITE, __NV_E5M2);
+}
+template <> __device__ __forceinline__ uint16_t to_e5m2_x2<__nv_bfloat16>(__nv_bfloat16 a, __nv_bfloat16 b) {
+  __nv_bfloat162_raw r;
+  r.x = static_cast<__nv_bfloat16_raw>(a).x;
+  r.y = static_cast<__nv_bfloat16_raw>(b).x;
+  return (uint16_t)__nv_cvt_bfloat16raw2_to_fp8x2(r, __NV_SATFINITE, __NV_E5M2);
+}
 // e5m2 -> T following the reference's widening chain (quant_utils.cuh:23-81):
 // fp8 -> half (intrinsic); bf16 goes half -> float -> bf16; float goes half -> float.
 template <typename T> __device__ __forceinline__ T from_e5m2(uint8_t v);

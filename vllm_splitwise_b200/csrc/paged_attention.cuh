@@ -86,7 +86,9 @@ template <int GT, int BS>
 __device__ __forceinline__ ItemInfo decode_item(const AttnParams& p, long long item, int ctx_known = -1) {
   ItemInfo it;
   const int per_part = p.num_seqs * p.tiles_per_seq;
-  it.part = (int)(item / per_part);
+  // 64-bit division is ~100 instructions; item ids fit 32 bits for every realistic launch (uniform branch)
+  if (p.total_items <= 0x7fffffffLL) it.part = (int)((unsigned)item / (unsigned)per_part);
+  else it.part = (int)(item / per_part);
   const int rem = (int)(item - (long long)it.part * per_part);
   it.seq = rem / p.tiles_per_seq;
   it.tile = rem - it.seq * p.tiles_per_seq;
@@ -262,15 +264,6 @@ __device__ __forceinline__ void attn_reduce_in_kernel(const AttnParams& p, const
 // ring as empty slots.  Query rows are staged in the (otherwise unused) merge buffer, two quads deep.
 constexpr int kQuadQueue = 2;
 
-template <int BS>
-__device__ __forceinline__ int quad_item_blocks(const AttnParams& p, long long item, int ctx) {
-  if (ctx < 0) return 0;
-  const int part = (int)(item / ((long long)p.num_seqs * p.tiles_per_seq));
-  const int nblk_ctx = (ctx + BS - 1) / BS;
-  const int b0 = part * p.partition_blocks;
-  return max(0, min(nblk_ctx, b0 + p.partition_blocks) - b0);
-}
-
 template <class Impl>
 __device__ __forceinline__ void attn_quad_mode(const AttnParams& p, unsigned char* stages, unsigned char* q_stage,
                                                long long* quad_q, int* ctx8, uint64_t* full_bar, uint64_t* empty_bar,
@@ -316,7 +309,7 @@ __device__ __forceinline__ void attn_quad_mode(const AttnParams& p, unsigned cha
       if (lane == 0 && k >= kQuadQueue) mbar_wait(&iq_empty[qs], ((k / kQuadQueue) - 1) & 1);
       __syncwarp();
       if (lane < 4) ctx8[qs * 4 + lane] = valid ? it.ctx : -1;
-      if (lane == 0) quad_q[qs] = done ? -1 : quad;
+      if (lane == 0) quad_q[qs] = done ? -1 : (quad | ((long long)rounds << 40));  // quad ids stay below 2^40
       uint32_t qbytes = (lane < 4 && my_n > 0 && p.q_bulk) ? (uint32_t)(it.ng * D * (int)sizeof(T)) : 0u;
       uint32_t qtot = qbytes + __shfl_xor_sync(0xffffffffu, qbytes, 1);
       qtot += __shfl_xor_sync(0xffffffffu, qtot, 2);
@@ -410,11 +403,10 @@ __device__ __forceinline__ void attn_quad_mode(const AttnParams& p, unsigned cha
   for (int k = 0;; ++k) {
     const int qs = k % kQuadQueue;
     mbar_wait(&iq_full[qs], (k / kQuadQueue) & 1);
-    const long long quad = quad_q[qs];
-    if (quad < 0) break;
-    int rounds = 0;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) rounds = max(rounds, quad_item_blocks<BS>(p, 4 * quad + j, ctx8[qs * 4 + j]));
+    const long long entry = quad_q[qs];
+    if (entry < 0) break;
+    const long long quad = entry & ((1LL << 40) - 1);
+    const int rounds = (int)(entry >> 40);  // the longest of the four items, from the producer
     const long long item = 4 * quad + warp;
     const int ctx = ctx8[qs * 4 + warp];
     ItemInfo it;

@@ -161,19 +161,46 @@ struct MmaImpl {
       qmul[r] = 1.f;
       st.scale2[r] = p.scale * kLog2e;
     }
+    // The four query elements a thread needs per k-step: d_lo, d_lo+1 (a0/a1) and d_hi, d_hi+1 (a2/a3).  fp8 caches:
+    // d_lo = 16kk + 4t, d_hi = d_lo + 2 -- one contiguous 8-byte word; 2-byte caches: d_lo = 16kk + 2t, d_hi = d_lo + 8
+    // -- two 4-byte words.  Rows staged in shared memory (q_bulk) are 16-byte aligned, so the words are loaded as such;
+    // rows read straight from global memory may not be, and go element by element.
+    float qv[R][KS][4];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int h = g + 8 * r;
+      const T* qh = qrow + h * D;
+#pragma unroll
+      for (int kk = 0; kk < KS; ++kk) {
+        const int d_lo = FP8 ? 16 * kk + 4 * t : 16 * kk + 2 * t;
+        const int d_hi = FP8 ? d_lo + 2 : d_lo + 8;
+        if (h >= it.ng) {
+          qv[r][kk][0] = qv[r][kk][1] = qv[r][kk][2] = qv[r][kk][3] = 0.f;
+        } else if (p.q_bulk) {
+          alignas(8) T w[4];
+          if constexpr (FP8) {
+            *reinterpret_cast<uint2*>(w) = *reinterpret_cast<const uint2*>(qh + d_lo);
+          } else {
+            *reinterpret_cast<uint32_t*>(w) = *reinterpret_cast<const uint32_t*>(qh + d_lo);
+            *reinterpret_cast<uint32_t*>(w + 2) = *reinterpret_cast<const uint32_t*>(qh + d_hi);
+          }
+#pragma unroll
+          for (int e = 0; e < 4; ++e) qv[r][kk][e] = to_f32<T>(w[e]);
+        } else {
+          qv[r][kk][0] = to_f32<T>(qh[d_lo]); qv[r][kk][1] = to_f32<T>(qh[d_lo + 1]);
+          qv[r][kk][2] = to_f32<T>(qh[d_hi]); qv[r][kk][3] = to_f32<T>(qh[d_hi + 1]);
+        }
+      }
+    }
     if constexpr (NORM) {
       // the quad (t = 0..3) of a row holds all D elements of head g (+8) between them
 #pragma unroll
       for (int r = 0; r < R; ++r) {
-        const int h = g + 8 * r;
         float mx = 0.f;
-        if (h < it.ng) {
-          const T* qh = qrow + h * D;
 #pragma unroll
-          for (int kk = 0; kk < KS; ++kk)
+        for (int kk = 0; kk < KS; ++kk)
 #pragma unroll
-            for (int e = 0; e < 4; ++e) mx = fmaxf(mx, fabsf(to_f32<T>(qh[16 * kk + 4 * t + e])));
-        }
+          for (int e = 0; e < 4; ++e) mx = fmaxf(mx, fabsf(qv[r][kk][e]));
         mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
         mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
         int ex = (int)((__float_as_uint(mx) >> 23) & 0xffu) - 127;  // floor(log2(mx)) for normal mx
@@ -185,19 +212,10 @@ struct MmaImpl {
     }
 #pragma unroll
     for (int kk = 0; kk < KS; ++kk) {
-      const int d_lo = FP8 ? 16 * kk + 4 * t : 16 * kk + 2 * t;
-      const int d_hi = FP8 ? d_lo + 2 : d_lo + 8;
 #pragma unroll
       for (int r = 0; r < R; ++r) {
-        const int h = g + 8 * r;
-        float x0 = 0.f, x1 = 0.f, y0 = 0.f, y1 = 0.f;
-        if (h < it.ng) {
-          const T* qh = qrow + h * D;
-          x0 = to_f32<T>(qh[d_lo]) * qmul[r]; x1 = to_f32<T>(qh[d_lo + 1]) * qmul[r];
-          y0 = to_f32<T>(qh[d_hi]) * qmul[r]; y1 = to_f32<T>(qh[d_hi + 1]) * qmul[r];
-        }
-        st.qa[kk][r] = pack2<MT>(x0, x1);       // a0 (r=0) / a1 (r=1)
-        st.qa[kk][R + r] = pack2<MT>(y0, y1);   // a2 / a3
+        st.qa[kk][r] = pack2<MT>(qv[r][kk][0] * qmul[r], qv[r][kk][1] * qmul[r]);       // a0 (r=0) / a1 (r=1)
+        st.qa[kk][R + r] = pack2<MT>(qv[r][kk][2] * qmul[r], qv[r][kk][3] * qmul[r]);   // a2 / a3
       }
     }
 #pragma unroll
