@@ -253,34 +253,25 @@ __global__ void __launch_bounds__(256) reshape_and_cache_tile_kernel(
     const int ngroups = TOK / G;
     constexpr int WPE = 8 / (int)sizeof(CT);  // cache elements per 8-byte word
     constexpr int VPE = 16 / (int)sizeof(CT); // cache elements per 16-byte vector
-    constexpr int RD = 8 / (int)sizeof(T);    // cache rows per thread: one 8-byte shared-memory read per token
-    if ((G % VPE) == 0 && (block_size % VPE) == 0 && (head_size % RD) == 0) {
-      // A group's row is whole 16-byte vectors (block_size 16/32; fp32 also 8).  A thread takes RD adjacent rows d:
-      // per token ONE 8-byte read of the shared tile (lanes read adjacent 8-byte words: conflict-free) instead of RD
-      // element reads, fp8 conversions two elements per instruction, one st.v4 per 16 output bytes.  (ncu, r05: the
-      // fp8 variant of this kernel was issue-bound -- 70 % issue-active, 17 instructions per element.)
-      const int dgroups = head_size / RD;
-      for (int i = threadIdx.x; i < dgroups * ngroups; i += blockDim.x) {
-        const int g = i / dgroups, d0 = (i - g * dgroups) * RD;
+    if ((G % VPE) == 0 && (block_size % VPE) == 0) {
+      // a group's row is whole 16-byte vectors (block_size 16/32; fp32 also 8): one st.v4 per 16 bytes, consecutive
+      // lanes write consecutive rows (one contiguous span per warp); fp8 conversions go two elements per instruction.
+      // (Tried, r05: RD = 4 adjacent rows per thread from one 8-byte shared-memory read per token -- fewer
+      // instructions, but the lanes' stores end up 64 bytes apart and the kernel lost 8-20 %.)
+      for (int i = threadIdx.x; i < head_size * ngroups; i += blockDim.x) {
+        const int g = i / head_size, d = i - g * head_size;
         const int tl = g * G;
-        CT* row0 = value_cache + s_base[tl] + (int64_t)d0 * block_size + s_off[tl];
-        const T* col = vt + tl * pitch + d0;
+        CT* row = value_cache + s_base[tl] + (int64_t)d * block_size + s_off[tl];
+        const T* col = vt + tl * pitch + d;
 #pragma unroll
         for (int w = 0; w < TOK / VPE; ++w) {
           if (w * VPE < G) {
-            alignas(8) T vals[VPE][RD];
+            alignas(16) T line[VPE];
 #pragma unroll
-            for (int e = 0; e < VPE; ++e)
-              *reinterpret_cast<uint2*>(vals[e]) = *reinterpret_cast<const uint2*>(col + (w * VPE + e) * pitch);
-#pragma unroll
-            for (int rr = 0; rr < RD; ++rr) {
-              alignas(16) T line[VPE];
-#pragma unroll
-              for (int e = 0; e < VPE; ++e) line[e] = vals[e][rr];
-              alignas(16) CT tmp[VPE];
-              cache_cvt_vec<T, CT, FP8, VPE>(line, tmp);
-              *reinterpret_cast<uint4*>(row0 + (int64_t)rr * block_size + w * VPE) = *reinterpret_cast<const uint4*>(tmp);
-            }
+            for (int e = 0; e < VPE; ++e) line[e] = col[(w * VPE + e) * pitch];
+            alignas(16) CT tmp[VPE];
+            cache_cvt_vec<T, CT, FP8, VPE>(line, tmp);
+            *reinterpret_cast<uint4*>(row + w * VPE) = *reinterpret_cast<const uint4*>(tmp);
           }
         }
       }
