@@ -1,0 +1,363 @@
+// Prefix prefill on tcgen05/TMEM, 256 query rows per CTA (two 128-row blocks A and B), head size 128.
+//
+// context_attn_tc_kernel (context_attention_tc.cuh) does 128 flop per byte it pulls out of L2 -- every 128-row CTA
+// reads all of its K/V -- and ncu (profiles/r05_ctx_tc_stalls_after.txt) shows where that ends: the MMA thread waits
+// for V tiles 28 % of its time, the softmax warps for S 35 % of theirs, L2 throughput at 48 %.  Here one CTA owns 256
+// consecutive query rows of a (sequence, head): every K/V tile is loaded ONCE and used by both row blocks (half the
+// L2 requests and loader work per flop, i.e. two ring stages hide as much latency as four did), and the blocks
+// ping-pong on the tensor pipe: while the softmax warps of A work on S_A(i+1), the pipe runs P_B(i).V and Q_B.K(i+1)^T.
+//
+// TMEM (512 columns): S_A | S_B | O_A | O_B, 128 fp32 columns each; P overwrites the S columns it came from.
+// Warps (16): 0-3 softmax of block A, 4-7 of block B -- ONE thread per query row holding the row's 128 scores in
+// registers (no cross-thread exchange; setmaxnreg gives these warps 192 registers), 8 = TMEM allocator + the
+// MMA-issuing thread, 9-10 = K (+Q) loaders, 11 idle, 12-15 = V loaders.
+// Shared memory: Q_A, Q_B, 2 K stages, 2 V stages (32 KiB each) = 192 KiB.
+// Layouts, descriptors, loaders and the lazy rescale are those of context_attention_tc.cuh.
+#pragma once
+
+#include "context_attention_tc.cuh"
+
+namespace b200 {
+namespace tc256 {
+
+using namespace tc;
+
+constexpr int kRows = 2 * kBM;   // query rows per CTA
+constexpr int kStg = 2;          // K/V ring depth
+constexpr int kThreads256 = 512;
+constexpr int kKLoad = 64, kVLoad = 128;
+constexpr int kRegsSm = 192, kRegsRest = 64;  // (8 x 192 + 8 x 64) x 32 = 64 Ki registers
+constexpr int kSmem256 = (2 + 2 * kStg) * kTileBytes + 256;
+
+struct Barriers256 {
+  uint64_t q_full;
+  uint64_t k_full[kStg], k_empty[kStg], v_full[kStg], v_empty[kStg];
+  uint64_t s_full[2], p_full[2];  // per row block
+  uint64_t o_full[2][4];          // per row block, tile t on [t % 4] (observed lazily, see context_attention_tc.cuh)
+  uint32_t tmem_base;
+};
+static_assert(sizeof(Barriers256) <= 256, "barrier block");
+
+// One softmax thread = one query row of block X: all 128 columns of every tile.
+template <typename MT>
+__device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256* bar, uint32_t tmem, int X, int warp, int tid,
+                                             int head, int m0, int q_len, int ctx_len, int n_ctx_tiles, int n_x, int64_t start) {
+  const int row = tid & 127;
+  const uint32_t lane_off = (uint32_t)(32 * (warp & 3)) << 16;
+  const int qrow = m0 + kBM * X + row;
+  const bool has_alibi = p.alibi_slopes != nullptr;
+  const float slope2 = has_alibi ? p.alibi_slopes[head] * 1.4426950408889634f : 0.f;
+  const uint32_t s_addr = tmem + lane_off + X * 128;
+  const uint32_t o_addr = tmem + lane_off + 256 + X * 128;
+  float m_used = -INFINITY, l_run = 0.f;  // lazily updated reference point (see context_attention_tc.cuh)
+  int o_next = 0;                         // first tile whose P.V completion this thread has not observed yet
+  auto observe_o_upto = [&](int last) {
+    for (; o_next <= last; ++o_next) mbar_wait(&bar->o_full[X][o_next & 3], (o_next >> 2) & 1);
+  };
+
+  for (int i = 0; i < n_x; ++i) {
+    const bool is_ctx = i < n_ctx_tiles;
+    const int n0 = (is_ctx ? i : i - n_ctx_tiles) * kBN;
+    const int limit = is_ctx ? ctx_len - n0 : qrow - n0 + 1;  // columns [0, limit) are visible to this row
+    const float bias0 = slope2 * (float)(is_ctx ? n0 - ctx_len - qrow : n0 - qrow);
+    mbar_wait(&bar->s_full[X], i & 1);
+    tc_fence_after();
+    float s[128];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) tmem_ld32(s_addr + 32 * c, reinterpret_cast<uint32_t*>(&s[32 * c]));
+    tmem_ld_wait();
+    // warp-uniform fast path: nothing masked, no bias -> raw maximum, scale folded into the exponent's FMA
+    const bool plain = !has_alibi && __all_sync(0xffffffffu, limit >= kBN);
+    float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+    float mx, mul;
+    if (plain) {
+#pragma unroll
+      for (int k = 0; k < 128; ++k) mx4[k & 3] = fmaxf(mx4[k & 3], s[k]);
+      mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;  // scale > 0
+      mul = p.scale_log2;
+    } else {
+#pragma unroll
+      for (int k = 0; k < 128; ++k) {
+        float v = fmaf(s[k], p.scale_log2, has_alibi ? fmaf(slope2, (float)k, bias0) : 0.f);
+        v = k < limit ? v : -INFINITY;
+        s[k] = v;
+        mx4[k & 3] = fmaxf(mx4[k & 3], v);
+      }
+      mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+      mul = 1.f;
+    }
+    if (__any_sync(0xffffffffu, mx > m_used + 8.f)) {
+      const float m_new = fmaxf(m_used, mx);
+      const float alpha = ex2_approx(m_used - m_new);
+      if (i > 0) {
+        observe_o_upto(i - 1);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          uint32_t r[32];
+          tmem_ld32(o_addr + 32 * c, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int k = 0; k < 32; ++k) r[k] = __float_as_uint(__uint_as_float(r[k]) * alpha);
+          tmem_st16(o_addr + 32 * c, r);
+          tmem_st16(o_addr + 32 * c + 16, r + 16);
+        }
+      }
+      l_run *= alpha;
+      m_used = m_new;
+    }
+    // P = 2^(score - reference) over the S columns already consumed (two elements per 32-bit column)
+    float sum4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      uint32_t pk[16];
+#pragma unroll
+      for (int k = 0; k < 32; k += 2) {
+        const float e0 = ex2_approx(fmaf(s[32 * c + k], mul, -m_used));  // masked columns are -inf -> 0
+        const float e1 = ex2_approx(fmaf(s[32 * c + k + 1], mul, -m_used));
+        sum4[(k >> 1) & 3] += e0 + e1;
+        pk[k >> 1] = pack2<MT>(e0, e1);
+      }
+      tmem_st16(s_addr + 16 * c, pk);
+    }
+    tmem_st_wait();
+    observe_o_upto(i - 4);
+    tc_fence_before();
+    mbar_arrive(&bar->p_full[X]);
+    l_run += (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
+  }
+
+  if (n_x > 0) {
+    observe_o_upto(n_x - 1);
+    tc_fence_after();
+    const float inv = 1.f / l_run;
+    MT* orow = static_cast<MT*>(p.o) + (start + qrow) * p.o_ts + (int64_t)head * p.o_hs;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t r[32];
+      tmem_ld32(o_addr + 32 * c, r);
+      tmem_ld_wait();
+      if (qrow < min(q_len, p.row_limit)) {
+#pragma unroll
+        for (int k = 0; k < 32; k += 8) {
+          uint4 w;
+          w.x = pack2<MT>(__uint_as_float(r[k]) * inv, __uint_as_float(r[k + 1]) * inv);
+          w.y = pack2<MT>(__uint_as_float(r[k + 2]) * inv, __uint_as_float(r[k + 3]) * inv);
+          w.z = pack2<MT>(__uint_as_float(r[k + 4]) * inv, __uint_as_float(r[k + 5]) * inv);
+          w.w = pack2<MT>(__uint_as_float(r[k + 6]) * inv, __uint_as_float(r[k + 7]) * inv);
+          *reinterpret_cast<uint4*>(orow + 32 * c + k) = w;
+        }
+      }
+    }
+  }
+}
+
+template <typename MT, int BS>
+__global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(const CtxAttnParams p) {
+  constexpr int TILE_UNITS = kBN * (kD / 8);
+  extern __shared__ __align__(1024) uint8_t tc256_smem[];
+  uint4* q_s = reinterpret_cast<uint4*>(tc256_smem);  // Q_A, Q_B
+  uint4* k_s = q_s + 2 * TILE_UNITS;
+  uint4* v_s = k_s + kStg * TILE_UNITS;
+  Barriers256* bar = reinterpret_cast<Barriers256*>(v_s + kStg * TILE_UNITS);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int mblk = gridDim.x - 1 - blockIdx.x;
+  const int head = blockIdx.y, seq = blockIdx.z;
+  const int ctx_len = p.b_ctx_len[seq];
+  const int q_len = p.b_seq_len[seq] - ctx_len;
+  const int m0 = mblk * kRows;
+  if (m0 >= q_len) return;
+  const int64_t start = p.b_start_loc[seq];
+  const int kvh = head / (p.num_heads / p.num_kv_heads);
+  const int n_ctx_tiles = (ctx_len + kBN - 1) / kBN;
+  // tiles each row block attends: the cached prefix, then the new tokens up to its own last row
+  const int n_a = n_ctx_tiles + (min(q_len, m0 + kBM) + kBN - 1) / kBN;
+  const int n_b = m0 + kBM < min(q_len, p.row_limit) ? n_ctx_tiles + (min(q_len, m0 + kRows) + kBN - 1) / kBN : 0;
+  const int n_load = max(n_a, n_b);
+
+  if (tid == 0) {
+    mbar_init(&bar->q_full, kKLoad);
+    for (int s = 0; s < kStg; ++s) {
+      mbar_init(&bar->k_full[s], kKLoad);
+      mbar_init(&bar->v_full[s], kVLoad);
+      mbar_init(&bar->k_empty[s], 1);
+      mbar_init(&bar->v_empty[s], 1);
+    }
+    for (int x = 0; x < 2; ++x) {
+      mbar_init(&bar->s_full[x], 1);
+      mbar_init(&bar->p_full[x], 128);
+      for (int s = 0; s < 4; ++s) mbar_init(&bar->o_full[x][s], 1);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 8) tmem_alloc_512(&bar->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bar->tmem_base;
+
+  if (warp < 8) {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsSm));
+    const int X = warp >> 2;
+    softmax_rows<MT>(p, bar, tmem, X, warp, tid, head, m0, q_len, ctx_len, n_ctx_tiles, X ? n_b : n_a, start);
+  } else {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsRest));
+    if (warp == 8) {
+      // ================= the MMA-issuing thread =================
+      if (lane == 0) {
+        const uint32_t idesc_k = instr_desc<MT>(kBN, false);
+        const uint32_t idesc_mn = instr_desc<MT>(kD, true);
+        const uint32_t q_addr = smem_u32(q_s);
+        mbar_wait(&bar->q_full, 0);
+        auto issue_qk = [&](int X, int i) {  // S_X = Q_X.K_i^T
+          const int st = i % kStg;
+          mbar_wait(&bar->k_full[st], (i / kStg) & 1);
+          tc_fence_after();
+          const uint32_t k_addr = smem_u32(k_s + st * TILE_UNITS);
+          const uint32_t qx = q_addr + X * kTileBytes;
+#pragma unroll
+          for (int ks = 0; ks < kD / 16; ++ks)
+            mma_ss(tmem + X * 128, smem_desc(qx + ks * 2 * kBM * 16, kBM * 16, 128),
+                   smem_desc(k_addr + ks * 2 * kBN * 16, kBN * 16, 128), idesc_k, ks > 0);
+          if (X == 1 || i >= n_b) tc_commit(&bar->k_empty[st]);  // last reader of K tile i
+          tc_commit(&bar->s_full[X]);
+        };
+        auto issue_pv = [&](int X, int i) {  // O_X += P_X.V_i
+          const int st = i % kStg;
+          mbar_wait(&bar->v_full[st], (i / kStg) & 1);
+          mbar_wait(&bar->p_full[X], i & 1);
+          tc_fence_after();
+          const uint32_t v_addr = smem_u32(v_s + st * TILE_UNITS);
+          const bool is_ctx = i < n_ctx_tiles;
+#pragma unroll
+          for (int kt = 0; kt < kBN / 16; ++kt) {
+            const uint64_t b = is_ctx ? smem_desc(v_addr + kt * 2 * kD * 16, kD * 16, 128)
+                                      : smem_desc(v_addr + kt * 16 * 16, 128, kBN * 16);
+            mma_ts(tmem + 256 + X * 128, tmem + X * 128 + kt * 8, b, is_ctx ? idesc_k : idesc_mn, (i | kt) > 0);
+          }
+          if (X == 1 || i >= n_b) tc_commit(&bar->v_empty[st]);  // last reader of V tile i
+          tc_commit(&bar->o_full[X][i & 3]);
+        };
+        // ping-pong: while block A's softmax works on S_A(i+1), the pipe runs block B's P.V(i) and Q.K(i+1), and back
+        issue_qk(0, 0);
+        if (n_b > 0) issue_qk(1, 0);
+        for (int i = 0; i < n_load; ++i) {
+          if (i < n_a) {
+            issue_pv(0, i);
+            if (i + 1 < n_a) issue_qk(0, i + 1);
+          }
+          if (i < n_b) {
+            issue_pv(1, i);
+            if (i + 1 < n_b) issue_qk(1, i + 1);
+          }
+        }
+      }
+      __syncwarp();
+    } else if (warp < 11) {
+      // ================= K (and Q) loaders =================
+      const int lt = tid - 9 * 32;
+      const MT* kc = static_cast<const MT*>(p.k_cache) + (int64_t)kvh * p.kc_hs;
+      const MT* kn = static_cast<const MT*>(p.k) + start * p.k_ts + (int64_t)kvh * p.k_hs;
+      const int32_t* bt = p.b_loc + (int64_t)seq * p.b_loc_stride;
+      auto issue_k = [&](int ti, int st) {
+        uint4* Ks = k_s + st * TILE_UNITS;
+        if (ti < n_ctx_tiles) {
+          const int n0 = ti * kBN;
+          load_k_ctx<MT, BS, kKLoad>(Ks, kc, p.kc_bs, bt + n0 / BS, ctx_len - n0, lt, lane);
+        } else {
+          const int n0 = (ti - n_ctx_tiles) * kBN;
+          load_rows<MT, kKLoad, false>(Ks, kn + (int64_t)n0 * p.k_ts, p.k_ts, q_len - n0, lt);
+        }
+      };
+      const MT* qb = static_cast<const MT*>(p.q) + (start + m0) * p.q_ts + (int64_t)head * p.q_hs;
+      load_rows<MT, kKLoad, true>(q_s, qb, p.q_ts, q_len - m0, lt);
+      load_rows<MT, kKLoad, true>(q_s + TILE_UNITS, qb + (int64_t)kBM * p.q_ts, p.q_ts, q_len - m0 - kBM, lt);
+      cp_async_commit();
+      issue_k(0, 0);
+      cp_async_commit();
+      cp_async_wait<1>();
+      fence_proxy_async_smem();
+      mbar_arrive(&bar->q_full);
+      if (n_load > 1) {
+        issue_k(1, 1);
+        cp_async_commit();
+      }
+      for (int i = 0; i < n_load; ++i) {
+        if (i + 1 < n_load) cp_async_wait<1>(); else cp_async_wait<0>();
+        fence_proxy_async_smem();
+        mbar_arrive(&bar->k_full[i % kStg]);
+        if (i + kStg < n_load) {
+          mbar_wait(&bar->k_empty[i % kStg], (i / kStg) & 1);
+          issue_k(i + kStg, i % kStg);
+          cp_async_commit();
+        }
+      }
+    } else if (warp >= 12) {
+      // ================= V loaders =================
+      const int lt = tid - 12 * 32;
+      const MT* vc = static_cast<const MT*>(p.v_cache) + (int64_t)kvh * p.vc_hs;
+      const MT* vn = static_cast<const MT*>(p.v) + start * p.v_ts + (int64_t)kvh * p.v_hs;
+      const int32_t* bt = p.b_loc + (int64_t)seq * p.b_loc_stride;
+      auto issue_v = [&](int ti, int st) {
+        uint4* Vs = v_s + st * TILE_UNITS;
+        if (ti < n_ctx_tiles) {
+          const int n0 = ti * kBN;
+          load_v_ctx<MT, BS, kVLoad>(Vs, vc, p.vc_bs, bt + n0 / BS, ctx_len - n0, lt, lane);
+        } else {
+          const int n0 = (ti - n_ctx_tiles) * kBN;
+          load_rows<MT, kVLoad, true>(Vs, vn + (int64_t)n0 * p.v_ts, p.v_ts, q_len - n0, lt);
+        }
+      };
+      issue_v(0, 0);
+      cp_async_commit();
+      if (n_load > 1) {
+        issue_v(1, 1);
+        cp_async_commit();
+      }
+      for (int i = 0; i < n_load; ++i) {
+        if (i + 1 < n_load) cp_async_wait<1>(); else cp_async_wait<0>();
+        if (i < n_ctx_tiles && i * kBN + kBN > ctx_len && ((ctx_len - i * kBN) & 7)) {
+          // the token octet that straddles ctx_len: slots past the end are stale cache memory (may be NaN / Inf)
+          asm volatile("bar.sync 1, %0;" ::"n"(kVLoad) : "memory");
+          const int tgb = (ctx_len - i * kBN) >> 3, rem = (ctx_len - i * kBN) & 7;
+          for (int d = lt; d < kD; d += kVLoad) {
+            MT* gp = reinterpret_cast<MT*>(&v_s[(i % kStg) * TILE_UNITS + tgb * kD + d]);
+            for (int x = rem; x < 8; ++x) gp[x] = MT(0.f);
+          }
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(&bar->v_full[i % kStg]);
+        if (i + kStg < n_load) {
+          mbar_wait(&bar->v_empty[i % kStg], (i / kStg) & 1);
+          issue_v(i + kStg, i % kStg);
+          cp_async_commit();
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  if (warp == 8) tmem_dealloc_512(tmem);
+}
+
+template <typename MT, int BS>
+int launch_ctx_attn_tc256(const CtxAttnParams& p, int batch, int max_input_len, cudaStream_t stream) {
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  B200_CUDA_TRY(cudaGetDevice(&dev));
+  dev &= 63;
+  if (!attr_set[dev]) {
+    B200_CUDA_TRY(cudaFuncSetAttribute(context_attn_tc256_kernel<MT, BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem256));
+    attr_set[dev] = true;
+  }
+  dim3 grid((max_input_len + kRows - 1) / kRows, p.num_heads, batch);
+  context_attn_tc256_kernel<MT, BS><<<grid, kThreads256, kSmem256, stream>>>(p);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+}  // namespace tc256
+}  // namespace b200
