@@ -11,7 +11,7 @@
 // Warps (16): 0-3 softmax of block A, 4-7 of block B -- ONE thread per query row holding the row's 128 scores in
 // registers (no cross-thread exchange; setmaxnreg gives these warps 192 registers), 8 = TMEM allocator + the
 // MMA-issuing thread, 9-10 = K (+Q) loaders, 11 idle, 12-15 = V loaders.
-// Shared memory: Q_A, Q_B, 2 K stages, 2 V stages (32 KiB each) = 192 KiB.
+// Shared memory: Q_A, Q_B, 2 K stages, 3 V stages (32 KiB each) = 224 KiB.
 // Layouts, descriptors, loaders and the lazy rescale are those of context_attention_tc.cuh.
 #pragma once
 
@@ -23,15 +23,17 @@ namespace tc256 {
 using namespace tc;
 
 constexpr int kRows = 2 * kBM;   // query rows per CTA
-constexpr int kStg = 2;          // K/V ring depth
+constexpr int kStg = 2;          // K ring depth
+constexpr int kStgV = 3;         // V ring depth: Q_A, Q_B, 2 K and 3 V tiles are what 227 KiB holds (ncu: the MMA thread
+                                 // waited for V tiles, not K tiles)
 constexpr int kThreads256 = 512;
 constexpr int kKLoad = 64, kVLoad = 128;
 constexpr int kRegsSm = 192, kRegsRest = 64;  // (8 x 192 + 8 x 64) x 32 = 64 Ki registers
-constexpr int kSmem256 = (2 + 2 * kStg) * kTileBytes + 256;
+constexpr int kSmem256 = (2 + kStg + kStgV) * kTileBytes + 256;
 
 struct Barriers256 {
   uint64_t q_full;
-  uint64_t k_full[kStg], k_empty[kStg], v_full[kStg], v_empty[kStg];
+  uint64_t k_full[kStg], k_empty[kStg], v_full[kStgV], v_empty[kStgV];
   uint64_t s_full[2], p_full[2];  // per row block
   uint64_t o_full[2][4];          // per row block, tile t on [t % 4] (observed lazily, see context_attention_tc.cuh)
   uint32_t tmem_base;
@@ -159,7 +161,7 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
   uint4* q_s = reinterpret_cast<uint4*>(tc256_smem);  // Q_A, Q_B
   uint4* k_s = q_s + 2 * TILE_UNITS;
   uint4* v_s = k_s + kStg * TILE_UNITS;
-  Barriers256* bar = reinterpret_cast<Barriers256*>(v_s + kStg * TILE_UNITS);
+  Barriers256* bar = reinterpret_cast<Barriers256*>(v_s + kStgV * TILE_UNITS);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int mblk = gridDim.x - 1 - blockIdx.x;
@@ -180,8 +182,10 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
     mbar_init(&bar->q_full, kKLoad);
     for (int s = 0; s < kStg; ++s) {
       mbar_init(&bar->k_full[s], kKLoad);
-      mbar_init(&bar->v_full[s], kVLoad);
       mbar_init(&bar->k_empty[s], 1);
+    }
+    for (int s = 0; s < kStgV; ++s) {
+      mbar_init(&bar->v_full[s], kVLoad);
       mbar_init(&bar->v_empty[s], 1);
     }
     for (int x = 0; x < 2; ++x) {
@@ -224,8 +228,8 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
           tc_commit(&bar->s_full[X]);
         };
         auto issue_pv = [&](int X, int i) {  // O_X += P_X.V_i
-          const int st = i % kStg;
-          mbar_wait(&bar->v_full[st], (i / kStg) & 1);
+          const int st = i % kStgV;
+          mbar_wait(&bar->v_full[st], (i / kStgV) & 1);
           mbar_wait(&bar->p_full[X], i & 1);
           tc_fence_after();
           const uint32_t v_addr = smem_u32(v_s + st * TILE_UNITS);
@@ -309,28 +313,26 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
           load_rows<MT, kVLoad, true>(Vs, vn + (int64_t)n0 * p.v_ts, p.v_ts, q_len - n0, lt);
         }
       };
-      issue_v(0, 0);
-      cp_async_commit();
-      if (n_load > 1) {
-        issue_v(1, 1);
+      for (int t = 0; t < kStgV && t < n_load; ++t) {
+        issue_v(t, t);
         cp_async_commit();
       }
       for (int i = 0; i < n_load; ++i) {
-        if (i + 1 < n_load) cp_async_wait<1>(); else cp_async_wait<0>();
+        cp_async_wait_upto(min(kStgV - 1, n_load - 1 - i));
         if (i < n_ctx_tiles && i * kBN + kBN > ctx_len && ((ctx_len - i * kBN) & 7)) {
           // the token octet that straddles ctx_len: slots past the end are stale cache memory (may be NaN / Inf)
           asm volatile("bar.sync 1, %0;" ::"n"(kVLoad) : "memory");
           const int tgb = (ctx_len - i * kBN) >> 3, rem = (ctx_len - i * kBN) & 7;
           for (int d = lt; d < kD; d += kVLoad) {
-            MT* gp = reinterpret_cast<MT*>(&v_s[(i % kStg) * TILE_UNITS + tgb * kD + d]);
+            MT* gp = reinterpret_cast<MT*>(&v_s[(i % kStgV) * TILE_UNITS + tgb * kD + d]);
             for (int x = rem; x < 8; ++x) gp[x] = MT(0.f);
           }
         }
         fence_proxy_async_smem();
-        mbar_arrive(&bar->v_full[i % kStg]);
-        if (i + kStg < n_load) {
-          mbar_wait(&bar->v_empty[i % kStg], (i / kStg) & 1);
-          issue_v(i + kStg, i % kStg);
+        mbar_arrive(&bar->v_full[i % kStgV]);
+        if (i + kStgV < n_load) {
+          mbar_wait(&bar->v_empty[i % kStgV], (i / kStgV) & 1);
+          issue_v(i + kStgV, i % kStgV);
           cp_async_commit();
         }
       }
