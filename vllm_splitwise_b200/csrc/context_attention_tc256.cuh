@@ -11,7 +11,7 @@
 // Warps (16): 0-3 softmax of block A, 4-7 of block B -- ONE thread per query row holding the row's 128 scores in
 // registers (no cross-thread exchange; setmaxnreg gives these warps 192 registers), 8 = TMEM allocator + the
 // MMA-issuing thread, 9-10 = K (+Q) loaders, 11 idle, 12-15 = V loaders.
-// Shared memory: Q_A, Q_B, 2 K stages, 3 V stages (32 KiB each) = 224 KiB.
+// Shared memory: Q_A, Q_B, 2 K stages, 2 V stages (32 KiB each) = 192 KiB.
 // Layouts, descriptors, loaders and the lazy rescale are those of context_attention_tc.cuh.
 #pragma once
 
@@ -24,8 +24,7 @@ using namespace tc;
 
 constexpr int kRows = 2 * kBM;   // query rows per CTA
 constexpr int kStg = 2;          // K ring depth
-constexpr int kStgV = 3;         // V ring depth: Q_A, Q_B, 2 K and 3 V tiles are what 227 KiB holds (ncu: the MMA thread
-                                 // waited for V tiles, not K tiles)
+constexpr int kStgV = 2;         // V ring depth (a third V stage fits in 227 KiB but measured 3-6 % slower, r05)
 constexpr int kThreads256 = 512;
 constexpr int kKLoad = 64, kVLoad = 128;
 constexpr int kRegsSm = 192, kRegsRest = 64;  // (8 x 192 + 8 x 64) x 32 = 64 Ki registers
@@ -213,6 +212,7 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
         const uint32_t idesc_k = instr_desc<MT>(kBN, false);
         const uint32_t idesc_mn = instr_desc<MT>(kD, true);
         const uint32_t q_addr = smem_u32(q_s);
+        const bool stagger = p.tc256_stagger != 0 && n_b > 0;
         mbar_wait(&bar->q_full, 0);
         auto issue_qk = [&](int X, int i) {  // S_X = Q_X.K_i^T
           const int st = i % kStg;
@@ -243,11 +243,18 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
           if (X == 1 || i >= n_b) tc_commit(&bar->v_empty[st]);  // last reader of V tile i
           tc_commit(&bar->o_full[X][i & 3]);
         };
-        // ping-pong: while block A's softmax works on S_A(i+1), the pipe runs block B's P.V(i) and Q.K(i+1), and back
+        // Ping-pong: while block A's softmax works on S_A(i+1), the pipe runs block B's P.V(i) and Q.K(i+1), and back.
+        // Block B is started one softmax pass behind A (its first Q.K^T is issued only after A's first P has arrived):
+        // started together, the two blocks stay in phase -- both in their exponential phase at once on a shared MUFU
+        // pipe, then both waiting for the tensor pipe (ncu: 49 % of the softmax warps' time waiting for S).
         issue_qk(0, 0);
+        if (stagger) {
+          issue_pv(0, 0);
+          if (1 < n_a) issue_qk(0, 1);
+        }
         if (n_b > 0) issue_qk(1, 0);
         for (int i = 0; i < n_load; ++i) {
-          if (i < n_a) {
+          if (i < n_a && !(stagger && i == 0)) {
             issue_pv(0, i);
             if (i + 1 < n_a) issue_qk(0, i + 1);
           }
