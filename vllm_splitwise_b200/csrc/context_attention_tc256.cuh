@@ -247,12 +247,12 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
         // Block B is started one softmax pass behind A (its first Q.K^T is issued only after A's first P has arrived):
         // started together, the two blocks stay in phase -- both in their exponential phase at once on a shared MUFU
         // pipe, then both waiting for the tensor pipe (ncu: 49 % of the softmax warps' time waiting for S).
+        // (Q_B.K_0^T goes before Q_A.K_1^T: the K loader announces tile 1 only after tile 0's stage has been released,
+        // and that takes block B's Q.K_0^T -- the other order deadlocks.)
         issue_qk(0, 0);
-        if (stagger) {
-          issue_pv(0, 0);
-          if (1 < n_a) issue_qk(0, 1);
-        }
+        if (stagger) issue_pv(0, 0);
         if (n_b > 0) issue_qk(1, 0);
+        if (stagger && 1 < n_a) issue_qk(0, 1);
         for (int i = 0; i < n_load; ++i) {
           if (i < n_a && !(stagger && i == 0)) {
             issue_pv(0, i);
