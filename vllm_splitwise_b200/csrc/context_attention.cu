@@ -39,8 +39,6 @@ extern "C" int b200_context_attention_fwd(const b200_context_attn_args_t* a, b20
   p.num_heads = a->num_heads;
   p.num_kv_heads = a->num_kv_heads;
   p.row_limit = (a->max_input_len + 127) / 128 * 128;
-  static const int stagger = getenv("B200_CTX_STAGGER") ? atoi(getenv("B200_CTX_STAGGER")) : 1;  // A/B knob
-  p.tc256_stagger = stagger;
 
   DeviceGuard guard;
   B200_CUDA_TRY(guard.set(a->device));

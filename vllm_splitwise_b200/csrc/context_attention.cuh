@@ -47,7 +47,6 @@ struct CtxAttnParams {
   int32_t b_loc_stride;
   int32_t num_heads;
   int32_t num_kv_heads;
-  int32_t tc256_stagger;  // 256-row kernel: start row block B one softmax pass behind A (B200_CTX_STAGGER=0 turns it off)
   int32_t row_limit;  // new-token rows >= row_limit are not computed: ceil(max_input_len / 128) * 128 (the reference's grid)
 };
 

@@ -117,9 +117,10 @@ __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.
 __device__ __forceinline__ void cp_async_wait_upto(int n) {
   if (n <= 0) cp_async_wait<0>();
   else if (n == 1) cp_async_wait<1>();
-  else cp_async_wait<2>();
+  else if (n == 2) cp_async_wait<2>();
+  else cp_async_wait<3>();
 }
-static_assert(kStages <= 3, "cp_async_wait_upto covers up to two groups in flight");
+static_assert(kStages <= 4, "cp_async_wait_upto covers up to three groups in flight");
 
 struct Barriers {
   uint64_t q_full;
@@ -143,35 +144,35 @@ __device__ __forceinline__ void row_major_granule(int e, int& row, int& j) {
 
 // [row][D] source (new K, new V, Q) -> [d-octet][row] granules.  A warp instruction covers 8 rows x 4 octets:
 // 64-byte global segments and four conflict-free 128-byte shared-memory lines.
-template <typename MT, int NT, bool ZERO_FILL>
+template <typename MT, int NT, bool ZERO_FILL, int ROWS = kBN>  // ROWS = rows of the tile
 __device__ __forceinline__ void load_rows(uint4* tile, const MT* src, int64_t row_stride, int rows_valid, int lt) {
   constexpr int JW = NT / 8;  // d-octets covered per pass
   const int row_lo = lt & 7, j_lo = lt >> 3;
   const MT* s0 = src + (int64_t)row_lo * row_stride + j_lo * 8;
-  uint4* d0 = tile + j_lo * kBN + row_lo;
+  uint4* d0 = tile + j_lo * ROWS + row_lo;
   const int64_t step = 8 * row_stride;
-  if (rows_valid >= kBN) {
+  if (rows_valid >= ROWS) {
 #pragma unroll
     for (int jh = 0; jh < 16 / JW; ++jh) {
       const MT* sp = s0 + jh * JW * 8;
 #pragma unroll
-      for (int rh = 0; rh < 16; ++rh, sp += step) cp_async16(d0 + jh * JW * kBN + rh * 8, sp);
+      for (int rh = 0; rh < ROWS / 8; ++rh, sp += step) cp_async16(d0 + jh * JW * ROWS + rh * 8, sp);
     }
   } else {
 #pragma unroll
     for (int jh = 0; jh < 16 / JW; ++jh) {
       const MT* sp = s0 + jh * JW * 8;
 #pragma unroll 4
-      for (int rh = 0; rh < 16; ++rh, sp += step) {
-        if (rh * 8 + row_lo < rows_valid) cp_async16(d0 + jh * JW * kBN + rh * 8, sp);
-        else if (ZERO_FILL) d0[jh * JW * kBN + rh * 8] = make_uint4(0u, 0u, 0u, 0u);
+      for (int rh = 0; rh < ROWS / 8; ++rh, sp += step) {
+        if (rh * 8 + row_lo < rows_valid) cp_async16(d0 + jh * JW * ROWS + rh * 8, sp);
+        else if (ZERO_FILL) d0[jh * JW * ROWS + rh * 8] = make_uint4(0u, 0u, 0u, 0u);
       }
     }
   }
 }
 
 // cached K: chunks [D/8][BS][8] of the blocks bt[0..] -> [d-octet][token] granules
-template <typename MT, int BS, int NT>
+template <typename MT, int BS, int NT, int TN = kBN>  // TN = tokens of the tile
 __device__ __forceinline__ void load_k_ctx(uint4* tile, const MT* kc, int64_t block_stride, const int32_t* bt,
                                            int toks_valid, int lt, int lane) {
   constexpr int JW = NT / BS;  // d-octets covered per pass
@@ -179,30 +180,30 @@ __device__ __forceinline__ void load_k_ctx(uint4* tile, const MT* kc, int64_t bl
   // lane c holds the physical number of the tile's c-th block; the loop gets it by shuffle, so no load sits in
   // front of a cp.async
   int my_bn = 0;
-  if (lane < kBN / BS && lane * BS < toks_valid) my_bn = bt[lane];
+  if (lane < TN / BS && lane * BS < toks_valid) my_bn = bt[lane];
 #pragma unroll
-  for (int c = 0; c < kBN / BS; ++c) {
+  for (int c = 0; c < TN / BS; ++c) {
     const int64_t bn = __shfl_sync(0xffffffffu, my_bn, c);
     if (c * BS + tt < toks_valid) {
       const MT* sp = kc + bn * block_stride + (jl * BS + tt) * 8;
-      uint4* dp = tile + jl * kBN + c * BS + tt;
+      uint4* dp = tile + jl * TN + c * BS + tt;
 #pragma unroll
-      for (int q = 0; q < 16 / JW; ++q) cp_async16(dp + q * JW * kBN, sp + q * JW * BS * 8);
+      for (int q = 0; q < 16 / JW; ++q) cp_async16(dp + q * JW * TN, sp + q * JW * BS * 8);
     }
   }
 }
 
 // cached V: chunks [D][BS] -> [token-octet][d] granules; octets past the context end are zero-filled
-template <typename MT, int BS, int NT>
+template <typename MT, int BS, int NT, int TN = kBN>
 __device__ __forceinline__ void load_v_ctx(uint4* tile, const MT* vc, int64_t block_stride, const int32_t* bt,
                                            int toks_valid, int lt, int lane) {
   constexpr int HG = BS / 8;   // token octets per block
   constexpr int DW = NT / HG;  // d rows covered per pass
   const int hh = lt % HG, dl = lt / HG;
   int my_bn = 0;
-  if (lane < kBN / BS && lane * BS < toks_valid) my_bn = bt[lane];
+  if (lane < TN / BS && lane * BS < toks_valid) my_bn = bt[lane];
 #pragma unroll
-  for (int c = 0; c < kBN / BS; ++c) {
+  for (int c = 0; c < TN / BS; ++c) {
     const int64_t bn = __shfl_sync(0xffffffffu, my_bn, c);
     const int tg = c * HG + hh;
     uint4* dp = tile + tg * kD + dl;

@@ -1,17 +1,21 @@
-// Prefix prefill on tcgen05/TMEM, 256 query rows per CTA (two 128-row blocks A and B), head size 128.
+// Prefix prefill on tcgen05/TMEM, 256 query rows per CTA (two 128-row blocks A and B), head size 128, 64-token KV tiles.
 //
 // context_attn_tc_kernel (context_attention_tc.cuh) does 128 flop per byte it pulls out of L2 -- every 128-row CTA
 // reads all of its K/V -- and ncu (profiles/r05_ctx_tc_stalls_after.txt) shows where that ends: the MMA thread waits
 // for V tiles 28 % of its time, the softmax warps for S 35 % of theirs, L2 throughput at 48 %.  Here one CTA owns 256
 // consecutive query rows of a (sequence, head): every K/V tile is loaded ONCE and used by both row blocks (half the
-// L2 requests and loader work per flop, i.e. two ring stages hide as much latency as four did), and the blocks
-// ping-pong on the tensor pipe: while the softmax warps of A work on S_A(i+1), the pipe runs P_B(i).V and Q_B.K(i+1)^T.
+// L2 requests and loader work per flop).
 //
-// TMEM (512 columns): S_A | S_B | O_A | O_B, 128 fp32 columns each; P overwrites the S columns it came from.
-// Warps (16): 0-3 softmax of block A, 4-7 of block B -- ONE thread per query row holding the row's 128 scores in
-// registers (no cross-thread exchange; setmaxnreg gives these warps 192 registers), 8 = TMEM allocator + the
-// MMA-issuing thread, 9-10 = K (+Q) loaders, 11 idle, 12-15 = V loaders.
-// Shared memory: Q_A, Q_B, 2 K stages, 2 V stages (32 KiB each) = 192 KiB.
+// A first version with 128-token tiles (S_A | S_B | O_A | O_B fill the 512 TMEM columns, so a block's next Q.K^T can
+// only be issued after its P.V) reached 647 TFLOP/s with the softmax warps waiting for S half of the time
+// (profiles/r05_ctx_tc256_stalls.txt): softmax -> P.V -> Q.K^T -> softmax is a serial chain per block and the two
+// blocks run it in phase.  With 64-token tiles an S buffer is 64 columns, every block has TWO of them
+// (S_A0 S_A1 | S_B0 S_B1 | O_A | O_B), and Q.K^T runs a tile ahead of the softmax: the chain per block is the softmax
+// alone.
+//
+// Warps (16): 0-3 softmax of block A, 4-7 of block B -- ONE thread per query row holding the row's 64 scores in
+// registers (no cross-thread exchange), 8 = TMEM allocator + the MMA-issuing thread, 9-10 = K (+Q) loaders, 11 idle,
+// 12-15 = V loaders.  Shared memory: Q_A, Q_B (32 KiB each), kStg K and kStgV V stages of 16 KiB.
 // Layouts, descriptors, loaders and the lazy rescale are those of context_attention_tc.cuh.
 #pragma once
 
@@ -23,23 +27,26 @@ namespace tc256 {
 using namespace tc;
 
 constexpr int kRows = 2 * kBM;   // query rows per CTA
-constexpr int kStg = 2;          // K ring depth
-constexpr int kStgV = 2;         // V ring depth (a third V stage fits in 227 KiB but measured 3-6 % slower, r05)
+constexpr int kTN = 64;          // KV tokens per tile
+constexpr int kStg = 4;          // K ring depth
+constexpr int kStgV = 4;         // V ring depth
+constexpr int kKVTileBytes = kTN * kD * 2;  // 16 KiB
 constexpr int kThreads256 = 512;
 constexpr int kKLoad = 64, kVLoad = 128;
-constexpr int kRegsSm = 192, kRegsRest = 64;  // (8 x 192 + 8 x 64) x 32 = 64 Ki registers
-constexpr int kSmem256 = (2 + kStg + kStgV) * kTileBytes + 256;
+constexpr int kRegsSm = 160, kRegsRest = 96;  // (8 x 160 + 8 x 96) x 32 = 64 Ki registers
+constexpr int kSmem256 = 2 * kTileBytes + (kStg + kStgV) * kKVTileBytes + 256;
 
 struct Barriers256 {
   uint64_t q_full;
   uint64_t k_full[kStg], k_empty[kStg], v_full[kStgV], v_empty[kStgV];
-  uint64_t s_full[2], p_full[2];  // per row block
-  uint64_t o_full[2][4];          // per row block, tile t on [t % 4] (observed lazily, see context_attention_tc.cuh)
+  uint64_t s_full[2][2];  // [row block][S buffer]
+  uint64_t p_full[2];     // per row block
+  uint64_t o_full[2][4];  // per row block, tile t on [t % 4] (observed lazily, see context_attention_tc.cuh)
   uint32_t tmem_base;
 };
 static_assert(sizeof(Barriers256) <= 256, "barrier block");
 
-// One softmax thread = one query row of block X: all 128 columns of every tile.
+// One softmax thread = one query row of block X: all 64 columns of every tile.
 template <typename MT>
 __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256* bar, uint32_t tmem, int X, int warp, int tid,
                                              int head, int m0, int q_len, int ctx_len, int n_ctx_tiles, int n_x, int64_t start) {
@@ -48,7 +55,6 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
   const int qrow = m0 + kBM * X + row;
   const bool has_alibi = p.alibi_slopes != nullptr;
   const float slope2 = has_alibi ? p.alibi_slopes[head] * 1.4426950408889634f : 0.f;
-  const uint32_t s_addr = tmem + lane_off + X * 128;
   const uint32_t o_addr = tmem + lane_off + 256 + X * 128;
   float m_used = -INFINITY, l_run = 0.f;  // lazily updated reference point (see context_attention_tc.cuh)
   int o_next = 0;                         // first tile whose P.V completion this thread has not observed yet
@@ -58,27 +64,28 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
 
   for (int i = 0; i < n_x; ++i) {
     const bool is_ctx = i < n_ctx_tiles;
-    const int n0 = (is_ctx ? i : i - n_ctx_tiles) * kBN;
+    const int n0 = (is_ctx ? i : i - n_ctx_tiles) * kTN;
     const int limit = is_ctx ? ctx_len - n0 : qrow - n0 + 1;  // columns [0, limit) are visible to this row
     const float bias0 = slope2 * (float)(is_ctx ? n0 - ctx_len - qrow : n0 - qrow);
-    mbar_wait(&bar->s_full[X], i & 1);
+    const uint32_t s_addr = tmem + lane_off + X * 128 + (i & 1) * kTN;
+    mbar_wait(&bar->s_full[X][i & 1], (i >> 1) & 1);
     tc_fence_after();
-    float s[128];
-#pragma unroll
-    for (int c = 0; c < 4; ++c) tmem_ld32(s_addr + 32 * c, reinterpret_cast<uint32_t*>(&s[32 * c]));
+    float s[kTN];
+    tmem_ld32(s_addr, reinterpret_cast<uint32_t*>(&s[0]));
+    tmem_ld32(s_addr + 32, reinterpret_cast<uint32_t*>(&s[32]));
     tmem_ld_wait();
     // warp-uniform fast path: nothing masked, no bias -> raw maximum, scale folded into the exponent's FMA
-    const bool plain = !has_alibi && __all_sync(0xffffffffu, limit >= kBN);
+    const bool plain = !has_alibi && __all_sync(0xffffffffu, limit >= kTN);
     float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
     float mx, mul;
     if (plain) {
 #pragma unroll
-      for (int k = 0; k < 128; ++k) mx4[k & 3] = fmaxf(mx4[k & 3], s[k]);
+      for (int k = 0; k < kTN; ++k) mx4[k & 3] = fmaxf(mx4[k & 3], s[k]);
       mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;  // scale > 0
       mul = p.scale_log2;
     } else {
 #pragma unroll
-      for (int k = 0; k < 128; ++k) {
+      for (int k = 0; k < kTN; ++k) {
         float v = fmaf(s[k], p.scale_log2, has_alibi ? fmaf(slope2, (float)k, bias0) : 0.f);
         v = k < limit ? v : -INFINITY;
         s[k] = v;
@@ -110,7 +117,7 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
     // P = 2^(score - reference) over the S columns already consumed (two elements per 32-bit column)
     float sum4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
+    for (int c = 0; c < kTN / 32; ++c) {
       uint32_t pk[16];
 #pragma unroll
       for (int k = 0; k < 32; k += 2) {
@@ -155,12 +162,13 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
 
 template <typename MT, int BS>
 __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(const CtxAttnParams p) {
-  constexpr int TILE_UNITS = kBN * (kD / 8);
+  constexpr int Q_UNITS = kBM * (kD / 8);    // 16-byte granules of a Q tile
+  constexpr int KV_UNITS = kTN * (kD / 8);   // ... of a K or V tile
   extern __shared__ __align__(1024) uint8_t tc256_smem[];
   uint4* q_s = reinterpret_cast<uint4*>(tc256_smem);  // Q_A, Q_B
-  uint4* k_s = q_s + 2 * TILE_UNITS;
-  uint4* v_s = k_s + kStg * TILE_UNITS;
-  Barriers256* bar = reinterpret_cast<Barriers256*>(v_s + kStgV * TILE_UNITS);
+  uint4* k_s = q_s + 2 * Q_UNITS;
+  uint4* v_s = k_s + kStg * KV_UNITS;
+  Barriers256* bar = reinterpret_cast<Barriers256*>(v_s + kStgV * KV_UNITS);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int mblk = gridDim.x - 1 - blockIdx.x;
@@ -171,10 +179,10 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
   if (m0 >= q_len) return;
   const int64_t start = p.b_start_loc[seq];
   const int kvh = head / (p.num_heads / p.num_kv_heads);
-  const int n_ctx_tiles = (ctx_len + kBN - 1) / kBN;
+  const int n_ctx_tiles = (ctx_len + kTN - 1) / kTN;
   // tiles each row block attends: the cached prefix, then the new tokens up to its own last row
-  const int n_a = n_ctx_tiles + (min(q_len, m0 + kBM) + kBN - 1) / kBN;
-  const int n_b = m0 + kBM < min(q_len, p.row_limit) ? n_ctx_tiles + (min(q_len, m0 + kRows) + kBN - 1) / kBN : 0;
+  const int n_a = n_ctx_tiles + (min(q_len, m0 + kBM) + kTN - 1) / kTN;
+  const int n_b = m0 + kBM < min(q_len, p.row_limit) ? n_ctx_tiles + (min(q_len, m0 + kRows) + kTN - 1) / kTN : 0;
   const int n_load = max(n_a, n_b);
 
   if (tid == 0) {
@@ -188,7 +196,8 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
       mbar_init(&bar->v_empty[s], 1);
     }
     for (int x = 0; x < 2; ++x) {
-      mbar_init(&bar->s_full[x], 1);
+      mbar_init(&bar->s_full[x][0], 1);
+      mbar_init(&bar->s_full[x][1], 1);
       mbar_init(&bar->p_full[x], 128);
       for (int s = 0; s < 4; ++s) mbar_init(&bar->o_full[x][s], 1);
     }
@@ -209,58 +218,58 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
     if (warp == 8) {
       // ================= the MMA-issuing thread =================
       if (lane == 0) {
-        const uint32_t idesc_k = instr_desc<MT>(kBN, false);
-        const uint32_t idesc_mn = instr_desc<MT>(kD, true);
+        const uint32_t idesc_qk = instr_desc<MT>(kTN, false);  // S = Q.K^T: N = 64 tokens, K-major B
+        const uint32_t idesc_pv = instr_desc<MT>(kD, false);   // O += P.V over cached V: N = 128, K-major B
+        const uint32_t idesc_mn = instr_desc<MT>(kD, true);    // ... over new V: MN-major B
         const uint32_t q_addr = smem_u32(q_s);
-        const bool stagger = p.tc256_stagger != 0 && n_b > 0;
         mbar_wait(&bar->q_full, 0);
-        auto issue_qk = [&](int X, int i) {  // S_X = Q_X.K_i^T
+        auto issue_qk = [&](int X, int i) {  // S_X[i & 1] = Q_X.K_i^T
           const int st = i % kStg;
           mbar_wait(&bar->k_full[st], (i / kStg) & 1);
           tc_fence_after();
-          const uint32_t k_addr = smem_u32(k_s + st * TILE_UNITS);
+          const uint32_t k_addr = smem_u32(k_s + st * KV_UNITS);
           const uint32_t qx = q_addr + X * kTileBytes;
 #pragma unroll
           for (int ks = 0; ks < kD / 16; ++ks)
-            mma_ss(tmem + X * 128, smem_desc(qx + ks * 2 * kBM * 16, kBM * 16, 128),
-                   smem_desc(k_addr + ks * 2 * kBN * 16, kBN * 16, 128), idesc_k, ks > 0);
+            mma_ss(tmem + X * 128 + (i & 1) * kTN, smem_desc(qx + ks * 2 * kBM * 16, kBM * 16, 128),
+                   smem_desc(k_addr + ks * 2 * kTN * 16, kTN * 16, 128), idesc_qk, ks > 0);
           if (X == 1 || i >= n_b) tc_commit(&bar->k_empty[st]);  // last reader of K tile i
-          tc_commit(&bar->s_full[X]);
+          tc_commit(&bar->s_full[X][i & 1]);
         };
         auto issue_pv = [&](int X, int i) {  // O_X += P_X.V_i
           const int st = i % kStgV;
           mbar_wait(&bar->v_full[st], (i / kStgV) & 1);
           mbar_wait(&bar->p_full[X], i & 1);
           tc_fence_after();
-          const uint32_t v_addr = smem_u32(v_s + st * TILE_UNITS);
+          const uint32_t v_addr = smem_u32(v_s + st * KV_UNITS);
           const bool is_ctx = i < n_ctx_tiles;
 #pragma unroll
-          for (int kt = 0; kt < kBN / 16; ++kt) {
+          for (int kt = 0; kt < kTN / 16; ++kt) {
+            // cached V: [token-octet][d] granules (K-major, LBO = next token octet, SBO = next 8 d rows);
+            // new V:    [d-octet][token] granules (MN-major, LBO = next 8 tokens, SBO = next d octet)
             const uint64_t b = is_ctx ? smem_desc(v_addr + kt * 2 * kD * 16, kD * 16, 128)
-                                      : smem_desc(v_addr + kt * 16 * 16, 128, kBN * 16);
-            mma_ts(tmem + 256 + X * 128, tmem + X * 128 + kt * 8, b, is_ctx ? idesc_k : idesc_mn, (i | kt) > 0);
+                                      : smem_desc(v_addr + kt * 16 * 16, 128, kTN * 16);
+            mma_ts(tmem + 256 + X * 128, tmem + X * 128 + (i & 1) * kTN + kt * 8, b, is_ctx ? idesc_pv : idesc_mn,
+                   (i | kt) > 0);
           }
           if (X == 1 || i >= n_b) tc_commit(&bar->v_empty[st]);  // last reader of V tile i
           tc_commit(&bar->o_full[X][i & 3]);
         };
-        // Ping-pong: while block A's softmax works on S_A(i+1), the pipe runs block B's P.V(i) and Q.K(i+1), and back.
-        // Block B is started one softmax pass behind A (its first Q.K^T is issued only after A's first P has arrived):
-        // started together, the two blocks stay in phase -- both in their exponential phase at once on a shared MUFU
-        // pipe, then both waiting for the tensor pipe (ncu: 49 % of the softmax warps' time waiting for S).
-        // (Q_B.K_0^T goes before Q_A.K_1^T: the K loader announces tile 1 only after tile 0's stage has been released,
-        // and that takes block B's Q.K_0^T -- the other order deadlocks.)
+        // Q.K^T runs one tile ahead of the softmax in each block: S_X[(i+2) & 1] is free again, in pipe order, as soon
+        // as P_X(i).V has been issued.  (Block B's Q.K_t^T is always issued before block A's Q.K_{t+1}^T: the K loader
+        // announces tile t+1 only after it has seen tile t's stage released.)
         issue_qk(0, 0);
-        if (stagger) issue_pv(0, 0);
         if (n_b > 0) issue_qk(1, 0);
-        if (stagger && 1 < n_a) issue_qk(0, 1);
+        if (1 < n_a) issue_qk(0, 1);
+        if (1 < n_b) issue_qk(1, 1);
         for (int i = 0; i < n_load; ++i) {
-          if (i < n_a && !(stagger && i == 0)) {
+          if (i < n_a) {
             issue_pv(0, i);
-            if (i + 1 < n_a) issue_qk(0, i + 1);
+            if (i + 2 < n_a) issue_qk(0, i + 2);
           }
           if (i < n_b) {
             issue_pv(1, i);
-            if (i + 1 < n_b) issue_qk(1, i + 1);
+            if (i + 2 < n_b) issue_qk(1, i + 2);
           }
         }
       }
@@ -271,36 +280,36 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
       const MT* kc = static_cast<const MT*>(p.k_cache) + (int64_t)kvh * p.kc_hs;
       const MT* kn = static_cast<const MT*>(p.k) + start * p.k_ts + (int64_t)kvh * p.k_hs;
       const int32_t* bt = p.b_loc + (int64_t)seq * p.b_loc_stride;
-      auto issue_k = [&](int ti, int st) {
-        uint4* Ks = k_s + st * TILE_UNITS;
+      auto issue_k = [&](int ti) {
+        uint4* Ks = k_s + (ti % kStg) * KV_UNITS;
         if (ti < n_ctx_tiles) {
-          const int n0 = ti * kBN;
-          load_k_ctx<MT, BS, kKLoad>(Ks, kc, p.kc_bs, bt + n0 / BS, ctx_len - n0, lt, lane);
+          const int n0 = ti * kTN;
+          load_k_ctx<MT, BS, kKLoad, kTN>(Ks, kc, p.kc_bs, bt + n0 / BS, ctx_len - n0, lt, lane);
         } else {
-          const int n0 = (ti - n_ctx_tiles) * kBN;
-          load_rows<MT, kKLoad, false>(Ks, kn + (int64_t)n0 * p.k_ts, p.k_ts, q_len - n0, lt);
+          const int n0 = (ti - n_ctx_tiles) * kTN;
+          load_rows<MT, kKLoad, false, kTN>(Ks, kn + (int64_t)n0 * p.k_ts, p.k_ts, q_len - n0, lt);
         }
       };
       const MT* qb = static_cast<const MT*>(p.q) + (start + m0) * p.q_ts + (int64_t)head * p.q_hs;
-      load_rows<MT, kKLoad, true>(q_s, qb, p.q_ts, q_len - m0, lt);
-      load_rows<MT, kKLoad, true>(q_s + TILE_UNITS, qb + (int64_t)kBM * p.q_ts, p.q_ts, q_len - m0 - kBM, lt);
+      load_rows<MT, kKLoad, true, kBM>(q_s, qb, p.q_ts, q_len - m0, lt);
+      load_rows<MT, kKLoad, true, kBM>(q_s + Q_UNITS, qb + (int64_t)kBM * p.q_ts, p.q_ts, q_len - m0 - kBM, lt);
       cp_async_commit();
-      issue_k(0, 0);
-      cp_async_commit();
-      cp_async_wait<1>();
-      fence_proxy_async_smem();
-      mbar_arrive(&bar->q_full);
-      if (n_load > 1) {
-        issue_k(1, 1);
+      const int pro = min(kStg, n_load);
+      for (int t = 0; t < pro; ++t) {
+        issue_k(t);
         cp_async_commit();
       }
+      cp_async_wait_upto(pro);  // Q (the oldest group) has landed
+      fence_proxy_async_smem();
+      mbar_arrive(&bar->q_full);
       for (int i = 0; i < n_load; ++i) {
-        if (i + 1 < n_load) cp_async_wait<1>(); else cp_async_wait<0>();
+        // groups younger than tile i: tiles i+1 .. min(i + kStg - 1, n_load - 1)
+        cp_async_wait_upto(min(kStg - 1, n_load - 1 - i));
         fence_proxy_async_smem();
         mbar_arrive(&bar->k_full[i % kStg]);
         if (i + kStg < n_load) {
           mbar_wait(&bar->k_empty[i % kStg], (i / kStg) & 1);
-          issue_k(i + kStg, i % kStg);
+          issue_k(i + kStg);
           cp_async_commit();
         }
       }
@@ -310,28 +319,28 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
       const MT* vc = static_cast<const MT*>(p.v_cache) + (int64_t)kvh * p.vc_hs;
       const MT* vn = static_cast<const MT*>(p.v) + start * p.v_ts + (int64_t)kvh * p.v_hs;
       const int32_t* bt = p.b_loc + (int64_t)seq * p.b_loc_stride;
-      auto issue_v = [&](int ti, int st) {
-        uint4* Vs = v_s + st * TILE_UNITS;
+      auto issue_v = [&](int ti) {
+        uint4* Vs = v_s + (ti % kStgV) * KV_UNITS;
         if (ti < n_ctx_tiles) {
-          const int n0 = ti * kBN;
-          load_v_ctx<MT, BS, kVLoad>(Vs, vc, p.vc_bs, bt + n0 / BS, ctx_len - n0, lt, lane);
+          const int n0 = ti * kTN;
+          load_v_ctx<MT, BS, kVLoad, kTN>(Vs, vc, p.vc_bs, bt + n0 / BS, ctx_len - n0, lt, lane);
         } else {
-          const int n0 = (ti - n_ctx_tiles) * kBN;
-          load_rows<MT, kVLoad, true>(Vs, vn + (int64_t)n0 * p.v_ts, p.v_ts, q_len - n0, lt);
+          const int n0 = (ti - n_ctx_tiles) * kTN;
+          load_rows<MT, kVLoad, true, kTN>(Vs, vn + (int64_t)n0 * p.v_ts, p.v_ts, q_len - n0, lt);
         }
       };
       for (int t = 0; t < kStgV && t < n_load; ++t) {
-        issue_v(t, t);
+        issue_v(t);
         cp_async_commit();
       }
       for (int i = 0; i < n_load; ++i) {
         cp_async_wait_upto(min(kStgV - 1, n_load - 1 - i));
-        if (i < n_ctx_tiles && i * kBN + kBN > ctx_len && ((ctx_len - i * kBN) & 7)) {
+        if (i < n_ctx_tiles && i * kTN + kTN > ctx_len && ((ctx_len - i * kTN) & 7)) {
           // the token octet that straddles ctx_len: slots past the end are stale cache memory (may be NaN / Inf)
-          asm volatile("bar.sync 1, %0;" ::"n"(kVLoad) : "memory");
-          const int tgb = (ctx_len - i * kBN) >> 3, rem = (ctx_len - i * kBN) & 7;
+          asm volatile("bar.sync 1, %0;" ::"n"(kVLoad) : "memory");  // every V loader's copies of tile i landed
+          const int tgb = (ctx_len - i * kTN) >> 3, rem = (ctx_len - i * kTN) & 7;
           for (int d = lt; d < kD; d += kVLoad) {
-            MT* gp = reinterpret_cast<MT*>(&v_s[(i % kStgV) * TILE_UNITS + tgb * kD + d]);
+            MT* gp = reinterpret_cast<MT*>(&v_s[(i % kStgV) * KV_UNITS + tgb * kD + d]);
             for (int x = rem; x < 8; ++x) gp[x] = MT(0.f);
           }
         }
@@ -339,7 +348,7 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
         mbar_arrive(&bar->v_full[i % kStgV]);
         if (i + kStgV < n_load) {
           mbar_wait(&bar->v_empty[i % kStgV], (i / kStgV) & 1);
-          issue_v(i + kStgV, i % kStgV);
+          issue_v(i + kStgV);
           cp_async_commit();
         }
       }
