@@ -34,17 +34,19 @@ constexpr int kKVTileBytes = kTN * kD * 2;  // 16 KiB
 constexpr int kThreads256 = 512;
 constexpr int kKLoad = 64, kVLoad = 128;
 constexpr int kRegsSm = 160, kRegsRest = 96;  // (8 x 160 + 8 x 96) x 32 = 64 Ki registers
-constexpr int kSmem256 = 2 * kTileBytes + (kStg + kStgV) * kKVTileBytes + 256;
+constexpr int kSmem256 = 2 * kTileBytes + (kStg + kStgV) * kKVTileBytes + 512;
 
 struct Barriers256 {
   uint64_t q_full;
   uint64_t k_full[kStg], k_empty[kStg], v_full[kStgV], v_empty[kStgV];
   uint64_t s_full[2][2];  // [row block][S buffer]
-  uint64_t p_full[2];     // per row block
+  uint64_t p_full[2][2];  // [row block][S buffer]: the softmax may finish tile i+1 before the MMA thread has looked at
+                          // tile i's P (S_{i+1} is ready early), so a single barrier per block could run two phases
+                          // ahead of its waiter -- per buffer it cannot (S_{i+2} needs P_i.V issued)
   uint64_t o_full[2][4];  // per row block, tile t on [t % 4] (observed lazily, see context_attention_tc.cuh)
   uint32_t tmem_base;
 };
-static_assert(sizeof(Barriers256) <= 256, "barrier block");
+static_assert(sizeof(Barriers256) <= 512, "barrier block");
 
 // One softmax thread = one query row of block X: all 64 columns of every tile.
 template <typename MT>
@@ -131,7 +133,7 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
     tmem_st_wait();
     observe_o_upto(i - 4);
     tc_fence_before();
-    mbar_arrive(&bar->p_full[X]);
+    mbar_arrive(&bar->p_full[X][i & 1]);
     l_run += (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
   }
 
@@ -198,7 +200,8 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
     for (int x = 0; x < 2; ++x) {
       mbar_init(&bar->s_full[x][0], 1);
       mbar_init(&bar->s_full[x][1], 1);
-      mbar_init(&bar->p_full[x], 128);
+      mbar_init(&bar->p_full[x][0], 128);
+      mbar_init(&bar->p_full[x][1], 128);
       for (int s = 0; s < 4; ++s) mbar_init(&bar->o_full[x][s], 1);
     }
     mbar_fence_init();
@@ -239,7 +242,7 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
         auto issue_pv = [&](int X, int i) {  // O_X += P_X.V_i
           const int st = i % kStgV;
           mbar_wait(&bar->v_full[st], (i / kStgV) & 1);
-          mbar_wait(&bar->p_full[X], i & 1);
+          mbar_wait(&bar->p_full[X][i & 1], (i >> 1) & 1);
           tc_fence_after();
           const uint32_t v_addr = smem_u32(v_s + st * KV_UNITS);
           const bool is_ctx = i < n_ctx_tiles;
