@@ -224,18 +224,26 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
         const uint32_t idesc_qk = instr_desc<MT>(kTN, false);  // S = Q.K^T: N = 64 tokens, K-major B
         const uint32_t idesc_pv = instr_desc<MT>(kD, false);   // O += P.V over cached V: N = 128, K-major B
         const uint32_t idesc_mn = instr_desc<MT>(kD, true);    // ... over new V: MN-major B
-        const uint32_t q_addr = smem_u32(q_s);
+        // Shared-memory descriptors are built ONCE: the start-address field is the low 14 bits (address >> 4), so the
+        // descriptor of "base + off" is the base descriptor plus off >> 4.  (ncu, r05: building two descriptors per
+        // tcgen05.mma from scratch made the issuing thread the bottleneck -- 80 % busy, tensor pipe 26 % active.)
+        const uint64_t qd[2] = {smem_desc(smem_u32(q_s), kBM * 16, 128), smem_desc(smem_u32(q_s) + kTileBytes, kBM * 16, 128)};
+        const uint64_t kd0 = smem_desc(smem_u32(k_s), kTN * 16, 128);      // K-major [d-octet][token]
+        const uint64_t vd0_ctx = smem_desc(smem_u32(v_s), kD * 16, 128);   // cached V: K-major [token-octet][d]
+        const uint64_t vd0_new = smem_desc(smem_u32(v_s), 128, kTN * 16);  // new V: MN-major [d-octet][token]
+        constexpr uint64_t kStageStep = kKVTileBytes >> 4;
         mbar_wait(&bar->q_full, 0);
         auto issue_qk = [&](int X, int i) {  // S_X[i & 1] = Q_X.K_i^T
           const int st = i % kStg;
           mbar_wait(&bar->k_full[st], (i / kStg) & 1);
           tc_fence_after();
-          const uint32_t k_addr = smem_u32(k_s + st * KV_UNITS);
-          const uint32_t qx = q_addr + X * kTileBytes;
+          const uint64_t kd = kd0 + (uint64_t)st * kStageStep;
+          const uint64_t qx = qd[X];
+          const uint32_t d_addr = tmem + X * 128 + (i & 1) * kTN;
 #pragma unroll
           for (int ks = 0; ks < kD / 16; ++ks)
-            mma_ss(tmem + X * 128 + (i & 1) * kTN, smem_desc(qx + ks * 2 * kBM * 16, kBM * 16, 128),
-                   smem_desc(k_addr + ks * 2 * kTN * 16, kTN * 16, 128), idesc_qk, ks > 0);
+            mma_ss(d_addr, qx + (uint64_t)(ks * ((2 * kBM * 16) >> 4)), kd + (uint64_t)(ks * ((2 * kTN * 16) >> 4)), idesc_qk,
+                   ks > 0);
           if (X == 1 || i >= n_b) tc_commit(&bar->k_empty[st]);  // last reader of K tile i
           tc_commit(&bar->s_full[X][i & 1]);
         };
@@ -244,17 +252,14 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
           mbar_wait(&bar->v_full[st], (i / kStgV) & 1);
           mbar_wait(&bar->p_full[X][i & 1], (i >> 1) & 1);
           tc_fence_after();
-          const uint32_t v_addr = smem_u32(v_s + st * KV_UNITS);
           const bool is_ctx = i < n_ctx_tiles;
+          // cached V: k-step = two token octets (2 * kD granules); new V: k-step = 16 tokens (16 granules)
+          const uint64_t vd = (is_ctx ? vd0_ctx : vd0_new) + (uint64_t)st * kStageStep;
+          const uint64_t step = is_ctx ? (uint64_t)((2 * kD * 16) >> 4) : (uint64_t)((16 * 16) >> 4);
+          const uint32_t idesc = is_ctx ? idesc_pv : idesc_mn;
+          const uint32_t o_addr = tmem + 256 + X * 128, p_addr = tmem + X * 128 + (i & 1) * kTN;
 #pragma unroll
-          for (int kt = 0; kt < kTN / 16; ++kt) {
-            // cached V: [token-octet][d] granules (K-major, LBO = next token octet, SBO = next 8 d rows);
-            // new V:    [d-octet][token] granules (MN-major, LBO = next 8 tokens, SBO = next d octet)
-            const uint64_t b = is_ctx ? smem_desc(v_addr + kt * 2 * kD * 16, kD * 16, 128)
-                                      : smem_desc(v_addr + kt * 16 * 16, 128, kTN * 16);
-            mma_ts(tmem + 256 + X * 128, tmem + X * 128 + (i & 1) * kTN + kt * 8, b, is_ctx ? idesc_pv : idesc_mn,
-                   (i | kt) > 0);
-          }
+          for (int kt = 0; kt < kTN / 16; ++kt) mma_ts(o_addr, p_addr + kt * 8, vd + kt * step, idesc, (i | kt) > 0);
           if (X == 1 || i >= n_b) tc_commit(&bar->v_empty[st]);  // last reader of V tile i
           tc_commit(&bar->o_full[X][i & 3]);
         };
