@@ -219,8 +219,8 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
   } else {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsRest));
     if (warp == 8) {
-      // ================= the MMA-issuing thread =================
-      if (lane == 0) {
+      // ================= the MMA warp (uniform: every lane runs the loop, elect.sync issues) =================
+      {
         const uint32_t idesc_qk = instr_desc<MT>(kTN, false);  // S = Q.K^T: N = 64 tokens, K-major B
         const uint32_t idesc_pv = instr_desc<MT>(kD, false);   // O += P.V over cached V: N = 128, K-major B
         const uint32_t idesc_mn = instr_desc<MT>(kD, true);    // ... over new V: MN-major B
@@ -242,10 +242,10 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
           const uint32_t d_addr = tmem + X * 128 + (i & 1) * kTN;
 #pragma unroll
           for (int ks = 0; ks < kD / 16; ++ks)
-            mma_ss(d_addr, qx + (uint64_t)(ks * ((2 * kBM * 16) >> 4)), kd + (uint64_t)(ks * ((2 * kTN * 16) >> 4)), idesc_qk,
+            mma_ss_u(d_addr, qx + (uint64_t)(ks * ((2 * kBM * 16) >> 4)), kd + (uint64_t)(ks * ((2 * kTN * 16) >> 4)), idesc_qk,
                    ks > 0);
-          if (X == 1 || i >= n_b) tc_commit(&bar->k_empty[st]);  // last reader of K tile i
-          tc_commit(&bar->s_full[X][i & 1]);
+          if (X == 1 || i >= n_b) tc_commit_u(&bar->k_empty[st]);  // last reader of K tile i
+          tc_commit_u(&bar->s_full[X][i & 1]);
         };
         auto issue_pv = [&](int X, int i) {  // O_X += P_X.V_i
           const int st = i % kStgV;
@@ -259,9 +259,9 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
           const uint32_t idesc = is_ctx ? idesc_pv : idesc_mn;
           const uint32_t o_addr = tmem + 256 + X * 128, p_addr = tmem + X * 128 + (i & 1) * kTN;
 #pragma unroll
-          for (int kt = 0; kt < kTN / 16; ++kt) mma_ts(o_addr, p_addr + kt * 8, vd + kt * step, idesc, (i | kt) > 0);
-          if (X == 1 || i >= n_b) tc_commit(&bar->v_empty[st]);  // last reader of V tile i
-          tc_commit(&bar->o_full[X][i & 3]);
+          for (int kt = 0; kt < kTN / 16; ++kt) mma_ts_u(o_addr, p_addr + kt * 8, vd + kt * step, idesc, (i | kt) > 0);
+          if (X == 1 || i >= n_b) tc_commit_u(&bar->v_empty[st]);  // last reader of V tile i
+          tc_commit_u(&bar->o_full[X][i & 3]);
         };
         // Q.K^T runs one tile ahead of the softmax in each block: S_X[(i+2) & 1] is free again, in pipe order, as soon
         // as P_X(i).V has been issued.  (Block B's Q.K_t^T is always issued before block A's Q.K_{t+1}^T: the K loader
