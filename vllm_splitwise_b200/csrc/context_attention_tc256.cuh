@@ -27,18 +27,25 @@ namespace tc256 {
 using namespace tc;
 
 constexpr int kRows = 2 * kBM;   // query rows per CTA
-constexpr int kTN = 64;          // KV tokens per tile
-constexpr int kStg = 4;          // K ring depth
-constexpr int kStgV = 4;         // V ring depth
-constexpr int kKVTileBytes = kTN * kD * 2;  // 16 KiB
 constexpr int kThreads256 = 512;
 constexpr int kKLoad = 64, kVLoad = 128;
-constexpr int kRegsSm = 160, kRegsRest = 96;  // (8 x 160 + 8 x 96) x 32 = 64 Ki registers
-constexpr int kSmem256 = 2 * kTileBytes + (kStg + kStgV) * kKVTileBytes + 512;
+constexpr int kMaxStg = 4;
+// TN = KV tokens per tile.  TN = 128: one S buffer per block (Q.K^T of tile i+1 follows P.V of tile i), two 32 KiB
+// stages each for K and V, 192 registers per softmax thread (128 scores).  TN = 64: two S buffers per block (Q.K^T a
+// tile ahead), four 16 KiB stages, 160 registers.  Measured (profiles/r05_prefix_prefill_tc256*.jsonl): see kDefaultTN.
+template <int TN>
+struct Cfg {
+  static constexpr int kNSB = 128 / TN;              // S buffers per row block
+  static constexpr int kStg = 256 / TN;              // K and V ring depth
+  static constexpr int kKVTileBytes = TN * kD * 2;
+  static constexpr int kSmem = 2 * kTileBytes + 2 * kStg * kKVTileBytes + 512;
+  static_assert(TN == 64 || TN == 128, "tile sizes");
+  static_assert(kStg <= kMaxStg, "ring depth");
+};
 
 struct Barriers256 {
   uint64_t q_full;
-  uint64_t k_full[kStg], k_empty[kStg], v_full[kStgV], v_empty[kStgV];
+  uint64_t k_full[kMaxStg], k_empty[kMaxStg], v_full[kMaxStg], v_empty[kMaxStg];
   uint64_t s_full[2][2];  // [row block][S buffer]
   uint64_t p_full[2][2];  // [row block][S buffer]: the softmax may finish tile i+1 before the MMA thread has looked at
                           // tile i's P (S_{i+1} is ready early), so a single barrier per block could run two phases
@@ -48,8 +55,8 @@ struct Barriers256 {
 };
 static_assert(sizeof(Barriers256) <= 512, "barrier block");
 
-// One softmax thread = one query row of block X: all 64 columns of every tile.
-template <typename MT>
+// One softmax thread = one query row of block X: all TN columns of every tile.
+template <typename MT, int TN>
 __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256* bar, uint32_t tmem, int X, int warp, int tid,
                                              int head, int m0, int q_len, int ctx_len, int n_ctx_tiles, int n_x, int64_t start) {
   const int row = tid & 127;
@@ -64,17 +71,18 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
     for (; o_next <= last; ++o_next) mbar_wait(&bar->o_full[X][o_next & 3], (o_next >> 2) & 1);
   };
 
+  constexpr int kTN = TN, NSB = Cfg<TN>::kNSB;
   for (int i = 0; i < n_x; ++i) {
     const bool is_ctx = i < n_ctx_tiles;
     const int n0 = (is_ctx ? i : i - n_ctx_tiles) * kTN;
     const int limit = is_ctx ? ctx_len - n0 : qrow - n0 + 1;  // columns [0, limit) are visible to this row
     const float bias0 = slope2 * (float)(is_ctx ? n0 - ctx_len - qrow : n0 - qrow);
-    const uint32_t s_addr = tmem + lane_off + X * 128 + (i & 1) * kTN;
-    mbar_wait(&bar->s_full[X][i & 1], (i >> 1) & 1);
+    const uint32_t s_addr = tmem + lane_off + X * 128 + (i % NSB) * kTN;
+    mbar_wait(&bar->s_full[X][i % NSB], (i / NSB) & 1);
     tc_fence_after();
     float s[kTN];
-    tmem_ld32(s_addr, reinterpret_cast<uint32_t*>(&s[0]));
-    tmem_ld32(s_addr + 32, reinterpret_cast<uint32_t*>(&s[32]));
+#pragma unroll
+    for (int c = 0; c < kTN / 32; ++c) tmem_ld32(s_addr + 32 * c, reinterpret_cast<uint32_t*>(&s[32 * c]));
     tmem_ld_wait();
     // warp-uniform fast path: nothing masked, no bias -> raw maximum, scale folded into the exponent's FMA
     const bool plain = !has_alibi && __all_sync(0xffffffffu, limit >= kTN);
@@ -133,7 +141,7 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
     tmem_st_wait();
     observe_o_upto(i - 4);
     tc_fence_before();
-    mbar_arrive(&bar->p_full[X][i & 1]);
+    mbar_arrive(&bar->p_full[X][i % NSB]);
     l_run += (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
   }
 
@@ -162,8 +170,10 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
   }
 }
 
-template <typename MT, int BS>
+template <typename MT, int BS, int TN>
 __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(const CtxAttnParams p) {
+  constexpr int kTN = TN, NSB = Cfg<TN>::kNSB, kStg = Cfg<TN>::kStg, kStgV = Cfg<TN>::kStg;
+  constexpr int kKVTileBytes = Cfg<TN>::kKVTileBytes;
   constexpr int Q_UNITS = kBM * (kD / 8);    // 16-byte granules of a Q tile
   constexpr int KV_UNITS = kTN * (kD / 8);   // ... of a K or V tile
   extern __shared__ __align__(1024) uint8_t tc256_smem[];
@@ -213,11 +223,13 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
   const uint32_t tmem = bar->tmem_base;
 
   if (warp < 8) {
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsSm));
+    if constexpr (TN == 128) asm volatile("setmaxnreg.inc.sync.aligned.u32 192;");  // (8 x 192 + 8 x 64) x 32 = 64 Ki
+    else asm volatile("setmaxnreg.inc.sync.aligned.u32 160;");                       // (8 x 160 + 8 x 96) x 32
     const int X = warp >> 2;
-    softmax_rows<MT>(p, bar, tmem, X, warp, tid, head, m0, q_len, ctx_len, n_ctx_tiles, X ? n_b : n_a, start);
+    softmax_rows<MT, TN>(p, bar, tmem, X, warp, tid, head, m0, q_len, ctx_len, n_ctx_tiles, X ? n_b : n_a, start);
   } else {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsRest));
+    if constexpr (TN == 128) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
+    else asm volatile("setmaxnreg.dec.sync.aligned.u32 96;");
     if (warp == 8) {
       // ================= the MMA warp (uniform: every lane runs the loop, elect.sync issues) =================
       {
@@ -239,45 +251,45 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
           tc_fence_after();
           const uint64_t kd = kd0 + (uint64_t)st * kStageStep;
           const uint64_t qx = qd[X];
-          const uint32_t d_addr = tmem + X * 128 + (i & 1) * kTN;
+          const uint32_t d_addr = tmem + X * 128 + (i % NSB) * kTN;
 #pragma unroll
           for (int ks = 0; ks < kD / 16; ++ks)
             mma_ss_u(d_addr, qx + (uint64_t)(ks * ((2 * kBM * 16) >> 4)), kd + (uint64_t)(ks * ((2 * kTN * 16) >> 4)), idesc_qk,
                    ks > 0);
           if (X == 1 || i >= n_b) tc_commit_u(&bar->k_empty[st]);  // last reader of K tile i
-          tc_commit_u(&bar->s_full[X][i & 1]);
+          tc_commit_u(&bar->s_full[X][i % NSB]);
         };
         auto issue_pv = [&](int X, int i) {  // O_X += P_X.V_i
           const int st = i % kStgV;
           mbar_wait(&bar->v_full[st], (i / kStgV) & 1);
-          mbar_wait(&bar->p_full[X][i & 1], (i >> 1) & 1);
+          mbar_wait(&bar->p_full[X][i % NSB], (i / NSB) & 1);
           tc_fence_after();
           const bool is_ctx = i < n_ctx_tiles;
           // cached V: k-step = two token octets (2 * kD granules); new V: k-step = 16 tokens (16 granules)
           const uint64_t vd = (is_ctx ? vd0_ctx : vd0_new) + (uint64_t)st * kStageStep;
           const uint64_t step = is_ctx ? (uint64_t)((2 * kD * 16) >> 4) : (uint64_t)((16 * 16) >> 4);
           const uint32_t idesc = is_ctx ? idesc_pv : idesc_mn;
-          const uint32_t o_addr = tmem + 256 + X * 128, p_addr = tmem + X * 128 + (i & 1) * kTN;
+          const uint32_t o_addr = tmem + 256 + X * 128, p_addr = tmem + X * 128 + (i % NSB) * kTN;
 #pragma unroll
           for (int kt = 0; kt < kTN / 16; ++kt) mma_ts_u(o_addr, p_addr + kt * 8, vd + kt * step, idesc, (i | kt) > 0);
           if (X == 1 || i >= n_b) tc_commit_u(&bar->v_empty[st]);  // last reader of V tile i
           tc_commit_u(&bar->o_full[X][i & 3]);
         };
-        // Q.K^T runs one tile ahead of the softmax in each block: S_X[(i+2) & 1] is free again, in pipe order, as soon
-        // as P_X(i).V has been issued.  (Block B's Q.K_t^T is always issued before block A's Q.K_{t+1}^T: the K loader
-        // announces tile t+1 only after it has seen tile t's stage released.)
-        issue_qk(0, 0);
-        if (n_b > 0) issue_qk(1, 0);
-        if (1 < n_a) issue_qk(0, 1);
-        if (1 < n_b) issue_qk(1, 1);
+        // Q.K^T runs NSB - 1 tiles ahead of the softmax in each block: S_X[(i + NSB) % NSB] is free again, in pipe
+        // order, as soon as P_X(i).V has been issued.  (Block B's Q.K_t^T is always issued before block A's Q.K_{t+1}^T:
+        // the K loader announces tile t+1 only after it has seen tile t's stage released.)
+        for (int t = 0; t < NSB; ++t) {
+          if (t < n_a) issue_qk(0, t);
+          if (t < n_b) issue_qk(1, t);
+        }
         for (int i = 0; i < n_load; ++i) {
           if (i < n_a) {
             issue_pv(0, i);
-            if (i + 2 < n_a) issue_qk(0, i + 2);
+            if (i + NSB < n_a) issue_qk(0, i + NSB);
           }
           if (i < n_b) {
             issue_pv(1, i);
-            if (i + 2 < n_b) issue_qk(1, i + 2);
+            if (i + NSB < n_b) issue_qk(1, i + NSB);
           }
         }
       }
@@ -369,20 +381,32 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
   if (warp == 8) tmem_dealloc_512(tmem);
 }
 
-template <typename MT, int BS>
-int launch_ctx_attn_tc256(const CtxAttnParams& p, int batch, int max_input_len, cudaStream_t stream) {
+// 128-token tiles measured faster than 64-token tiles once the MMA issue was made warp-uniform? -> see the r05 numbers
+// in profiles/README.md; B200_CTX_TN=64|128 overrides (A/B knob).
+constexpr int kDefaultTN = 128;
+
+template <typename MT, int BS, int TN>
+int launch_ctx_attn_tc256_tn(const CtxAttnParams& p, int batch, int max_input_len, cudaStream_t stream) {
   static bool attr_set[64] = {false};
   int dev = 0;
   B200_CUDA_TRY(cudaGetDevice(&dev));
   dev &= 63;
   if (!attr_set[dev]) {
-    B200_CUDA_TRY(cudaFuncSetAttribute(context_attn_tc256_kernel<MT, BS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem256));
+    B200_CUDA_TRY(cudaFuncSetAttribute(context_attn_tc256_kernel<MT, BS, TN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg<TN>::kSmem));
     attr_set[dev] = true;
   }
   dim3 grid((max_input_len + kRows - 1) / kRows, p.num_heads, batch);
-  context_attn_tc256_kernel<MT, BS><<<grid, kThreads256, kSmem256, stream>>>(p);
+  context_attn_tc256_kernel<MT, BS, TN><<<grid, kThreads256, Cfg<TN>::kSmem, stream>>>(p);
   B200_LAUNCH_CHECK();
   return B200_OK;
+}
+
+template <typename MT, int BS>
+int launch_ctx_attn_tc256(const CtxAttnParams& p, int batch, int max_input_len, cudaStream_t stream) {
+  static const int tn = getenv("B200_CTX_TN") ? atoi(getenv("B200_CTX_TN")) : kDefaultTN;
+  if (tn == 64) return launch_ctx_attn_tc256_tn<MT, BS, 64>(p, batch, max_input_len, stream);
+  return launch_ctx_attn_tc256_tn<MT, BS, 128>(p, batch, max_input_len, stream);
 }
 
 }  // namespace tc256
