@@ -780,7 +780,7 @@ def run_n1(args):
             "gpu_launches": int(launches),
             "roofline": {"bound": "tensor", "achieved": round(tf, 1), "peak": peak, "unit": "TFLOP/s",
                          "frac": round(tf / peak, 4), "traffic": None,
-                         "kernel": "tc::context_attn_tc_kernel (tcgen05.mma, TMEM accumulators)", "kernel_ms": round(ms, 4),
+                         "kernel": "tc256::context_attn_tc256_kernel (tcgen05.mma, TMEM accumulators, 256 query rows per CTA)", "kernel_ms": round(ms, 4),
                          "algorithmic_flops_per_launch": flops, "peak_source": peak_src}}
     print(json.dumps(line), flush=True)
     return 0
