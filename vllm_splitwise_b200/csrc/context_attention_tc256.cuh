@@ -55,24 +55,8 @@ struct Barriers256 {
 };
 static_assert(sizeof(Barriers256) <= 512, "barrier block");
 
-// 2^x on the FMA pipe: x = n + f with n = round(x), f in [-0.5, 0.5]; 2^f by a cubic (interpolated at the Chebyshev
-// nodes, max relative error 1.0e-4 -- below the rounding of P to the 16-bit element type); 2^n by adding n to the
-// exponent field (the integer sits in the low mantissa bits of x + 1.5 * 2^23).  Masked scores (-inf) clamp to 2^-126,
-// which rounds to zero in P.  Used for a fraction of the columns because the exponential phase of the softmax is
-// bound by the MUFU pipe (16 ex2 per clock per SM), not by issue slots.
-__device__ __forceinline__ float ex2_poly3(float x) {
-  x = fmaxf(x, -126.f);
-  const float r = x + 12582912.f;
-  const float f = x - (r - 12582912.f);
-  float p = fmaf(f, 0.0558382829f, 0.2426394785f);
-  p = fmaf(p, f, 0.6931367339f);
-  p = fmaf(p, f, 0.9999245570f);
-  return __int_as_float(__float_as_int(p) + (__float_as_int(r) << 23));
-}
-
-// One softmax thread = one query row of block X: all TN columns of every tile.  POLY: pairs of columns out of every
-// four that take ex2_poly3 instead of MUFU (0, 1 or 2).
-template <typename MT, int TN, int POLY>
+// One softmax thread = one query row of block X: all TN columns of every tile.
+template <typename MT, int TN>
 __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256* bar, uint32_t tmem, int X, int warp, int tid,
                                              int head, int m0, int q_len, int ctx_len, int n_ctx_tiles, int n_x, int64_t start) {
   const int row = tid & 127;
@@ -147,10 +131,8 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
       uint32_t pk[16];
 #pragma unroll
       for (int k = 0; k < 32; k += 2) {
-        const float x0 = fmaf(s[32 * c + k], mul, -m_used), x1 = fmaf(s[32 * c + k + 1], mul, -m_used);
-        const bool poly = ((k >> 1) & 3) < POLY;                        // compile-time per unrolled iteration
-        const float e0 = poly ? ex2_poly3(x0) : ex2_approx(x0);         // masked columns are -inf -> 0
-        const float e1 = poly ? ex2_poly3(x1) : ex2_approx(x1);
+        const float e0 = ex2_approx(fmaf(s[32 * c + k], mul, -m_used));  // masked columns are -inf -> 0
+        const float e1 = ex2_approx(fmaf(s[32 * c + k + 1], mul, -m_used));
         sum4[(k >> 1) & 3] += e0 + e1;
         pk[k >> 1] = pack2<MT>(e0, e1);
       }
@@ -188,7 +170,7 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
   }
 }
 
-template <typename MT, int BS, int TN, int POLY>
+template <typename MT, int BS, int TN>
 __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(const CtxAttnParams p) {
   constexpr int kTN = TN, NSB = Cfg<TN>::kNSB, kStg = Cfg<TN>::kStg, kStgV = Cfg<TN>::kStg;
   constexpr int kKVTileBytes = Cfg<TN>::kKVTileBytes;
@@ -244,7 +226,7 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
     if constexpr (TN == 128) asm volatile("setmaxnreg.inc.sync.aligned.u32 192;");  // (8 x 192 + 8 x 64) x 32 = 64 Ki
     else asm volatile("setmaxnreg.inc.sync.aligned.u32 160;");                       // (8 x 160 + 8 x 96) x 32
     const int X = warp >> 2;
-    softmax_rows<MT, TN, POLY>(p, bar, tmem, X, warp, tid, head, m0, q_len, ctx_len, n_ctx_tiles, X ? n_b : n_a, start);
+    softmax_rows<MT, TN>(p, bar, tmem, X, warp, tid, head, m0, q_len, ctx_len, n_ctx_tiles, X ? n_b : n_a, start);
   } else {
     if constexpr (TN == 128) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
     else asm volatile("setmaxnreg.dec.sync.aligned.u32 96;");
@@ -402,21 +384,20 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
 // 128-token tiles measured faster than 64-token tiles once the MMA issue was made warp-uniform? -> see the r05 numbers
 // in profiles/README.md; B200_CTX_TN=64|128 overrides (A/B knob).
 constexpr int kDefaultTN = 128;
-constexpr int kDefaultPoly = 0;
 
-template <typename MT, int BS, int TN, int POLY>
+template <typename MT, int BS, int TN>
 int launch_ctx_attn_tc256_tn(const CtxAttnParams& p, int batch, int max_input_len, cudaStream_t stream) {
   static bool attr_set[64] = {false};
   int dev = 0;
   B200_CUDA_TRY(cudaGetDevice(&dev));
   dev &= 63;
   if (!attr_set[dev]) {
-    B200_CUDA_TRY(cudaFuncSetAttribute(context_attn_tc256_kernel<MT, BS, TN, POLY>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    B200_CUDA_TRY(cudaFuncSetAttribute(context_attn_tc256_kernel<MT, BS, TN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        Cfg<TN>::kSmem));
     attr_set[dev] = true;
   }
   dim3 grid((max_input_len + kRows - 1) / kRows, p.num_heads, batch);
-  context_attn_tc256_kernel<MT, BS, TN, POLY><<<grid, kThreads256, Cfg<TN>::kSmem, stream>>>(p);
+  context_attn_tc256_kernel<MT, BS, TN><<<grid, kThreads256, Cfg<TN>::kSmem, stream>>>(p);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -424,11 +405,8 @@ int launch_ctx_attn_tc256_tn(const CtxAttnParams& p, int batch, int max_input_le
 template <typename MT, int BS>
 int launch_ctx_attn_tc256(const CtxAttnParams& p, int batch, int max_input_len, cudaStream_t stream) {
   static const int tn = getenv("B200_CTX_TN") ? atoi(getenv("B200_CTX_TN")) : kDefaultTN;
-  static const int poly = getenv("B200_CTX_POLY") ? atoi(getenv("B200_CTX_POLY")) : kDefaultPoly;  // A/B knob
-  if (tn == 64) return launch_ctx_attn_tc256_tn<MT, BS, 64, 0>(p, batch, max_input_len, stream);
-  if (poly == 1) return launch_ctx_attn_tc256_tn<MT, BS, 128, 1>(p, batch, max_input_len, stream);
-  if (poly == 2) return launch_ctx_attn_tc256_tn<MT, BS, 128, 2>(p, batch, max_input_len, stream);
-  return launch_ctx_attn_tc256_tn<MT, BS, 128, 0>(p, batch, max_input_len, stream);
+  if (tn == 64) return launch_ctx_attn_tc256_tn<MT, BS, 64>(p, batch, max_input_len, stream);
+  return launch_ctx_attn_tc256_tn<MT, BS, 128>(p, batch, max_input_len, stream);
 }
 
 }  // namespace tc256
