@@ -85,9 +85,9 @@ EXTRA_N1 = [("c3tp8", "c3tp8", "v1"), ("c3", "c3", "v1"), ("c4_v1", "c4", "v1"),
 # captures of the same commands (mean of the captured launches) -- NOT measured by this run; the file is named in
 # roofline.traffic_source.  Workloads without a capture report traffic null.
 NCU_TRAFFIC = {
-    "c2": (4_295_847_500 + 4_181_760, "profiles/r03_c2_attn_ncu_full.txt"),
-    "c4": (2_148_911_000 + 4_078_976, "profiles/r03_c4_attn_ncu_full.txt"),
-    "c3tp8": (537_709_952 + 3_330_560, "profiles/r03_c3tp8_attn_ncu_full.txt"),
+    "c2": (4_295_645_000 + 4_476_672, "profiles/r05_c2_v1_attn_ncu_full.txt"),
+    "c4": (2_148_934_000 + 3_824_640, "profiles/r05_c4_v1_attn_ncu_full.txt"),
+    "c3tp8": (537_801_216 + 6_942_464, "profiles/r05_c3tp8_v1_attn_ncu_full.txt"),
 }
 
 

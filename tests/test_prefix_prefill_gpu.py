@@ -176,3 +176,46 @@ def test_forward_prefix_mirror():
                          context_lens=c["b_ctx_len"].int(), max_seq_len=c["max_input_len"])
     out = PagedAttentionImpl.forward_prefix(c["q"], c["k"], c["v"], c["k_cache"], c["v_cache"], md, c["alibi_slopes"])
     _check(out, _oracle(c), torch.float16, "forward_prefix")
+
+
+# ---- the 256-row kernel (context_attention_tc256.cuh): row-block and tile boundaries ----------------------------
+_EDGE_Q = [129, 255, 256, 257, 384, 511]
+_EDGE_CTX = [0, 1, 63, 64, 127, 128, 129, 1000]
+
+
+def _edge_case(seed, ql, cl, dtype, heads=(4, 2), bs=16, alibi=False):
+    c = make_case(seed, heads[0], heads[1], 128, bs, ql, cl, alibi, scale=1.0)
+    return _to_dev(c, dtype)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("ctx", _EDGE_CTX)
+def test_256_row_kernel_block_and_tile_boundaries(ctx, dtype):
+    """Sequences whose new tokens end just before / at / after a 128-row block and a 256-row CTA, over cached prefixes
+    that end just before / at / after a 64- and a 128-token tile; one batch per prefix length so that max_input_len
+    > 128 routes the call to the 256-row kernel (block B absent, partial and full)."""
+    c = _edge_case(100 + ctx, _EDGE_Q, [ctx] * len(_EDGE_Q), dtype)
+    _check(_run(c), _oracle(c), dtype, f"ctx {ctx}")
+
+
+@pytest.mark.parametrize("bs", [8, 32])
+def test_256_row_kernel_ragged_batch_alibi_block_sizes(bs):
+    """Ragged batch (1 .. 700 new tokens, 0 .. 900 cached) with ALiBi, block sizes 8 and 32, GQA 8:1."""
+    random.seed(bs)
+    ql = [1, 128, 700] + [random.randint(1, 700) for _ in range(4)]
+    cl = [900, 0, 333] + [random.randint(0, 900) for _ in range(4)]
+    c = _edge_case(7 + bs, ql, cl, torch.float16, heads=(8, 1), bs=bs, alibi=True)
+    _check(_run(c), _oracle(c), torch.float16, f"bs {bs}")
+
+
+@pytest.mark.parametrize("env", [{"B200_CTX_TN": "64"}, {"B200_CTX_ATTN": "tc128"}], ids=["tn64", "tc128"])
+def test_other_kernel_variants_in_a_subprocess(env):
+    """The kernel choice is read once per process: the 64-token-tile variant of the 256-row kernel and the 128-row
+    kernel forced for long inputs run the boundary cases in a child process."""
+    import subprocess
+    import sys
+    child = dict(os.environ, **env)
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", __file__, "-k",
+                        "block_and_tile_boundaries or ragged_batch_alibi"], env=child, capture_output=True, text=True,
+                       timeout=600, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-1000:]
