@@ -183,9 +183,17 @@ _EDGE_Q = [129, 255, 256, 257, 384, 511]
 _EDGE_CTX = [0, 1, 63, 64, 127, 128, 129, 1000]
 
 
-def _edge_case(seed, ql, cl, dtype, heads=(4, 2), bs=16, alibi=False):
-    c = make_case(seed, heads[0], heads[1], 128, bs, ql, cl, alibi, scale=1.0)
+def _edge_case(seed, ql, cl, dtype, heads=(4, 2), bs=16, alibi=False, D=128):
+    c = make_case(seed, heads[0], heads[1], D, bs, ql, cl, alibi, scale=1.0)
     return _to_dev(c, dtype)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("ctx,bs", [(0, 16), (129, 8), (1000, 32), (63, 16)])
+def test_256_row_kernel_head_size_64(ctx, bs, dtype):
+    """Head size 64 on the 256-row tcgen05 kernel (N = 64 P.V tiles, four k-steps of Q.K^T): the same boundary lengths."""
+    c = _edge_case(300 + ctx, _EDGE_Q, [ctx] * len(_EDGE_Q), dtype, bs=bs, D=64)
+    _check(_run(c), _oracle(c), dtype, f"D 64 ctx {ctx} bs {bs}")
 
 
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
@@ -216,6 +224,6 @@ def test_other_kernel_variants_in_a_subprocess(env):
     import sys
     child = dict(os.environ, **env)
     r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", __file__, "-k",
-                        "block_and_tile_boundaries or ragged_batch_alibi"], env=child, capture_output=True, text=True,
+                        "block_and_tile_boundaries or ragged_batch_alibi or head_size_64"], env=child, capture_output=True, text=True,
                        timeout=600, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-1000:]

@@ -169,23 +169,24 @@ __device__ __forceinline__ void row_major_granule(int e, int& row, int& j) {
 
 // [row][D] source (new K, new V, Q) -> [d-octet][row] granules.  A warp instruction covers 8 rows x 4 octets:
 // 64-byte global segments and four conflict-free 128-byte shared-memory lines.
-template <typename MT, int NT, bool ZERO_FILL, int ROWS = kBN>  // ROWS = rows of the tile
+template <typename MT, int NT, bool ZERO_FILL, int ROWS = kBN, int D = kD>  // ROWS = rows of the tile, D = head size
 __device__ __forceinline__ void load_rows(uint4* tile, const MT* src, int64_t row_stride, int rows_valid, int lt) {
   constexpr int JW = NT / 8;  // d-octets covered per pass
+  static_assert(JW <= D / 8 && (D / 8) % JW == 0, "loader threads vs head size");
   const int row_lo = lt & 7, j_lo = lt >> 3;
   const MT* s0 = src + (int64_t)row_lo * row_stride + j_lo * 8;
   uint4* d0 = tile + j_lo * ROWS + row_lo;
   const int64_t step = 8 * row_stride;
   if (rows_valid >= ROWS) {
 #pragma unroll
-    for (int jh = 0; jh < 16 / JW; ++jh) {
+    for (int jh = 0; jh < (D / 8) / JW; ++jh) {
       const MT* sp = s0 + jh * JW * 8;
 #pragma unroll
       for (int rh = 0; rh < ROWS / 8; ++rh, sp += step) cp_async16(d0 + jh * JW * ROWS + rh * 8, sp);
     }
   } else {
 #pragma unroll
-    for (int jh = 0; jh < 16 / JW; ++jh) {
+    for (int jh = 0; jh < (D / 8) / JW; ++jh) {
       const MT* sp = s0 + jh * JW * 8;
 #pragma unroll 4
       for (int rh = 0; rh < ROWS / 8; ++rh, sp += step) {
@@ -197,10 +198,11 @@ __device__ __forceinline__ void load_rows(uint4* tile, const MT* src, int64_t ro
 }
 
 // cached K: chunks [D/8][BS][8] of the blocks bt[0..] -> [d-octet][token] granules
-template <typename MT, int BS, int NT, int TN = kBN>  // TN = tokens of the tile
+template <typename MT, int BS, int NT, int TN = kBN, int D = kD>  // TN = tokens of the tile
 __device__ __forceinline__ void load_k_ctx(uint4* tile, const MT* kc, int64_t block_stride, const int32_t* bt,
                                            int toks_valid, int lt, int lane) {
   constexpr int JW = NT / BS;  // d-octets covered per pass
+  static_assert(JW <= D / 8 && (D / 8) % JW == 0, "loader threads vs head size");
   const int tt = lt % BS, jl = lt / BS;
   // lane c holds the physical number of the tile's c-th block; the loop gets it by shuffle, so no load sits in
   // front of a cp.async
@@ -213,17 +215,18 @@ __device__ __forceinline__ void load_k_ctx(uint4* tile, const MT* kc, int64_t bl
       const MT* sp = kc + bn * block_stride + (jl * BS + tt) * 8;
       uint4* dp = tile + jl * TN + c * BS + tt;
 #pragma unroll
-      for (int q = 0; q < 16 / JW; ++q) cp_async16(dp + q * JW * TN, sp + q * JW * BS * 8);
+      for (int q = 0; q < (D / 8) / JW; ++q) cp_async16(dp + q * JW * TN, sp + q * JW * BS * 8);
     }
   }
 }
 
 // cached V: chunks [D][BS] -> [token-octet][d] granules; octets past the context end are zero-filled
-template <typename MT, int BS, int NT, int TN = kBN>
+template <typename MT, int BS, int NT, int TN = kBN, int D = kD>
 __device__ __forceinline__ void load_v_ctx(uint4* tile, const MT* vc, int64_t block_stride, const int32_t* bt,
                                            int toks_valid, int lt, int lane) {
   constexpr int HG = BS / 8;   // token octets per block
   constexpr int DW = NT / HG;  // d rows covered per pass
+  static_assert(DW <= D && D % DW == 0, "loader threads vs head size");
   const int hh = lt % HG, dl = lt / HG;
   int my_bn = 0;
   if (lane < TN / BS && lane * BS < toks_valid) my_bn = bt[lane];
@@ -231,14 +234,14 @@ __device__ __forceinline__ void load_v_ctx(uint4* tile, const MT* vc, int64_t bl
   for (int c = 0; c < TN / BS; ++c) {
     const int64_t bn = __shfl_sync(0xffffffffu, my_bn, c);
     const int tg = c * HG + hh;
-    uint4* dp = tile + tg * kD + dl;
+    uint4* dp = tile + tg * D + dl;
     if (tg * 8 < toks_valid) {
       const MT* sp = vc + bn * block_stride + dl * BS + hh * 8;
 #pragma unroll
-      for (int q = 0; q < kD / DW; ++q) cp_async16(dp + q * DW, sp + q * DW * BS);
+      for (int q = 0; q < D / DW; ++q) cp_async16(dp + q * DW, sp + q * DW * BS);
     } else {
 #pragma unroll
-      for (int q = 0; q < kD / DW; ++q) dp[q * DW] = make_uint4(0u, 0u, 0u, 0u);
+      for (int q = 0; q < D / DW; ++q) dp[q * DW] = make_uint4(0u, 0u, 0u, 0u);
     }
   }
 }

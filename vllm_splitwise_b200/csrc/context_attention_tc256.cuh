@@ -1,4 +1,4 @@
-// Prefix prefill on tcgen05/TMEM, 256 query rows per CTA (two 128-row blocks A and B), head size 128, 64-token KV tiles.
+// Prefix prefill on tcgen05/TMEM, 256 query rows per CTA (two 128-row blocks A and B), head sizes 128 and 64.
 //
 // context_attn_tc_kernel (context_attention_tc.cuh) does 128 flop per byte it pulls out of L2 -- every 128-row CTA
 // reads all of its K/V -- and ncu (profiles/r05_ctx_tc_stalls_after.txt) shows where that ends: the MMA thread waits
@@ -28,17 +28,20 @@ using namespace tc;
 
 constexpr int kRows = 2 * kBM;   // query rows per CTA
 constexpr int kThreads256 = 512;
-constexpr int kKLoad = 64, kVLoad = 128;
+constexpr int kKLoad = 64;  // K (+Q) loader threads; V loader threads: Cfg::kVLoad
 constexpr int kMaxStg = 4;
 // TN = KV tokens per tile.  TN = 128: one S buffer per block (Q.K^T of tile i+1 follows P.V of tile i), two 32 KiB
 // stages each for K and V, 192 registers per softmax thread (128 scores).  TN = 64: two S buffers per block (Q.K^T a
 // tile ahead), four 16 KiB stages, 160 registers.  Measured (profiles/r05_prefix_prefill_tc256*.jsonl): see kDefaultTN.
-template <int TN>
+template <int TN, int D = kD>
 struct Cfg {
   static constexpr int kNSB = 128 / TN;              // S buffers per row block
   static constexpr int kStg = 256 / TN;              // K and V ring depth
-  static constexpr int kKVTileBytes = TN * kD * 2;
-  static constexpr int kSmem = 2 * kTileBytes + 2 * kStg * kKVTileBytes + 512;
+  static constexpr int kQTileBytes = kBM * D * 2;
+  static constexpr int kKVTileBytes = TN * D * 2;
+  static constexpr int kVLoad = D == 128 ? 128 : 64;  // V loader threads (a pass of the cached-V loader covers 32-128 d rows)
+  static constexpr int kSmem = 2 * kQTileBytes + 2 * kStg * kKVTileBytes + 512;
+  static_assert(D == 64 || D == 128, "head sizes of this kernel");
   static_assert(TN == 64 || TN == 128, "tile sizes");
   static_assert(kStg <= kMaxStg, "ring depth");
 };
@@ -56,7 +59,7 @@ struct Barriers256 {
 static_assert(sizeof(Barriers256) <= 512, "barrier block");
 
 // One softmax thread = one query row of block X: all TN columns of every tile.
-template <typename MT, int TN>
+template <typename MT, int TN, int D>
 __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256* bar, uint32_t tmem, int X, int warp, int tid,
                                              int head, int m0, int q_len, int ctx_len, int n_ctx_tiles, int n_x, int64_t start) {
   const int row = tid & 127;
@@ -111,7 +114,7 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
         observe_o_upto(i - 1);
         tc_fence_after();
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < D / 32; ++c) {
           uint32_t r[32];
           tmem_ld32(o_addr + 32 * c, r);
           tmem_ld_wait();
@@ -151,7 +154,7 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
     const float inv = 1.f / l_run;
     MT* orow = static_cast<MT*>(p.o) + (start + qrow) * p.o_ts + (int64_t)head * p.o_hs;
 #pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
+    for (int c = 0; c < D / 32; ++c) {
       uint32_t r[32];
       tmem_ld32(o_addr + 32 * c, r);
       tmem_ld_wait();
@@ -170,12 +173,13 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
   }
 }
 
-template <typename MT, int BS, int TN>
+template <typename MT, int BS, int TN, int D>
 __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(const CtxAttnParams p) {
-  constexpr int kTN = TN, NSB = Cfg<TN>::kNSB, kStg = Cfg<TN>::kStg, kStgV = Cfg<TN>::kStg;
-  constexpr int kKVTileBytes = Cfg<TN>::kKVTileBytes;
-  constexpr int Q_UNITS = kBM * (kD / 8);    // 16-byte granules of a Q tile
-  constexpr int KV_UNITS = kTN * (kD / 8);   // ... of a K or V tile
+  using C = Cfg<TN, D>;
+  constexpr int kTN = TN, NSB = C::kNSB, kStg = C::kStg, kStgV = C::kStg, kVLoad = C::kVLoad;
+  constexpr int kKVTileBytes = C::kKVTileBytes, kQTileBytes = C::kQTileBytes;
+  constexpr int Q_UNITS = kBM * (D / 8);    // 16-byte granules of a Q tile
+  constexpr int KV_UNITS = kTN * (D / 8);   // ... of a K or V tile
   extern __shared__ __align__(1024) uint8_t tc256_smem[];
   uint4* q_s = reinterpret_cast<uint4*>(tc256_smem);  // Q_A, Q_B
   uint4* k_s = q_s + 2 * Q_UNITS;
@@ -226,7 +230,7 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
     if constexpr (TN == 128) asm volatile("setmaxnreg.inc.sync.aligned.u32 192;");  // (8 x 192 + 8 x 64) x 32 = 64 Ki
     else asm volatile("setmaxnreg.inc.sync.aligned.u32 160;");                       // (8 x 160 + 8 x 96) x 32
     const int X = warp >> 2;
-    softmax_rows<MT, TN>(p, bar, tmem, X, warp, tid, head, m0, q_len, ctx_len, n_ctx_tiles, X ? n_b : n_a, start);
+    softmax_rows<MT, TN, D>(p, bar, tmem, X, warp, tid, head, m0, q_len, ctx_len, n_ctx_tiles, X ? n_b : n_a, start);
   } else {
     if constexpr (TN == 128) asm volatile("setmaxnreg.dec.sync.aligned.u32 64;");
     else asm volatile("setmaxnreg.dec.sync.aligned.u32 96;");
@@ -234,14 +238,14 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
       // ================= the MMA warp (uniform: every lane runs the loop, elect.sync issues) =================
       {
         const uint32_t idesc_qk = instr_desc<MT>(kTN, false);  // S = Q.K^T: N = 64 tokens, K-major B
-        const uint32_t idesc_pv = instr_desc<MT>(kD, false);   // O += P.V over cached V: N = 128, K-major B
-        const uint32_t idesc_mn = instr_desc<MT>(kD, true);    // ... over new V: MN-major B
+        const uint32_t idesc_pv = instr_desc<MT>(D, false);    // O += P.V over cached V: N = 128, K-major B
+        const uint32_t idesc_mn = instr_desc<MT>(D, true);     // ... over new V: MN-major B
         // Shared-memory descriptors are built ONCE: the start-address field is the low 14 bits (address >> 4), so the
         // descriptor of "base + off" is the base descriptor plus off >> 4.  (ncu, r05: building two descriptors per
         // tcgen05.mma from scratch made the issuing thread the bottleneck -- 80 % busy, tensor pipe 26 % active.)
-        const uint64_t qd[2] = {smem_desc(smem_u32(q_s), kBM * 16, 128), smem_desc(smem_u32(q_s) + kTileBytes, kBM * 16, 128)};
+        const uint64_t qd[2] = {smem_desc(smem_u32(q_s), kBM * 16, 128), smem_desc(smem_u32(q_s) + kQTileBytes, kBM * 16, 128)};
         const uint64_t kd0 = smem_desc(smem_u32(k_s), kTN * 16, 128);      // K-major [d-octet][token]
-        const uint64_t vd0_ctx = smem_desc(smem_u32(v_s), kD * 16, 128);   // cached V: K-major [token-octet][d]
+        const uint64_t vd0_ctx = smem_desc(smem_u32(v_s), D * 16, 128);    // cached V: K-major [token-octet][d]
         const uint64_t vd0_new = smem_desc(smem_u32(v_s), 128, kTN * 16);  // new V: MN-major [d-octet][token]
         constexpr uint64_t kStageStep = kKVTileBytes >> 4;
         mbar_wait(&bar->q_full, 0);
@@ -253,7 +257,7 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
           const uint64_t qx = qd[X];
           const uint32_t d_addr = tmem + X * 128 + (i % NSB) * kTN;
 #pragma unroll
-          for (int ks = 0; ks < kD / 16; ++ks)
+          for (int ks = 0; ks < D / 16; ++ks)
             mma_ss_u(d_addr, qx + (uint64_t)(ks * ((2 * kBM * 16) >> 4)), kd + (uint64_t)(ks * ((2 * kTN * 16) >> 4)), idesc_qk,
                    ks > 0);
           if (X == 1 || i >= n_b) tc_commit_u(&bar->k_empty[st]);  // last reader of K tile i
@@ -267,7 +271,7 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
           const bool is_ctx = i < n_ctx_tiles;
           // cached V: k-step = two token octets (2 * kD granules); new V: k-step = 16 tokens (16 granules)
           const uint64_t vd = (is_ctx ? vd0_ctx : vd0_new) + (uint64_t)st * kStageStep;
-          const uint64_t step = is_ctx ? (uint64_t)((2 * kD * 16) >> 4) : (uint64_t)((16 * 16) >> 4);
+          const uint64_t step = is_ctx ? (uint64_t)((2 * D * 16) >> 4) : (uint64_t)((16 * 16) >> 4);
           const uint32_t idesc = is_ctx ? idesc_pv : idesc_mn;
           const uint32_t o_addr = tmem + 256 + X * 128, p_addr = tmem + X * 128 + (i % NSB) * kTN;
 #pragma unroll
@@ -304,15 +308,15 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
         uint4* Ks = k_s + (ti % kStg) * KV_UNITS;
         if (ti < n_ctx_tiles) {
           const int n0 = ti * kTN;
-          load_k_ctx<MT, BS, kKLoad, kTN>(Ks, kc, p.kc_bs, bt + n0 / BS, ctx_len - n0, lt, lane);
+          load_k_ctx<MT, BS, kKLoad, kTN, D>(Ks, kc, p.kc_bs, bt + n0 / BS, ctx_len - n0, lt, lane);
         } else {
           const int n0 = (ti - n_ctx_tiles) * kTN;
-          load_rows<MT, kKLoad, false, kTN>(Ks, kn + (int64_t)n0 * p.k_ts, p.k_ts, q_len - n0, lt);
+          load_rows<MT, kKLoad, false, kTN, D>(Ks, kn + (int64_t)n0 * p.k_ts, p.k_ts, q_len - n0, lt);
         }
       };
       const MT* qb = static_cast<const MT*>(p.q) + (start + m0) * p.q_ts + (int64_t)head * p.q_hs;
-      load_rows<MT, kKLoad, true, kBM>(q_s, qb, p.q_ts, q_len - m0, lt);
-      load_rows<MT, kKLoad, true, kBM>(q_s + Q_UNITS, qb + (int64_t)kBM * p.q_ts, p.q_ts, q_len - m0 - kBM, lt);
+      load_rows<MT, kKLoad, true, kBM, D>(q_s, qb, p.q_ts, q_len - m0, lt);
+      load_rows<MT, kKLoad, true, kBM, D>(q_s + Q_UNITS, qb + (int64_t)kBM * p.q_ts, p.q_ts, q_len - m0 - kBM, lt);
       cp_async_commit();
       const int pro = min(kStg, n_load);
       for (int t = 0; t < pro; ++t) {
@@ -333,7 +337,7 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
           cp_async_commit();
         }
       }
-    } else if (warp >= 12) {
+    } else if (warp >= 12 && warp < 12 + kVLoad / 32) {
       // ================= V loaders =================
       const int lt = tid - 12 * 32;
       const MT* vc = static_cast<const MT*>(p.v_cache) + (int64_t)kvh * p.vc_hs;
@@ -343,10 +347,10 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
         uint4* Vs = v_s + (ti % kStgV) * KV_UNITS;
         if (ti < n_ctx_tiles) {
           const int n0 = ti * kTN;
-          load_v_ctx<MT, BS, kVLoad, kTN>(Vs, vc, p.vc_bs, bt + n0 / BS, ctx_len - n0, lt, lane);
+          load_v_ctx<MT, BS, kVLoad, kTN, D>(Vs, vc, p.vc_bs, bt + n0 / BS, ctx_len - n0, lt, lane);
         } else {
           const int n0 = (ti - n_ctx_tiles) * kTN;
-          load_rows<MT, kVLoad, true, kTN>(Vs, vn + (int64_t)n0 * p.v_ts, p.v_ts, q_len - n0, lt);
+          load_rows<MT, kVLoad, true, kTN, D>(Vs, vn + (int64_t)n0 * p.v_ts, p.v_ts, q_len - n0, lt);
         }
       };
       for (int t = 0; t < kStgV && t < n_load; ++t) {
@@ -359,8 +363,8 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
           // the token octet that straddles ctx_len: slots past the end are stale cache memory (may be NaN / Inf)
           asm volatile("bar.sync 1, %0;" ::"n"(kVLoad) : "memory");  // every V loader's copies of tile i landed
           const int tgb = (ctx_len - i * kTN) >> 3, rem = (ctx_len - i * kTN) & 7;
-          for (int d = lt; d < kD; d += kVLoad) {
-            MT* gp = reinterpret_cast<MT*>(&v_s[(i % kStgV) * KV_UNITS + tgb * kD + d]);
+          for (int d = lt; d < D; d += kVLoad) {
+            MT* gp = reinterpret_cast<MT*>(&v_s[(i % kStgV) * KV_UNITS + tgb * D + d]);
             for (int x = rem; x < 8; ++x) gp[x] = MT(0.f);
           }
         }
@@ -385,28 +389,28 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
 // in profiles/README.md; B200_CTX_TN=64|128 overrides (A/B knob).
 constexpr int kDefaultTN = 128;
 
-template <typename MT, int BS, int TN>
+template <typename MT, int BS, int TN, int D>
 int launch_ctx_attn_tc256_tn(const CtxAttnParams& p, int batch, int max_input_len, cudaStream_t stream) {
   static bool attr_set[64] = {false};
   int dev = 0;
   B200_CUDA_TRY(cudaGetDevice(&dev));
   dev &= 63;
   if (!attr_set[dev]) {
-    B200_CUDA_TRY(cudaFuncSetAttribute(context_attn_tc256_kernel<MT, BS, TN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       Cfg<TN>::kSmem));
+    B200_CUDA_TRY(cudaFuncSetAttribute(context_attn_tc256_kernel<MT, BS, TN, D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg<TN, D>::kSmem));
     attr_set[dev] = true;
   }
   dim3 grid((max_input_len + kRows - 1) / kRows, p.num_heads, batch);
-  context_attn_tc256_kernel<MT, BS, TN><<<grid, kThreads256, Cfg<TN>::kSmem, stream>>>(p);
+  context_attn_tc256_kernel<MT, BS, TN, D><<<grid, kThreads256, Cfg<TN, D>::kSmem, stream>>>(p);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
 
-template <typename MT, int BS>
+template <typename MT, int BS, int D = kD>
 int launch_ctx_attn_tc256(const CtxAttnParams& p, int batch, int max_input_len, cudaStream_t stream) {
   static const int tn = getenv("B200_CTX_TN") ? atoi(getenv("B200_CTX_TN")) : kDefaultTN;
-  if (tn == 64) return launch_ctx_attn_tc256_tn<MT, BS, 64>(p, batch, max_input_len, stream);
-  return launch_ctx_attn_tc256_tn<MT, BS, 128>(p, batch, max_input_len, stream);
+  if (tn == 64) return launch_ctx_attn_tc256_tn<MT, BS, 64, D>(p, batch, max_input_len, stream);
+  return launch_ctx_attn_tc256_tn<MT, BS, 128, D>(p, batch, max_input_len, stream);
 }
 
 }  // namespace tc256
