@@ -426,23 +426,28 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
   } else if (warp < 12) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsOther));
    if (warp == kMmaWarp) {
-    // ================= the MMA-issuing thread =================
-    if (lane == 0) {
+    // ================= the MMA warp (uniform: every lane runs the loop, elect.sync issues) =================
+    {
       const uint32_t idesc_k = instr_desc<MT>(kBN, false);   // Q.K^T and P.V over cached V: K-major B
       const uint32_t idesc_mn = instr_desc<MT>(kD, true);    // P.V over new V: MN-major B
-      const uint32_t q_addr = smem_u32(q_s);
+      // descriptors are built once and advanced by integer adds on the start-address field (address >> 4)
+      const uint64_t qd = smem_desc(smem_u32(q_s), kBM * 16, 128);
+      const uint64_t kd0 = smem_desc(smem_u32(k_s), kBN * 16, 128);
+      const uint64_t vd0_ctx = smem_desc(smem_u32(v_s), kD * 16, 128);   // cached V: K-major [token-octet][d]
+      const uint64_t vd0_new = smem_desc(smem_u32(v_s), 128, kBN * 16);  // new V: MN-major [d-octet][token]
+      constexpr uint64_t kStageStep = kTileBytes >> 4;
       mbar_wait(&bar->q_full, 0);
       auto issue_qk = [&](int i) {  // S_i = Q.K_i^T into S buffer i%3
         const int st = i % kStages;
         mbar_wait(&bar->k_full[st], (i / kStages) & 1);
         tc_fence_after();
-        const uint32_t k_addr = smem_u32(k_s + st * TILE_UNITS);
+        const uint64_t kd = kd0 + (uint64_t)st * kStageStep;
 #pragma unroll
         for (int ks = 0; ks < kD / 16; ++ks)
-          mma_ss(tmem + (i % 3) * 128, smem_desc(q_addr + ks * 2 * kBM * 16, kBM * 16, 128),
-                 smem_desc(k_addr + ks * 2 * kBN * 16, kBN * 16, 128), idesc_k, ks > 0);
-        tc_commit(&bar->k_empty[st]);
-        tc_commit(&bar->s_full[i % 3]);
+          mma_ss_u(tmem + (i % 3) * 128, qd + (uint64_t)(ks * ((2 * kBM * 16) >> 4)),
+                   kd + (uint64_t)(ks * ((2 * kBN * 16) >> 4)), idesc_k, ks > 0);
+        tc_commit_u(&bar->k_empty[st]);
+        tc_commit_u(&bar->s_full[i % 3]);
       };
       // Q.K^T runs three tiles ahead of P.V (three S buffers; a buffer is free again, in pipe order, as soon as the
       // P.V that reads it has been issued): S_{j+1} and S_{j+2} are ready when the softmax warps finish tile j
@@ -453,20 +458,20 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
         {  // O += P_j.V_j (first: it is on the softmax warps' critical path)
           const int st = j % kStages, sb = j % 3;
           mbar_wait(&bar->v_full[st], (j / kStages) & 1);
-          mbar_wait(&bar->p_full[sb], (j / 3) & 1);  // implies the softmax threads have seen O_{j-1} (and rescaled it)
+          mbar_wait(&bar->p_full[sb], (j / 3) & 1);
           tc_fence_after();
-          const uint32_t v_addr = smem_u32(v_s + st * TILE_UNITS);
           const bool is_ctx = j < n_ctx_tiles;
+          // cached V: [token-octet][d] granules (K-major, LBO = next token octet, SBO = next 8 d rows), k-step = two
+          // token octets; new V: [d-octet][token] granules (MN-major, LBO = next 8 tokens, SBO = next d octet), k-step =
+          // 16 tokens
+          const uint64_t vd = (is_ctx ? vd0_ctx : vd0_new) + (uint64_t)st * kStageStep;
+          const uint64_t step = is_ctx ? (uint64_t)((2 * kD * 16) >> 4) : (uint64_t)((16 * 16) >> 4);
+          const uint32_t idesc = is_ctx ? idesc_k : idesc_mn;
 #pragma unroll
-          for (int kt = 0; kt < kBN / 16; ++kt) {
-            // cached V: [token-octet][d] granules (K-major, LBO = next token octet, SBO = next 8 d rows);
-            // new V:    [d-octet][token] granules (MN-major, LBO = next 8 tokens, SBO = next d octet)
-            const uint64_t b = is_ctx ? smem_desc(v_addr + kt * 2 * kD * 16, kD * 16, 128)
-                                      : smem_desc(v_addr + kt * 16 * 16, 128, kBN * 16);
-            mma_ts(tmem + 384, tmem + sb * 128 + kt * 8, b, is_ctx ? idesc_k : idesc_mn, (j | kt) > 0);
-          }
-          tc_commit(&bar->v_empty[st]);
-          tc_commit(&bar->o_full[j & 3]);
+          for (int kt = 0; kt < kBN / 16; ++kt)
+            mma_ts_u(tmem + 384, tmem + sb * 128 + kt * 8, vd + kt * step, idesc, (j | kt) > 0);
+          tc_commit_u(&bar->v_empty[st]);
+          tc_commit_u(&bar->o_full[j & 3]);
         }
         // S buffer j % 3 is free again in pipe order (P_j.V_j was just issued and tcgen05.mma's execute in order)
         if (j + 3 < n_tiles) issue_qk(j + 3);
