@@ -48,7 +48,8 @@ typedef enum {
   B200_ERR_ALIGN = -5,      /* cache chunk not 16-byte aligned (bulk-copy requirement) */
   B200_ERR_CUDA = -6,       /* a CUDA runtime call failed; see b200_kv_last_cuda_error() */
   B200_ERR_DEVICE = -7,     /* swap_blocks: src and dst on different GPUs (cache_kernels.cu:28-32) */
-  B200_ERR_TIMEOUT = -8     /* kv wait: bounded spin expired (kv_comm_kernels.cu:7) */
+  B200_ERR_TIMEOUT = -8,    /* kv wait: bounded spin expired (kv_comm_kernels.cu:7) */
+  B200_ERR_SCRATCH_LIMIT = -9 /* b200_paged_attention_v2_static_scratch: the call needs more than B200_V2_STATIC_SCRATCH_BYTES */
 } b200_status_t;
 
 typedef enum {
@@ -128,6 +129,25 @@ typedef struct {
 B200_API int b200_paged_attention_v1(const b200_paged_attn_args_t* args, b200_stream_t stream);
 B200_API int b200_paged_attention_v2(const b200_paged_attn_args_t* args, b200_stream_t stream);
 B200_API int64_t b200_paged_attention_workspace_bytes(const b200_paged_attn_args_t* args);
+
+/* paged_attention_v2 for callers that cannot allocate (code under CUDA graph capture, serving loops and harnesses
+ * that forbid cudaMalloc).  No counterpart in the reference.
+ * Same kernels and the same results, bit for bit, as b200_paged_attention_v2, but the v2 scratch (tmp_out, exp_sums,
+ * max_logits) lives in a file-scope __device__ array of B200_V2_STATIC_SCRATCH_BYTES inside the library, resolved
+ * once per device with cudaGetSymbolAddress; args->tmp_out / exp_sums / max_logits / max_num_partitions are ignored
+ * (partitions = ceil(max_context_len / 512)).  The call allocates nothing (no cudaMalloc / cudaFree, no allocating
+ * library routine) and never synchronises.
+ *   limit   num_seqs * num_heads * partitions * (head_size * sizeof(query element) + 8) bytes, each of the three
+ *           pieces rounded up to 256 -- b200_paged_attention_v2_static_scratch_bytes(args) -- must not exceed
+ *           B200_V2_STATIC_SCRATCH_BYTES, else B200_ERR_SCRATCH_LIMIT and nothing is launched
+ *           (8 MiB = e.g. 64 sequences x 32 heads x 4096 tokens of context at head size 128, f16/bf16).
+ *   sharing every call on a device uses the SAME array (it keeps the last call's contents; nothing in it has to
+ *           start at zero).  Calls that can overlap on the GPU -- different streams, or graphs replayed
+ *           concurrently -- race on it: serialise them, or use b200_paged_attention_v2 with caller scratch.
+ * Every GPU that loads the library holds the array until the process exits. */
+#define B200_V2_STATIC_SCRATCH_BYTES (8 << 20)
+B200_API int b200_paged_attention_v2_static_scratch(const b200_paged_attn_args_t* args, b200_stream_t stream);
+B200_API int64_t b200_paged_attention_v2_static_scratch_bytes(const b200_paged_attn_args_t* args);
 
 /* ------------------------------------------------------------------------------------------
  * Cache writes and block moves.

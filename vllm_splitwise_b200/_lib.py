@@ -98,6 +98,8 @@ SIGNATURES = {
     "b200_paged_attention_v1": (c_int32, [POINTER(PagedAttnArgs), c_void_p]),
     "b200_paged_attention_v2": (c_int32, [POINTER(PagedAttnArgs), c_void_p]),
     "b200_paged_attention_workspace_bytes": (c_int64, [POINTER(PagedAttnArgs)]),
+    "b200_paged_attention_v2_static_scratch": (c_int32, [POINTER(PagedAttnArgs), c_void_p]),
+    "b200_paged_attention_v2_static_scratch_bytes": (c_int64, [POINTER(PagedAttnArgs)]),
     "b200_context_attention_fwd": (c_int32, [POINTER(ContextAttnArgs), c_void_p]),
     "b200_allreduce_oneshot": (c_int32, [POINTER(c_int64), POINTER(c_int64), POINTER(c_int64), c_void_p, c_void_p,
                                          c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_int32, c_uint64,

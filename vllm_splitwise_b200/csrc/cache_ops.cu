@@ -531,6 +531,7 @@ B200_API const char* b200_kv_strerror(int status) {
     case B200_ERR_CUDA: return "CUDA runtime error";
     case B200_ERR_DEVICE: return "src and dst must be on the same GPU";
     case B200_ERR_TIMEOUT: return "KV wait timed out";
+    case B200_ERR_SCRATCH_LIMIT: return "call needs more scratch than the library's static array holds (B200_V2_STATIC_SCRATCH_BYTES)";
     default: return "unknown status";
   }
 }

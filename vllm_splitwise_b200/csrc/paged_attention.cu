@@ -264,6 +264,30 @@ int plan_v1_split(const b200_paged_attn_args_t* a, int tiles_per_seq, int slots,
   return best_np;
 }
 
+// Scratch of b200_paged_attention_v2_static_scratch: tmp_out | exp_sums | max_logits of ONE v2 call, held in the
+// library's own image instead of caller tensors (every device that loads the library keeps these bytes until the
+// process exits).  In host code `g_v2_static_scratch` is only a handle for cudaGetSymbolAddress -- never a device
+// address -- so the host side resolves it once per device, with that device current.
+static __device__ __align__(256) unsigned char g_v2_static_scratch[B200_V2_STATIC_SCRATCH_BYTES];
+
+int static_scratch_base(unsigned char** out) {
+  static std::atomic<unsigned char*> base[64];
+  int dev = 0;
+  B200_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return B200_ERR_ARG;
+  unsigned char* b = base[dev].load(std::memory_order_acquire);
+  if (!b) {
+    void* sym = nullptr;
+    B200_CUDA_TRY(cudaGetSymbolAddress(&sym, g_v2_static_scratch));
+    b = static_cast<unsigned char*>(sym);
+    base[dev].store(b, std::memory_order_release);  // racing threads resolve the same address
+  }
+  *out = b;
+  return B200_OK;
+}
+
+constexpr int64_t align256(int64_t v) { return (v + 255) / 256 * 256; }
+
 }  // namespace
 }  // namespace b200
 
@@ -351,6 +375,38 @@ B200_API int b200_paged_attention_v2(const b200_paged_attn_args_t* a, b200_strea
   st = dispatch(a, p, tile, budget, sms, stream);
   if (st != B200_OK) return st;
   return launch_reduce(a, a->max_num_partitions, kV2PartitionTokens, stream);
+}
+
+B200_API int64_t b200_paged_attention_v2_static_scratch_bytes(const b200_paged_attn_args_t* a) {
+  if (!a || a->num_seqs <= 0 || a->num_heads <= 0 || a->head_size <= 0 || a->max_context_len <= 0) return 0;
+  const int64_t np = (a->max_context_len + kV2PartitionTokens - 1) / kV2PartitionTokens;
+  const int64_t rows = (int64_t)a->num_seqs * a->num_heads * np;
+  return align256(rows * a->head_size * dtype_size(a->query_dtype)) + 2 * align256(rows * 4);
+}
+
+B200_API int b200_paged_attention_v2_static_scratch(const b200_paged_attn_args_t* a, b200_stream_t stream) {
+  int st = check_common(a);
+  if (st != B200_OK || a->num_seqs == 0) return st;
+  if (a->max_context_len <= 0) return B200_ERR_ARG;
+  const int64_t need = b200_paged_attention_v2_static_scratch_bytes(a);
+  if (need > (int64_t)B200_V2_STATIC_SCRATCH_BYTES) return B200_ERR_SCRATCH_LIMIT;
+  unsigned char* base = nullptr;
+  {
+    DeviceGuard guard;  // the symbol's address is per device: resolve it with the call's device current
+    B200_CUDA_TRY(guard.set(a->device));
+    st = static_scratch_base(&base);
+    if (st != B200_OK) return st;
+  }
+  // Nothing in the scratch has to start at zero: the attention kernel writes every partial the reduce kernel reads
+  // (partitions past a sequence's context are never read), so the previous call's contents are simply overwritten.
+  const int64_t np = (a->max_context_len + kV2PartitionTokens - 1) / kV2PartitionTokens;
+  const int64_t rows = (int64_t)a->num_seqs * a->num_heads * np;
+  b200_paged_attn_args_t v2 = *a;
+  v2.tmp_out = base;
+  v2.exp_sums = reinterpret_cast<float*>(base + align256(rows * a->head_size * dtype_size(a->query_dtype)));
+  v2.max_logits = v2.exp_sums + align256(rows * 4) / 4;
+  v2.max_num_partitions = (int32_t)np;
+  return b200_paged_attention_v2(&v2, stream);
 }
 
 }  // extern "C"
