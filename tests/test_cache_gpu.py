@@ -125,6 +125,42 @@ def test_reshape_and_cache_large_prefill_32_token_tiles(cache_ops, kv_cache_fact
 
 
 @pytest.mark.parametrize("kv_cache_dtype", ["auto", "fp8_e5m2"])
+@pytest.mark.parametrize("dtype,head_size", [(torch.bfloat16, 128), (torch.float, 128), (torch.half, 64), (torch.half, 80)])
+@pytest.mark.parametrize("layout", ["block_aligned", "shifted", "shuffled_blocks_padding"])
+def test_reshape_and_cache_streamed_prefill(cache_ops, kv_cache_factory, layout, dtype, head_size, kv_cache_dtype):
+    """Calls with several (token tile, head) items per resident CTA take the streamed kernel (cp.async ring,
+    csrc/cache_ops.cu reshape_and_cache_stream_kernel; 32-token tiles, 16 for fp32): 20007 tokens x 8 heads, a ragged
+    last tile, slots that start on a block boundary (vector V path), that start mid-block (element-wise V path), and
+    whole blocks in shuffled order with padding tokens in between.  Bit-exact against the oracle and the reference."""
+    from oracle import paged_kv_oracle as O
+    _seed(9)
+    N, H, bs = 20007, 8, 16
+    nblk = (N + bs - 1) // bs
+    NB = nblk + 9
+    key, value, kc, vc, _ = _rc_inputs(N, H, head_size, bs, NB, dtype, kv_cache_dtype, kv_cache_factory,
+                                       contiguous_slots=True)
+    if layout == "block_aligned":
+        slots = torch.arange(N) + 3 * bs
+    elif layout == "shifted":
+        slots = torch.arange(N) + 3 * bs + 5
+    else:
+        blocks = torch.randperm(NB)[:nblk]
+        slots = (blocks[:, None] * bs + torch.arange(bs)[None, :]).reshape(-1)[:N].clone()
+        slots[torch.randperm(N)[:200]] = -1
+        slots[64:96] = -1   # a whole tile of padding
+    slots = slots.to(torch.long).cuda()
+    kc_o, vc_o = kc.cpu().clone(), vc.cpu().clone()
+    kc_r, vc_r = kc.clone(), vc.clone()
+    cache_ops.reshape_and_cache(key, value, kc, vc, slots, kv_cache_dtype)
+    O.reshape_and_cache(key.cpu(), value.cpu(), kc_o, vc_o, slots.cpu(), kv_cache_dtype)
+    assert _same(kc, kc_o) and _same(vc, vc_o)
+    ref = load_ref_cuda()
+    if ref is not None:
+        ref.cache_ops.reshape_and_cache(key, value, kc_r, vc_r, slots, kv_cache_dtype)
+        assert _same(kc, kc_r) and _same(vc, vc_r)
+
+
+@pytest.mark.parametrize("kv_cache_dtype", ["auto", "fp8_e5m2"])
 @pytest.mark.parametrize("dtype", DTYPES)
 @pytest.mark.parametrize("block_size", BLOCK_SIZES)
 @pytest.mark.parametrize("max_prompt_len", [64, 77])

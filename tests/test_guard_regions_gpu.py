@@ -41,7 +41,8 @@ def _ok(a, b, atol=1e-3):
     return torch.allclose(a.float(), b.float(), atol=atol, rtol=1e-3)
 
 
-@pytest.mark.parametrize("num_tokens,contiguous", [(37, False), (700, True), (8200, True), (4099, False)])
+@pytest.mark.parametrize("num_tokens,contiguous", [(37, False), (700, True), (8200, True), (4099, False),
+                                                   (16400, True), (12001, False)])  # the last two: streamed kernel
 @pytest.mark.parametrize("kv", ["auto", "fp8_e5m2"])
 def test_reshape_and_cache_writes_stay_inside_the_caches(num_tokens, contiguous, kv):
     from oracle import paged_kv_oracle as O

@@ -300,6 +300,196 @@ __global__ void __launch_bounds__(256) reshape_and_cache_tile_kernel(
   }
 }
 
+// Prefill-sized calls with 16-byte aligned rows, streamed: the tile kernel above is one (token tile, head) per CTA --
+// load, barrier, store, exit -- and ncu shows what that costs (r05: 69 % of the warps resident, every CTA's loads
+// exposed once).  Here a resident grid walks the (token tile, head) items with a ring of STAGES shared-memory stages
+// filled by cp.async: the loads of items i+1 .. i+STAGES-1 are in flight while item i is converted and stored, one
+// __syncthreads per item.  Same stores, same bits as the tile kernel's vector path.
+
+__device__ __forceinline__ void rc_cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc)
+               : "memory");
+}
+__device__ __forceinline__ void rc_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void rc_cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <typename T, typename CT, bool FP8, int X, int TOK, int STAGES>
+__global__ void __launch_bounds__(256) reshape_and_cache_stream_kernel(
+    const T* __restrict__ key, const T* __restrict__ value, CT* __restrict__ key_cache,
+    CT* __restrict__ value_cache, const int64_t* __restrict__ slot_mapping, int64_t key_stride,
+    int64_t value_stride, int num_tokens, int num_heads, int head_size, int block_size,
+    int64_t num_blocks, int num_tiles) {
+  static_assert(TOK == 16 || TOK == 32, "the slot decode runs on one warp");
+  constexpr int PER = 16 / (int)sizeof(T);
+  constexpr int VPE = 16 / (int)sizeof(CT);  // cache elements per 16-byte vector
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int pitch = head_size + PER;  // elements; rows stay 16-byte aligned
+  const int stage_elems = 2 * TOK * pitch;  // V tile, then K tile
+  static_assert(STAGES == 2 || STAGES == 3, "ring depth");
+  __shared__ int64_t s_base[STAGES][TOK];  // element offset of (blk, h, 0, 0) or -1 = skip
+  __shared__ int s_off[STAGES][TOK];
+  __shared__ int s_fast[STAGES];
+
+  // items = (token tile, head), heads fastest: CTAs that run together read one contiguous span of each source row
+  const int vpr = head_size / PER;  // 16-byte vectors per source row
+  const int G = min(block_size, TOK);
+  const int64_t head_elems = (int64_t)head_size * block_size;
+  const bool v_vec = (G % VPE) == 0 && (block_size % VPE) == 0 && (TOK % G) == 0;
+
+  // cp.async of one item's V and K tiles.  256 threads cover 256 / vpr rows per pass when vpr divides 256.
+  const bool even = (256 % vpr) == 0;
+  const int my_t = even ? threadIdx.x / vpr : 0, my_c = even ? threadIdx.x - my_t * vpr : 0, rows_per_pass = even ? 256 / vpr : 0;
+  auto issue = [&](int tile, int h, int stage) {
+    const int t0 = tile * TOK;
+    const int nt = min(TOK, num_tokens - t0);
+    T* vt = reinterpret_cast<T*>(smem_raw) + (size_t)stage * stage_elems;
+    T* kt = vt + TOK * pitch;
+    const T* vsrc = value + (int64_t)t0 * value_stride + h * head_size;
+    const T* ksrc = key + (int64_t)t0 * key_stride + h * head_size;
+    if (even) {
+      for (int t = my_t; t < nt; t += rows_per_pass) {
+        rc_cp_async16(vt + t * pitch + my_c * PER, vsrc + (int64_t)t * value_stride + my_c * PER);
+        rc_cp_async16(kt + t * pitch + my_c * PER, ksrc + (int64_t)t * key_stride + my_c * PER);
+      }
+    } else {
+      for (int v = threadIdx.x; v < nt * vpr; v += blockDim.x) {
+        const int t = v / vpr, c = v - t * vpr;
+        rc_cp_async16(vt + t * pitch + c * PER, vsrc + (int64_t)t * value_stride + c * PER);
+        rc_cp_async16(kt + t * pitch + c * PER, ksrc + (int64_t)t * key_stride + c * PER);
+      }
+    }
+  };
+  // Slots (first warp).  The slot of lane t is LOADED one iteration before it is decoded, so the global-memory round
+  // trip hides behind an item's stores instead of holding the first warp -- and with it the CTA's next barrier -- up.
+  auto load_slot = [&](int tile) -> int64_t {
+    const int t0 = tile * TOK;
+    return (int)threadIdx.x < min(TOK, num_tokens - t0) ? slot_mapping[t0 + threadIdx.x] : -1;
+  };
+  auto decode_slot = [&](int tile, int h, int stage, int64_t slot) {
+    const int nt = min(TOK, num_tokens - tile * TOK);
+    const int t = threadIdx.x;
+    int64_t base = -1;
+    int off = 0;
+    if (slot >= 0) {
+      int64_t blk;
+      if ((slot >> 31) == 0) blk = (uint32_t)slot / (uint32_t)block_size;  // the usual case without a 64-bit division
+      else blk = slot / block_size;
+      off = static_cast<int>(slot - blk * block_size);
+      if (blk < num_blocks) base = (blk * num_heads + h) * head_elems;
+    }
+    if (t < TOK) {
+      s_base[stage][t] = base;
+      s_off[stage][t] = off;
+    }
+    const int lead = t & ~(G - 1);  // first token of this token's aligned group of G (G is a power of two here)
+    const int64_t lbase = __shfl_sync(0xffffffffu, base, lead & 31);
+    const int loff = __shfl_sync(0xffffffffu, off, lead & 31);
+    const bool ok = t >= TOK || (nt == TOK && base >= 0 && base == lbase && off == loff + (t - lead) && (loff & (G - 1)) == 0);
+    const bool all_ok = __all_sync(0xffffffffu, ok);
+    if (t == 0) s_fast[stage] = all_ok && v_vec;
+  };
+
+  // Items are walked with (tile, head) cursors advanced by the grid stride -- no division per item.
+  struct Cursor {
+    int tile, h;
+  };
+  const int step_t = (int)(gridDim.x / (unsigned)num_heads), step_h = (int)(gridDim.x % (unsigned)num_heads);
+  auto advance = [&](Cursor& c) {
+    c.tile += step_t;
+    c.h += step_h;
+    if (c.h >= num_heads) {
+      c.h -= num_heads;
+      ++c.tile;
+    }
+  };
+  const bool slot_warp = threadIdx.x < 32;
+  const int vg0 = threadIdx.x / head_size, vd0 = threadIdx.x - vg0 * head_size;
+  Cursor cur{(int)(blockIdx.x / (unsigned)num_heads), (int)(blockIdx.x % (unsigned)num_heads)};
+  Cursor nxt = cur;  // the item whose copies are issued next
+#pragma unroll
+  for (int s = 0; s < STAGES - 1; ++s) {
+    if (nxt.tile < num_tiles) {
+      issue(nxt.tile, nxt.h, s);
+      if (slot_warp) decode_slot(nxt.tile, nxt.h, s, load_slot(nxt.tile));
+    }
+    rc_cp_async_commit();  // one group per stage, empty or not: the wait below counts groups
+    advance(nxt);
+  }
+  Cursor pf = nxt;       // the item whose slots are loaded next: one ahead of nxt
+  int64_t slot_pf = -1;  // slots of item nxt
+  if (slot_warp && nxt.tile < num_tiles) slot_pf = load_slot(nxt.tile);
+  advance(pf);
+  int stage = 0;
+  for (; cur.tile < num_tiles; advance(cur)) {
+    rc_cp_async_wait<STAGES - 2>();  // this thread's copies of the current item have landed
+    __syncthreads();                 // everybody's have, and everybody is done with the stage refilled next
+    {
+      const int ns = stage == 0 ? STAGES - 1 : stage - 1;
+      if (nxt.tile < num_tiles) {
+        issue(nxt.tile, nxt.h, ns);
+        if (slot_warp) decode_slot(nxt.tile, nxt.h, ns, slot_pf);
+      }
+      rc_cp_async_commit();
+      if (slot_warp) slot_pf = pf.tile < num_tiles ? load_slot(pf.tile) : -1;
+      advance(nxt);
+      advance(pf);
+    }
+    const int tile = cur.tile;
+    const int nt = min(TOK, num_tokens - tile * TOK);
+    const T* vt = reinterpret_cast<const T*>(smem_raw) + (size_t)stage * stage_elems;
+    const T* kt = vt + TOK * pitch;
+    // ---- K: one 16-byte cache vector per (token, chunk), token-fastest ----
+    const int chunks = head_size / X;
+    for (int v = threadIdx.x; v < nt * chunks; v += blockDim.x) {
+      const int c = nt == TOK ? v / TOK : v / nt, t = v - c * nt;
+      const int64_t base = s_base[stage][t];
+      if (base < 0) continue;
+      alignas(16) T src[X];
+#pragma unroll
+      for (int i = 0; i < X / PER; ++i)
+        *reinterpret_cast<uint4*>(src + i * PER) = *reinterpret_cast<const uint4*>(kt + t * pitch + c * X + i * PER);
+      alignas(16) CT tmp[X];
+      cache_cvt_vec<T, CT, FP8, X>(src, tmp);
+      *reinterpret_cast<uint4*>(key_cache + base + ((int64_t)c * block_size + s_off[stage][t]) * X) =
+          *reinterpret_cast<const uint4*>(tmp);
+    }
+    // ---- V: a group's row is whole 16-byte vectors; consecutive lanes write consecutive rows ----
+    if (s_fast[stage]) {
+      const int ngroups = TOK / G;
+      for (int i = threadIdx.x, pass = 0; i < head_size * ngroups; i += blockDim.x, ++pass) {
+        int g = vg0, d = vd0;  // first pass: computed once per kernel
+        if (pass != 0) {
+          g = i / head_size;
+          d = i - g * head_size;
+        }
+        const int tl = g * G;
+        CT* row = value_cache + s_base[stage][tl] + (int64_t)d * block_size + s_off[stage][tl];
+        const T* col = vt + tl * pitch + d;
+#pragma unroll
+        for (int w = 0; w < TOK / VPE; ++w) {
+          if (w * VPE < G) {
+            alignas(16) T line[VPE];
+#pragma unroll
+            for (int e = 0; e < VPE; ++e) line[e] = col[(w * VPE + e) * pitch];
+            alignas(16) CT tmp[VPE];
+            cache_cvt_vec<T, CT, FP8, VPE>(line, tmp);
+            *reinterpret_cast<uint4*>(row + w * VPE) = *reinterpret_cast<const uint4*>(tmp);
+          }
+        }
+      }
+    } else {
+      for (int i = threadIdx.x; i < nt * head_size; i += blockDim.x) {
+        const int d = i / nt, t = i - d * nt;
+        if (s_base[stage][t] < 0) continue;
+        value_cache[s_base[stage][t] + (int64_t)d * block_size + s_off[stage][t]] = cache_cvt<T, CT, FP8>(vt[t * pitch + d]);
+      }
+    }
+    stage = stage + 1 == STAGES ? 0 : stage + 1;
+  }
+  rc_cp_async_wait<0>();
+}
+
 template <typename T, typename CT, bool FP8>
 static int launch_reshape_and_cache(const void* key, const void* value, void* key_cache,
                                     void* value_cache, const int64_t* slot_mapping, int num_tokens,
@@ -337,6 +527,36 @@ static int launch_reshape_and_cache(const void* key, const void* value, void* ke
     // and while 32-token tiles still give every SM a few waves of CTAs (measured: C4 prefill +20 %, C5 -6 %)
     const bool many = (long long)((num_tokens + 31) / 32) * num_heads >= 4ll * 8 * num_sms(-1);
     const int tok = (tok_env == 32 && many && (ksmem ? 2 : 1) * 32 * row <= 48 * 1024) ? 32 : 16;
+    // streamed variant: vector path only, and only where V rows of a group are whole 16-byte vectors
+    static const bool no_stream = getenv("B200_RC_NO_STREAM") != nullptr;  // A/B knob
+    constexpr int VPE = 16 / (int)sizeof(CT);
+    if (vec && !no_stream && block_size % VPE == 0) {
+      static const int stok_env = getenv("B200_RC_STREAM_TOK") ? atoi(getenv("B200_RC_STREAM_TOK")) : 32;  // tuning knobs
+      static const int stages = getenv("B200_RC_STREAM_STAGES") ? atoi(getenv("B200_RC_STREAM_STAGES")) : 3;
+      const int nst = stages == 2 ? 2 : 3;
+      const int stok = (stok_env == 32 && 3 * 2 * 32 * row <= 56 * 1024) ? 32 : 16;
+      const size_t ssmem = (size_t)nst * 2 * stok * row;
+      if (ssmem <= 100 * 1024 && stok % std::min(block_size, stok) == 0) {
+        const int stiles = (num_tokens + stok - 1) / stok;
+        const long long items = (long long)stiles * num_heads;
+        const int per_sm = (int)std::min<size_t>(8, (227 * 1024) / (ssmem + 2048));
+        const long long resident = (long long)per_sm * num_sms(-1);
+        // the ring only pays when every resident CTA walks several items; smaller calls keep one CTA per tile
+        if (items >= 4 * resident) {
+        const int grid = (int)resident;
+        auto kern = stok == 32 ? (nst == 3 ? reshape_and_cache_stream_kernel<T, CT, FP8, X, 32, 3>
+                                           : reshape_and_cache_stream_kernel<T, CT, FP8, X, 32, 2>)
+                               : (nst == 3 ? reshape_and_cache_stream_kernel<T, CT, FP8, X, 16, 3>
+                                           : reshape_and_cache_stream_kernel<T, CT, FP8, X, 16, 2>);
+        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssmem));
+        kern<<<grid, 256, ssmem, stream>>>((const T*)key, (const T*)value, (CT*)key_cache, (CT*)value_cache, slot_mapping,
+                                           key_stride, value_stride, num_tokens, num_heads, head_size, block_size,
+                                           num_blocks, stiles);
+        B200_LAUNCH_CHECK();
+        return B200_OK;
+        }
+      }
+    }
     const int tiles = (num_tokens + tok - 1) / tok;
     const int head_major = (variant & 2) && tiles <= 65535;
     dim3 grid = head_major ? dim3(num_heads, tiles) : dim3(tiles, num_heads);
