@@ -319,7 +319,7 @@ __global__ void __launch_bounds__(256) reshape_and_cache_stream_kernel(
     const T* __restrict__ key, const T* __restrict__ value, CT* __restrict__ key_cache,
     CT* __restrict__ value_cache, const int64_t* __restrict__ slot_mapping, int64_t key_stride,
     int64_t value_stride, int num_tokens, int num_heads, int head_size, int block_size,
-    int64_t num_blocks, int num_tiles) {
+    int64_t num_blocks, int num_tiles, int wide) {
   static_assert(TOK == 16 || TOK == 32, "the slot decode runs on one warp");
   constexpr int PER = 16 / (int)sizeof(T);
   constexpr int VPE = 16 / (int)sizeof(CT);  // cache elements per 16-byte vector
@@ -336,6 +336,7 @@ __global__ void __launch_bounds__(256) reshape_and_cache_stream_kernel(
   const int G = min(block_size, TOK);
   const int64_t head_elems = (int64_t)head_size * block_size;
   const bool v_vec = (G % VPE) == 0 && (block_size % VPE) == 0 && (TOK % G) == 0;
+  const bool v_wide = wide && (G % (2 * VPE)) == 0 && (block_size % (2 * VPE)) == 0;  // rows of whole 32-byte sectors
 
   // cp.async of one item's V and K tiles.  256 threads cover 256 / vpr rows per pass when vpr divides 256.
   const bool even = (256 % vpr) == 0;
@@ -466,6 +467,21 @@ __global__ void __launch_bounds__(256) reshape_and_cache_stream_kernel(
         const int tl = g * G;
         CT* row = value_cache + s_base[stage][tl] + (int64_t)d * block_size + s_off[stage][tl];
         const T* col = vt + tl * pitch + d;
+        if (v_wide) {
+          // a group's row is 32 bytes (16 two-byte tokens): one 256-bit store per lane, whole sectors only
+#pragma unroll
+          for (int w = 0; w < TOK / (2 * VPE); ++w) {
+            if (w * 2 * VPE < G) {
+              alignas(16) T line[2 * VPE];
+#pragma unroll
+              for (int e = 0; e < 2 * VPE; ++e) line[e] = col[(w * 2 * VPE + e) * pitch];
+              alignas(16) CT tmp[2 * VPE];
+              cache_cvt_vec<T, CT, FP8, 2 * VPE>(line, tmp);
+              st_v8(row + w * 2 * VPE, *reinterpret_cast<const uint4*>(tmp), *reinterpret_cast<const uint4*>(tmp + VPE));
+            }
+          }
+          continue;
+        }
 #pragma unroll
         for (int w = 0; w < TOK / VPE; ++w) {
           if (w * VPE < G) {
@@ -548,10 +564,12 @@ static int launch_reshape_and_cache(const void* key, const void* value, void* ke
                                            : reshape_and_cache_stream_kernel<T, CT, FP8, X, 32, 2>)
                                : (nst == 3 ? reshape_and_cache_stream_kernel<T, CT, FP8, X, 16, 3>
                                            : reshape_and_cache_stream_kernel<T, CT, FP8, X, 16, 2>);
+        static const bool no_wide = getenv("B200_NO_ST256") != nullptr;  // A/B knob
+        const int swide = !no_wide && reinterpret_cast<uintptr_t>(value_cache) % 32 == 0;
         B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssmem));
         kern<<<grid, 256, ssmem, stream>>>((const T*)key, (const T*)value, (CT*)key_cache, (CT*)value_cache, slot_mapping,
                                            key_stride, value_stride, num_tokens, num_heads, head_size, block_size,
-                                           num_blocks, stiles);
+                                           num_blocks, stiles, swide);
         B200_LAUNCH_CHECK();
         return B200_OK;
         }
@@ -687,7 +705,8 @@ __global__ void __launch_bounds__(256) to_fp8_kernel(const T* __restrict__ src, 
   for (int64_t i = done + tid; i < n; i += stride) dst[i] = to_e5m2<T>(src[i]);
 }
 template <typename T, bool VEC>
-__global__ void __launch_bounds__(256) from_fp8_kernel(const uint8_t* __restrict__ src, T* __restrict__ dst, int64_t n) {
+__global__ void __launch_bounds__(256) from_fp8_kernel(const uint8_t* __restrict__ src, T* __restrict__ dst, int64_t n,
+                                                       int wide) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int64_t done = 0;
@@ -706,9 +725,15 @@ __global__ void __launch_bounds__(256) from_fp8_kernel(const uint8_t* __restrict
           alignas(16) T out[16];
 #pragma unroll
           for (int e = 0; e < 16; ++e) out[e] = from_e5m2<T>(in[e]);
+          if (sizeof(T) == 2 && wide) {
+            // 16 two-byte elements = one 32-byte sector per lane, one 256-bit store: a warp writes 1 KiB in one piece
+            // (two 16-byte stores per lane left every store instruction with half-filled sectors: 0.71 of the HBM peak)
+            st_v8(dst + (g0 + u * stride) * 16, *reinterpret_cast<const uint4*>(out), *reinterpret_cast<const uint4*>(out + 8));
+          } else {
 #pragma unroll
-          for (int v = 0; v < 16 / PER; ++v)
-            st_na_v4(dst + (g0 + u * stride) * 16 + v * PER, *reinterpret_cast<const uint4*>(out + v * PER));
+            for (int v = 0; v < 16 / PER; ++v)
+              st_na_v4(dst + (g0 + u * stride) * 16 + v * PER, *reinterpret_cast<const uint4*>(out + v * PER));
+          }
         }
       }
     }
@@ -724,8 +749,10 @@ static void launch_to_fp8(const void* src, void* dst, int64_t n, int blocks, boo
 }
 template <typename T>
 static void launch_from_fp8(const void* src, void* dst, int64_t n, int blocks, bool vec, cudaStream_t stream) {
-  if (vec) from_fp8_kernel<T, true><<<blocks, 256, 0, stream>>>((const uint8_t*)src, (T*)dst, n);
-  else from_fp8_kernel<T, false><<<blocks, 256, 0, stream>>>((const uint8_t*)src, (T*)dst, n);
+  static const bool no_wide = getenv("B200_NO_ST256") != nullptr;  // A/B knob
+  const int wide = !no_wide && reinterpret_cast<uintptr_t>(dst) % 32 == 0;
+  if (vec) from_fp8_kernel<T, true><<<blocks, 256, 0, stream>>>((const uint8_t*)src, (T*)dst, n, wide);
+  else from_fp8_kernel<T, false><<<blocks, 256, 0, stream>>>((const uint8_t*)src, (T*)dst, n, wide);
 }
 
 }  // namespace b200

@@ -186,6 +186,12 @@ __device__ __forceinline__ void st_na_v4(void* p, const uint4& v) {
                : "memory");
 }
 
+// 256-bit store (sm_100: STG.E.256): one lane writes a whole 32-byte sector.  p must be 32-byte aligned.
+__device__ __forceinline__ void st_v8(void* p, const uint4& lo, const uint4& hi) {
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(lo.x), "r"(lo.y), "r"(lo.z), "r"(lo.w),
+               "r"(hi.x), "r"(hi.y), "r"(hi.z), "r"(hi.w)
+               : "memory");
+}
 // ---- element conversions ------------------------------------------------------------------
 // fp8 e5m2 is the high byte of an IEEE half, so widening is a byte permute (exact).
 __device__ __forceinline__ float2 e5m2x2_lo_to_float2(uint32_t w) {  // bytes 0,1
