@@ -11,6 +11,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <type_traits>
 
 #include "common.cuh"
 
@@ -84,6 +85,22 @@ __device__ __forceinline__ void cache_cvt_vec(const T* src, CT* dst /* 2-byte al
   } else {
 #pragma unroll
     for (int e = 0; e < N; ++e) dst[e] = src[e];
+  }
+}
+
+// The same for source elements that sit PACKED in registers (16-byte vectors read from global or shared memory): a bf16
+// pair widens with one shift and one mask, no per-element extraction.
+template <typename T, typename CT, bool FP8, int N>
+__device__ __forceinline__ void cache_cvt_vec_packed(const T* src /* 4-byte aligned */, CT* dst) {
+  if constexpr (FP8 && std::is_same<T, __nv_bfloat16>::value) {
+#pragma unroll
+    for (int e = 0; e < N; e += 2) {
+      const uint32_t w = *reinterpret_cast<const uint32_t*>(src + e);
+      *reinterpret_cast<uint16_t*>(dst + e) = (uint16_t)__nv_cvt_float2_to_fp8x2(
+          make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xffff0000u)), __NV_SATFINITE, __NV_E5M2);
+    }
+  } else {
+    cache_cvt_vec<T, CT, FP8, N>(src, dst);
   }
 }
 
@@ -451,7 +468,7 @@ __global__ void __launch_bounds__(256) reshape_and_cache_stream_kernel(
       for (int i = 0; i < X / PER; ++i)
         *reinterpret_cast<uint4*>(src + i * PER) = *reinterpret_cast<const uint4*>(kt + t * pitch + c * X + i * PER);
       alignas(16) CT tmp[X];
-      cache_cvt_vec<T, CT, FP8, X>(src, tmp);
+      cache_cvt_vec_packed<T, CT, FP8, X>(src, tmp);
       *reinterpret_cast<uint4*>(key_cache + base + ((int64_t)c * block_size + s_off[stage][t]) * X) =
           *reinterpret_cast<const uint4*>(tmp);
     }

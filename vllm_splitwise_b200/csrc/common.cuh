@@ -297,10 +297,10 @@ template <> __device__ __forceinline__ uint16_t to_e5m2_x2<__half>(__half a, __h
   return (uint16_t)__nv_cvt_halfraw2_to_fp8x2(r, __NV_SATFINITE, __NV_E5M2);
 }
 template <> __device__ __forceinline__ uint16_t to_e5m2_x2<__nv_bfloat16>(__nv_bfloat16 a, __nv_bfloat16 b) {
-  __nv_bfloat162_raw r;
-  r.x = static_cast<__nv_bfloat16_raw>(a).x;
-  r.y = static_cast<__nv_bfloat16_raw>(b).x;
-  return (uint16_t)__nv_cvt_bfloat16raw2_to_fp8x2(r, __NV_SATFINITE, __NV_E5M2);
+  // bf16 widens to fp32 exactly, and the fp32 pair converts in ONE instruction (F2FP...E5M2.F32.PACK_AB).  The packed
+  // bf16 intrinsic (__nv_cvt_bfloat16raw2_to_fp8x2) converts the halves one at a time and merges the bytes with integer
+  // ops: ~9 instructions per pair, which made the bf16 -> fp8 cache write issue-bound (r05 ncu: issue slots 72 % busy).
+  return (uint16_t)__nv_cvt_float2_to_fp8x2(make_float2(__bfloat162float(a), __bfloat162float(b)), __NV_SATFINITE, __NV_E5M2);
 }
 // e5m2 -> T following the reference's widening chain (quant_utils.cuh:23-81):
 // fp8 -> half (intrinsic); bf16 goes half -> float -> bf16; float goes half -> float.
