@@ -39,6 +39,8 @@ extern "C" int b200_context_attention_fwd(const b200_context_attn_args_t* a, b20
   p.num_heads = a->num_heads;
   p.num_kv_heads = a->num_kv_heads;
   p.row_limit = (a->max_input_len + 127) / 128 * 128;
+  static const int pair_group = getenv("B200_CTX_PAIR_GROUP") ? atoi(getenv("B200_CTX_PAIR_GROUP")) : 32;  // tuning knob (measured: profiles/r05_prefix_prefill_lpt.jsonl)
+  p.pair_group = pair_group;
 
   DeviceGuard guard;
   B200_CUDA_TRY(guard.set(a->device));

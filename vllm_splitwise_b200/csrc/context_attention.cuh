@@ -48,7 +48,28 @@ struct CtxAttnParams {
   int32_t num_heads;
   int32_t num_kv_heads;
   int32_t row_limit;  // new-token rows >= row_limit are not computed: ceil(max_input_len / 128) * 128 (the reference's grid)
+  int32_t pair_group; // (head, sequence) pairs whose row blocks are issued longest-first together (ctx_cta_coords); <= 1: one
 };
+
+// CTA -> (row block, head, sequence) for the tcgen05 kernels.  CTAs are issued with blockIdx.x fastest.  Causal work grows
+// with the row block, so a plain (row block, head, sequence) grid ends on the heavy-to-light sawtooth of its last pairs and
+// the last heavy CTA sets the tail.  Here the grid is walked in groups of `pair_group` (head, sequence) pairs: inside a
+// group the heaviest row block of EVERY pair goes first, then the next heaviest, ... (longest-first across the group), so
+// the grid ends on a whole group's lightest CTAs.  Consecutive heads stay in one group, so the query heads of a KV head
+// still run together and share its K/V in L2; groups keep the K/V live at any time to a few pairs' worth.
+__device__ __forceinline__ void ctx_cta_coords(int pair_group, int& mblk, int& head, int& seq) {
+  const int M = gridDim.x, H = gridDim.y, P = H * gridDim.z;
+  const int G = max(1, min(pair_group, P));
+  const int L = blockIdx.x + M * (blockIdx.y + H * blockIdx.z);
+  const int g = L / (M * G);
+  const int r = L - g * M * G;
+  const int Gp = min(G, P - g * G);  // the last group may be short
+  const int mr = r / Gp;
+  const int pair = g * G + (r - mr * Gp);
+  mblk = M - 1 - mr;
+  seq = pair / H;
+  head = pair - seq * H;
+}
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");

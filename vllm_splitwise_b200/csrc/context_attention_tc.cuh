@@ -259,8 +259,8 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
   Exchange* xch = reinterpret_cast<Exchange*>(reinterpret_cast<uint8_t*>(bar) + 256);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int mblk = gridDim.x - 1 - blockIdx.x;
-  const int head = blockIdx.y, seq = blockIdx.z;
+  int mblk, head, seq;
+  ctx_cta_coords(p.pair_group, mblk, head, seq);
   const int ctx_len = p.b_ctx_len[seq];
   const int q_len = p.b_seq_len[seq] - ctx_len;
   const int m0 = mblk * kBM;

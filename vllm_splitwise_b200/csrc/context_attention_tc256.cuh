@@ -187,8 +187,8 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
   Barriers256* bar = reinterpret_cast<Barriers256*>(v_s + kStgV * KV_UNITS);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int mblk = gridDim.x - 1 - blockIdx.x;
-  const int head = blockIdx.y, seq = blockIdx.z;
+  int mblk, head, seq;
+  ctx_cta_coords(p.pair_group, mblk, head, seq);
   const int ctx_len = p.b_ctx_len[seq];
   const int q_len = p.b_seq_len[seq] - ctx_len;
   const int m0 = mblk * kRows;
