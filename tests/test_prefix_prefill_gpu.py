@@ -216,10 +216,12 @@ def test_256_row_kernel_ragged_batch_alibi_block_sizes(bs):
     _check(_run(c), _oracle(c), torch.float16, f"bs {bs}")
 
 
-@pytest.mark.parametrize("env", [{"B200_CTX_TN": "64"}, {"B200_CTX_ATTN": "tc128"}], ids=["tn64", "tc128"])
+@pytest.mark.parametrize("env", [{"B200_CTX_TN": "64"}, {"B200_CTX_TN": "128"}, {"B200_CTX_ATTN": "tc128"},
+                                 {"B200_CTX_PAIR_GROUP": "1"}], ids=["tn64", "tn128", "tc128", "pair_group_1"])
 def test_other_kernel_variants_in_a_subprocess(env):
-    """The kernel choice is read once per process: the 64-token-tile variant of the 256-row kernel and the 128-row
-    kernel forced for long inputs run the boundary cases in a child process."""
+    """The kernel choice is read once per process: both tile sizes of the 256-row kernel for both head sizes (the default
+    is 64 tokens for head size 128 and 128 for head size 64), the 128-row kernel forced for long inputs, and the plain CTA
+    order run the boundary cases in a child process."""
     import subprocess
     import sys
     child = dict(os.environ, **env)

@@ -41,6 +41,9 @@ extern "C" int b200_context_attention_fwd(const b200_context_attn_args_t* a, b20
   p.row_limit = (a->max_input_len + 127) / 128 * 128;
   static const int pair_group = getenv("B200_CTX_PAIR_GROUP") ? atoi(getenv("B200_CTX_PAIR_GROUP")) : 32;  // tuning knob (measured: profiles/r05_prefix_prefill_lpt.jsonl)
   p.pair_group = pair_group;
+#ifdef B200_CTX_TRACE
+  p.trace = getenv("B200_CTX_TRACE_PTR") ? reinterpret_cast<unsigned long long*>(strtoull(getenv("B200_CTX_TRACE_PTR"), nullptr, 16)) : nullptr;
+#endif
 
   DeviceGuard guard;
   B200_CUDA_TRY(guard.set(a->device));

@@ -49,7 +49,20 @@ struct CtxAttnParams {
   int32_t num_kv_heads;
   int32_t row_limit;  // new-token rows >= row_limit are not computed: ceil(max_input_len / 128) * 128 (the reference's grid)
   int32_t pair_group; // (head, sequence) pairs whose row blocks are issued longest-first together (ctx_cta_coords); <= 1: one
+#ifdef B200_CTX_TRACE
+  unsigned long long* trace;  // development builds only (make TRACE=1): clock64 stamps of CTA (0,0,0), tools/ctx_trace.py
+#endif
 };
+#ifdef B200_CTX_TRACE
+// who: 0-7 = softmax warps (0-3 block A, 4-7 block B), 8 = MMA warp, 9 = V loader (warp 12), 10 = K loader (warp 9); tile < 32; event < 8
+#define B200_CTX_STAMP(p, who, tile, ev)                                                              \
+  do {                                                                                                \
+    if ((p).trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (tile) < 32)            \
+      (p).trace[(((who) * 32 + (tile)) * 8) + (ev)] = (unsigned long long)clock64();                 \
+  } while (0)
+#else
+#define B200_CTX_STAMP(p, who, tile, ev) do {} while (0)
+#endif
 
 // CTA -> (row block, head, sequence) for the tcgen05 kernels.  CTAs are issued with blockIdx.x fastest.  Causal work grows
 // with the row block, so a plain (row block, head, sequence) grid ends on the heavy-to-light sawtooth of its last pairs and

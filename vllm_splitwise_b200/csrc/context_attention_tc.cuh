@@ -197,17 +197,35 @@ __device__ __forceinline__ void load_rows(uint4* tile, const MT* src, int64_t ro
   }
 }
 
+// The physical number of a cached-prefix tile's c-th block, held by lane c (0 in the other lanes and past the context).
+// Loaded separately from the copies so that a loader can fetch it BEFORE it waits for its stage to drain.
+template <int BS, int TN>
+__device__ __forceinline__ int ctx_tile_blocks(const int32_t* bt, int toks_valid, int lane) {
+  return (lane < TN / BS && lane * BS < toks_valid) ? bt[lane] : 0;
+}
+
+// (Tried, r05: cached K by bulk copies -- one cp.async.bulk of BS * 16 bytes per (block, d-octet), completing k_full by
+// itself.  128 copies of 256 bytes per tile took the two loader warps ~4 000 cycles to ISSUE, 1 000 more than the 2 048
+// 16-byte cp.async they replace, and the 2k+2k shape went from 712 to 665 TFLOP/s.  Removed.)
+
 // cached K: chunks [D/8][BS][8] of the blocks bt[0..] -> [d-octet][token] granules
+template <typename MT, int BS, int NT, int TN, int D>
+__device__ __forceinline__ void load_k_ctx_bn(uint4* tile, const MT* kc, int64_t block_stride, int my_bn, int toks_valid,
+                                              int lt);
 template <typename MT, int BS, int NT, int TN = kBN, int D = kD>  // TN = tokens of the tile
 __device__ __forceinline__ void load_k_ctx(uint4* tile, const MT* kc, int64_t block_stride, const int32_t* bt,
                                            int toks_valid, int lt, int lane) {
   constexpr int JW = NT / BS;  // d-octets covered per pass
   static_assert(JW <= D / 8 && (D / 8) % JW == 0, "loader threads vs head size");
-  const int tt = lt % BS, jl = lt / BS;
   // lane c holds the physical number of the tile's c-th block; the loop gets it by shuffle, so no load sits in
   // front of a cp.async
-  int my_bn = 0;
-  if (lane < TN / BS && lane * BS < toks_valid) my_bn = bt[lane];
+  load_k_ctx_bn<MT, BS, NT, TN, D>(tile, kc, block_stride, ctx_tile_blocks<BS, TN>(bt, toks_valid, lane), toks_valid, lt);
+}
+template <typename MT, int BS, int NT, int TN, int D>
+__device__ __forceinline__ void load_k_ctx_bn(uint4* tile, const MT* kc, int64_t block_stride, int my_bn, int toks_valid,
+                                              int lt) {
+  constexpr int JW = NT / BS;  // d-octets covered per pass
+  const int tt = lt % BS, jl = lt / BS;
 #pragma unroll
   for (int c = 0; c < TN / BS; ++c) {
     const int64_t bn = __shfl_sync(0xffffffffu, my_bn, c);
@@ -221,15 +239,23 @@ __device__ __forceinline__ void load_k_ctx(uint4* tile, const MT* kc, int64_t bl
 }
 
 // cached V: chunks [D][BS] -> [token-octet][d] granules; octets past the context end are zero-filled
+template <typename MT, int BS, int NT, int TN, int D>
+__device__ __forceinline__ void load_v_ctx_bn(uint4* tile, const MT* vc, int64_t block_stride, int my_bn, int toks_valid,
+                                              int lt);
 template <typename MT, int BS, int NT, int TN = kBN, int D = kD>
 __device__ __forceinline__ void load_v_ctx(uint4* tile, const MT* vc, int64_t block_stride, const int32_t* bt,
                                            int toks_valid, int lt, int lane) {
   constexpr int HG = BS / 8;   // token octets per block
   constexpr int DW = NT / HG;  // d rows covered per pass
   static_assert(DW <= D && D % DW == 0, "loader threads vs head size");
+  load_v_ctx_bn<MT, BS, NT, TN, D>(tile, vc, block_stride, ctx_tile_blocks<BS, TN>(bt, toks_valid, lane), toks_valid, lt);
+}
+template <typename MT, int BS, int NT, int TN, int D>
+__device__ __forceinline__ void load_v_ctx_bn(uint4* tile, const MT* vc, int64_t block_stride, int my_bn, int toks_valid,
+                                              int lt) {
+  constexpr int HG = BS / 8;   // token octets per block
+  constexpr int DW = NT / HG;  // d rows covered per pass
   const int hh = lt % HG, dl = lt / HG;
-  int my_bn = 0;
-  if (lane < TN / BS && lane * BS < toks_valid) my_bn = bt[lane];
 #pragma unroll
   for (int c = 0; c < TN / BS; ++c) {
     const int64_t bn = __shfl_sync(0xffffffffu, my_bn, c);

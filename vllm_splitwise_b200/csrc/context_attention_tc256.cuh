@@ -32,7 +32,7 @@ constexpr int kKLoad = 64;  // K (+Q) loader threads; V loader threads: Cfg::kVL
 constexpr int kMaxStg = 4;
 // TN = KV tokens per tile.  TN = 128: one S buffer per block (Q.K^T of tile i+1 follows P.V of tile i), two 32 KiB
 // stages each for K and V, 192 registers per softmax thread (128 scores).  TN = 64: two S buffers per block (Q.K^T a
-// tile ahead), four 16 KiB stages, 160 registers.  Measured (profiles/r05_prefix_prefill_tc256*.jsonl): see kDefaultTN.
+// tile ahead), four 16 KiB stages, 160 registers.  Measured: see default_tn().
 template <int TN, int D = kD>
 struct Cfg {
   static constexpr int kNSB = 128 / TN;              // S buffers per row block
@@ -83,10 +83,12 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
     const uint32_t s_addr = tmem + lane_off + X * 128 + (i % NSB) * kTN;
     mbar_wait(&bar->s_full[X][i % NSB], (i / NSB) & 1);
     tc_fence_after();
+    if ((tid & 31) == 0) B200_CTX_STAMP(p, warp, i, 0);
     float s[kTN];
 #pragma unroll
     for (int c = 0; c < kTN / 32; ++c) tmem_ld32(s_addr + 32 * c, reinterpret_cast<uint32_t*>(&s[32 * c]));
     tmem_ld_wait();
+    if ((tid & 31) == 0) B200_CTX_STAMP(p, warp, i, 1);
     // warp-uniform fast path: nothing masked, no bias -> raw maximum, scale folded into the exponent's FMA
     const bool plain = !has_alibi && __all_sync(0xffffffffu, limit >= kTN);
     float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
@@ -127,6 +129,7 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
       l_run *= alpha;
       m_used = m_new;
     }
+    if ((tid & 31) == 0) B200_CTX_STAMP(p, warp, i, 2);
     // P = 2^(score - reference) over the S columns already consumed (two elements per 32-bit column)
     float sum4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -142,9 +145,11 @@ __device__ __forceinline__ void softmax_rows(const CtxAttnParams& p, Barriers256
       tmem_st16(s_addr + 16 * c, pk);
     }
     tmem_st_wait();
+    if ((tid & 31) == 0) B200_CTX_STAMP(p, warp, i, 3);
     observe_o_upto(i - 4);
     tc_fence_before();
     mbar_arrive(&bar->p_full[X][i % NSB]);
+    if ((tid & 31) == 0) B200_CTX_STAMP(p, warp, i, 4);
     l_run += (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
   }
 
@@ -251,6 +256,7 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
         mbar_wait(&bar->q_full, 0);
         auto issue_qk = [&](int X, int i) {  // S_X[i & 1] = Q_X.K_i^T
           const int st = i % kStg;
+          if (lane == 0 && i > 0) B200_CTX_STAMP(p, 8, i - 1, 5 + 2 * X);  // P.V of tile i - 1 issued, about to wait for K tile i
           mbar_wait(&bar->k_full[st], (i / kStg) & 1);
           tc_fence_after();
           const uint64_t kd = kd0 + (uint64_t)st * kStageStep;
@@ -266,8 +272,10 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
         auto issue_pv = [&](int X, int i) {  // O_X += P_X.V_i
           const int st = i % kStgV;
           mbar_wait(&bar->v_full[st], (i / kStgV) & 1);
+          if (lane == 0) B200_CTX_STAMP(p, 8, i, 4 + 2 * X);
           mbar_wait(&bar->p_full[X][i % NSB], (i / NSB) & 1);
           tc_fence_after();
+          if (lane == 0) B200_CTX_STAMP(p, 8, i, 2 * X);
           const bool is_ctx = i < n_ctx_tiles;
           // cached V: k-step = two token octets (2 * kD granules); new V: k-step = 16 tokens (16 granules)
           const uint64_t vd = (is_ctx ? vd0_ctx : vd0_new) + (uint64_t)st * kStageStep;
@@ -290,10 +298,12 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
           if (i < n_a) {
             issue_pv(0, i);
             if (i + NSB < n_a) issue_qk(0, i + NSB);
+            if (lane == 0) B200_CTX_STAMP(p, 8, i, 1);
           }
           if (i < n_b) {
             issue_pv(1, i);
             if (i + NSB < n_b) issue_qk(1, i + NSB);
+            if (lane == 0) B200_CTX_STAMP(p, 8, i, 3);
           }
         }
       }
@@ -304,11 +314,14 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
       const MT* kc = static_cast<const MT*>(p.k_cache) + (int64_t)kvh * p.kc_hs;
       const MT* kn = static_cast<const MT*>(p.k) + start * p.k_ts + (int64_t)kvh * p.k_hs;
       const int32_t* bt = p.b_loc + (int64_t)seq * p.b_loc_stride;
-      auto issue_k = [&](int ti) {
+      // block numbers of a cached-prefix tile (lane c: the c-th block), fetched before the wait for the stage
+      auto k_blocks = [&](int ti) -> int {
+        return ti < n_ctx_tiles ? ctx_tile_blocks<BS, kTN>(bt + ti * kTN / BS, ctx_len - ti * kTN, lane) : 0;
+      };
+      auto issue_k = [&](int ti, int my_bn) {
         uint4* Ks = k_s + (ti % kStg) * KV_UNITS;
         if (ti < n_ctx_tiles) {
-          const int n0 = ti * kTN;
-          load_k_ctx<MT, BS, kKLoad, kTN, D>(Ks, kc, p.kc_bs, bt + n0 / BS, ctx_len - n0, lt, lane);
+          load_k_ctx_bn<MT, BS, kKLoad, kTN, D>(Ks, kc, p.kc_bs, my_bn, ctx_len - ti * kTN, lt);
         } else {
           const int n0 = (ti - n_ctx_tiles) * kTN;
           load_rows<MT, kKLoad, false, kTN, D>(Ks, kn + (int64_t)n0 * p.k_ts, p.k_ts, q_len - n0, lt);
@@ -320,21 +333,51 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
       cp_async_commit();
       const int pro = min(kStg, n_load);
       for (int t = 0; t < pro; ++t) {
-        issue_k(t);
+        issue_k(t, k_blocks(t));
         cp_async_commit();
       }
       cp_async_wait_upto(pro);  // Q (the oldest group) has landed
       fence_proxy_async_smem();
       mbar_arrive(&bar->q_full);
-      for (int i = 0; i < n_load; ++i) {
-        // groups younger than tile i: tiles i+1 .. min(i + kStg - 1, n_load - 1)
-        cp_async_wait_upto(min(kStg - 1, n_load - 1 - i));
+      // A tile is announced as soon as it has landed, one tile AHEAD of the refill that follows it in program order.
+      // (r05 trace, tools/ctx_trace.py: with "announce i, wait for stage i to drain, issue i + kStg, announce i + 1" the
+      // announcement of tile i + 1 -- long landed -- sat behind the wait for the MMA warp AND the ~2-3 k cycles it takes
+      // to issue the next tile's copies, and the MMA warp spent 60 % of every period waiting for exactly that.)
+      auto announce_k = [&](int t) {
         fence_proxy_async_smem();
-        mbar_arrive(&bar->k_full[i % kStg]);
-        if (i + kStg < n_load) {
-          mbar_wait(&bar->k_empty[i % kStg], (i / kStg) & 1);
-          issue_k(i + kStg);
+        mbar_arrive(&bar->k_full[t % kStg]);
+        if (tid == 9 * 32) B200_CTX_STAMP(p, 10, t, 2);
+      };
+      if (n_load > 0) {
+        cp_async_wait_upto(pro - 1);
+        announce_k(0);
+      }
+      // When the stage of the next refill has ALREADY drained (the consumer is ahead: small head sizes, short tiles) the
+      // refill goes first, so that two tiles stay in flight; otherwise the landed tile is announced before the loader
+      // blocks on the stage.  The decision is per warp (one instruction reads the barrier for all its lanes).
+      int issued = pro;  // tile groups committed so far
+      for (int i = 0; i < n_load; ++i) {
+        const bool more = i + kStg < n_load;
+        const int bn = more ? k_blocks(i + kStg) : 0;
+        auto refill = [&]() {
+          if (tid == 9 * 32) B200_CTX_STAMP(p, 10, i + kStg, 0);
+          issue_k(i + kStg, bn);
           cp_async_commit();
+          ++issued;
+          if (tid == 9 * 32) B200_CTX_STAMP(p, 10, i + kStg, 1);
+        };
+        bool refilled = false;
+        if (more && __all_sync(0xffffffffu, mbar_test(&bar->k_empty[i % kStg], (i / kStg) & 1))) {
+          refill();
+          refilled = true;
+        }
+        if (i + 1 < n_load) {
+          cp_async_wait_upto(issued - (i + 2));  // groups younger than tile i + 1
+          announce_k(i + 1);
+        }
+        if (more && !refilled) {
+          mbar_wait(&bar->k_empty[i % kStg], (i / kStg) & 1);
+          refill();
         }
       }
     } else if (warp >= 12 && warp < 12 + kVLoad / 32) {
@@ -343,37 +386,64 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
       const MT* vc = static_cast<const MT*>(p.v_cache) + (int64_t)kvh * p.vc_hs;
       const MT* vn = static_cast<const MT*>(p.v) + start * p.v_ts + (int64_t)kvh * p.v_hs;
       const int32_t* bt = p.b_loc + (int64_t)seq * p.b_loc_stride;
-      auto issue_v = [&](int ti) {
+      auto v_blocks = [&](int ti) -> int {
+        return ti < n_ctx_tiles ? ctx_tile_blocks<BS, kTN>(bt + ti * kTN / BS, ctx_len - ti * kTN, lane) : 0;
+      };
+      auto issue_v = [&](int ti, int my_bn) {
         uint4* Vs = v_s + (ti % kStgV) * KV_UNITS;
         if (ti < n_ctx_tiles) {
-          const int n0 = ti * kTN;
-          load_v_ctx<MT, BS, kVLoad, kTN, D>(Vs, vc, p.vc_bs, bt + n0 / BS, ctx_len - n0, lt, lane);
+          load_v_ctx_bn<MT, BS, kVLoad, kTN, D>(Vs, vc, p.vc_bs, my_bn, ctx_len - ti * kTN, lt);
         } else {
           const int n0 = (ti - n_ctx_tiles) * kTN;
           load_rows<MT, kVLoad, true, kTN, D>(Vs, vn + (int64_t)n0 * p.v_ts, p.v_ts, q_len - n0, lt);
         }
       };
-      for (int t = 0; t < kStgV && t < n_load; ++t) {
-        issue_v(t);
+      const int pro = min(kStgV, n_load);
+      for (int t = 0; t < pro; ++t) {
+        issue_v(t, v_blocks(t));
         cp_async_commit();
       }
-      for (int i = 0; i < n_load; ++i) {
-        cp_async_wait_upto(min(kStgV - 1, n_load - 1 - i));
-        if (i < n_ctx_tiles && i * kTN + kTN > ctx_len && ((ctx_len - i * kTN) & 7)) {
+      auto announce_v = [&](int t) {  // the copies of tile t have landed (this thread's)
+        if (t < n_ctx_tiles && t * kTN + kTN > ctx_len && ((ctx_len - t * kTN) & 7)) {
           // the token octet that straddles ctx_len: slots past the end are stale cache memory (may be NaN / Inf)
-          asm volatile("bar.sync 1, %0;" ::"n"(kVLoad) : "memory");  // every V loader's copies of tile i landed
-          const int tgb = (ctx_len - i * kTN) >> 3, rem = (ctx_len - i * kTN) & 7;
+          asm volatile("bar.sync 1, %0;" ::"n"(kVLoad) : "memory");  // every V loader's copies of tile t landed
+          const int tgb = (ctx_len - t * kTN) >> 3, rem = (ctx_len - t * kTN) & 7;
           for (int d = lt; d < D; d += kVLoad) {
-            MT* gp = reinterpret_cast<MT*>(&v_s[(i % kStgV) * KV_UNITS + tgb * D + d]);
+            MT* gp = reinterpret_cast<MT*>(&v_s[(t % kStgV) * KV_UNITS + tgb * D + d]);
             for (int x = rem; x < 8; ++x) gp[x] = MT(0.f);
           }
         }
         fence_proxy_async_smem();
-        mbar_arrive(&bar->v_full[i % kStgV]);
-        if (i + kStgV < n_load) {
-          mbar_wait(&bar->v_empty[i % kStgV], (i / kStgV) & 1);
-          issue_v(i + kStgV);
+        mbar_arrive(&bar->v_full[t % kStgV]);
+        if (tid == 12 * 32) B200_CTX_STAMP(p, 9, t, 2);
+      };
+      if (n_load > 0) {
+        cp_async_wait_upto(pro - 1);
+        announce_v(0);
+      }
+      int issued = pro;
+      for (int i = 0; i < n_load; ++i) {  // the K loader's order: refill first if the stage is free, else announce first
+        const bool more = i + kStgV < n_load;
+        const int bn = more ? v_blocks(i + kStgV) : 0;
+        auto refill = [&]() {
+          if (tid == 12 * 32) B200_CTX_STAMP(p, 9, i + kStgV, 0);
+          issue_v(i + kStgV, bn);
           cp_async_commit();
+          ++issued;
+          if (tid == 12 * 32) B200_CTX_STAMP(p, 9, i + kStgV, 1);
+        };
+        bool refilled = false;
+        if (more && __all_sync(0xffffffffu, mbar_test(&bar->v_empty[i % kStgV], (i / kStgV) & 1))) {
+          refill();
+          refilled = true;
+        }
+        if (i + 1 < n_load) {
+          cp_async_wait_upto(issued - (i + 2));
+          announce_v(i + 1);
+        }
+        if (more && !refilled) {
+          mbar_wait(&bar->v_empty[i % kStgV], (i / kStgV) & 1);
+          refill();
         }
       }
     }
@@ -385,9 +455,12 @@ __global__ void __launch_bounds__(kThreads256, 1) context_attn_tc256_kernel(cons
   if (warp == 8) tmem_dealloc_512(tmem);
 }
 
-// 128-token tiles measured faster than 64-token tiles once the MMA issue was made warp-uniform? -> see the r05 numbers
-// in profiles/README.md; B200_CTX_TN=64|128 overrides (A/B knob).
-constexpr int kDefaultTN = 128;
+// Tile size (B200_CTX_TN=64|128 overrides, A/B knob).  While the loaders announced a landed tile only after the next
+// refill, 128-token tiles were faster (647 vs 598 TFLOP/s); with the loaders off the critical path
+// (profiles/r05_prefix_prefill_loaders.jsonl) the look-ahead Q.K^T of the 64-token variant pays: head size 128 --
+// 783 vs 736 (2k + 2k), 597 vs 581 (4k, no prefix), 789 vs 742, 875 vs 841, 484 vs 451; head size 64 -- 481 vs 502.
+template <int D>
+constexpr int default_tn() { return D == 128 ? 64 : 128; }
 
 template <typename MT, int BS, int TN, int D>
 int launch_ctx_attn_tc256_tn(const CtxAttnParams& p, int batch, int max_input_len, cudaStream_t stream) {
@@ -408,7 +481,7 @@ int launch_ctx_attn_tc256_tn(const CtxAttnParams& p, int batch, int max_input_le
 
 template <typename MT, int BS, int D = kD>
 int launch_ctx_attn_tc256(const CtxAttnParams& p, int batch, int max_input_len, cudaStream_t stream) {
-  static const int tn = getenv("B200_CTX_TN") ? atoi(getenv("B200_CTX_TN")) : kDefaultTN;
+  static const int tn = getenv("B200_CTX_TN") ? atoi(getenv("B200_CTX_TN")) : default_tn<D>();
   if (tn == 64) return launch_ctx_attn_tc256_tn<MT, BS, 64, D>(p, batch, max_input_len, stream);
   return launch_ctx_attn_tc256_tn<MT, BS, 128, D>(p, batch, max_input_len, stream);
 }
