@@ -19,7 +19,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
 NWHO = 11
-trace = torch.zeros(NWHO * 32 * 8, dtype=torch.int64, device="cuda")
+NT = 64
+trace = torch.zeros(NWHO * NT * 8, dtype=torch.int64, device="cuda")
 os.environ["B200_CTX_TRACE_PTR"] = hex(trace.data_ptr())
 
 from prefix_prefill_bench import CASES, build  # noqa: E402
@@ -36,19 +37,19 @@ def main():
         trace.zero_()
         context_attention_fwd(q, k, v, o, kc, vc, bt, start, seq, cl, L)
         torch.cuda.synchronize()
-    t = trace.cpu().view(NWHO, 32, 8)
+    t = trace.cpu().view(NWHO, NT, 8)
     if int(t.max()) == 0:
         print("no stamps: the library was not built with TRACE=1")
         return
     t0 = int(t[t > 0].min())
-    n = max(i for i in range(32) if int(t[:, i].max()) > 0) + 1
+    n = max(i for i in range(NT) if int(t[:, i].max()) > 0) + 1
 
     def rel(w, i, e):
         return int(t[w, i, e]) - t0 if int(t[w, i, e]) else None
 
     def fmt(x):
         return f"{x:7d}" if x is not None else "      -"
-    for i in [j for j in (10, 11, 12, 21, 22, 23) if j < n - 1]:
+    for i in [j for j in (n // 4, n // 4 + 1, n // 4 + 2, 3 * n // 4 - 2, 3 * n // 4 - 1, 3 * n // 4) if 0 <= j < n - 1]:
         print(f"--- tile {i}")
         for w in range(8):
             print(f"  softmax warp {w} ({'AB'[w >> 2]}): " + " ".join(fmt(rel(w, i, e)) for e in range(5)))
@@ -66,8 +67,8 @@ def main():
     for w in range(8):
         print(f"  warp {w}: {avg(w, 0, w, 1):6.0f} {avg(w, 1, w, 2):6.0f} {avg(w, 2, w, 3):6.0f} {avg(w, 3, w, 4):6.0f} {avg(w, 4, w, 0, 1):6.0f}"
               f"   period {avg(w, 0, w, 0, 1):6.0f}")
-    lastA = [max(int(t[w, j, 4]) for w in range(4)) for j in range(32)]
-    lastB = [max(int(t[w, j, 4]) for w in range(4, 8)) for j in range(32)]
+    lastA = [max(int(t[w, j, 4]) for w in range(4)) for j in range(NT)]
+    lastB = [max(int(t[w, j, 4]) for w in range(4, 8)) for j in range(NT)]
     dA = [int(t[8, j, 0]) - lastA[j] for j in range(lo, hi) if lastA[j] and int(t[8, j, 0])]
     dB = [int(t[8, j, 2]) - lastB[j] for j in range(lo, hi) if lastB[j] and int(t[8, j, 2])]
     print(f"last warp of A announces -> MMA sees P_A: {sum(dA) / max(1, len(dA)):.0f}   B: {sum(dB) / max(1, len(dB)):.0f}")

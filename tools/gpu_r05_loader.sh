@@ -3,14 +3,13 @@
 set -uo pipefail
 OUT=gpurun_out/r05ld
 mkdir -p $OUT
-timeout 300 python -m pytest tests/test_prefix_prefill_gpu.py -q -x > $OUT/pytest.log 2>&1
+timeout 400 python -m pytest tests/test_prefix_prefill_gpu.py -q -x > $OUT/pytest.log 2>&1
 echo "pytest exit $?"; tail -2 $OUT/pytest.log | cut -c1-200
-timeout 120 python tools/prefix_prefill_bench.py > $OUT/pp.jsonl 2>&1; echo "bench exit $?"
-B200_CTX_TN=64 timeout 120 python tools/prefix_prefill_bench.py > $OUT/pp_tn64.jsonl 2>&1; echo "tn64 exit $?"
-
+timeout 120 python tools/prefix_prefill_bench.py > $OUT/pp_default.jsonl 2>&1; echo "bench exit $?"
+B200_CTX_ATTN=tc128 timeout 120 python tools/prefix_prefill_bench.py > $OUT/pp_tc128.jsonl 2>&1; echo "tc128 exit $?"
 python - <<'P'
 import json
-for f in ("pp","pp_tn64"):
+for f in ('pp_default','pp_tc128'):
     for l in open(f'gpurun_out/r05ld/{f}.jsonl'):
         try: d=json.loads(l)
         except Exception: continue

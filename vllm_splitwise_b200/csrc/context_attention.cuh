@@ -54,11 +54,11 @@ struct CtxAttnParams {
 #endif
 };
 #ifdef B200_CTX_TRACE
-// who: 0-7 = softmax warps (0-3 block A, 4-7 block B), 8 = MMA warp, 9 = V loader (warp 12), 10 = K loader (warp 9); tile < 32; event < 8
+// who: 0-7 = softmax warps (0-3 block A, 4-7 block B), 8 = MMA warp, 9 = V loader (warp 12), 10 = K loader (warp 9); tile < 64; event < 8
 #define B200_CTX_STAMP(p, who, tile, ev)                                                              \
   do {                                                                                                \
-    if ((p).trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (tile) < 32)            \
-      (p).trace[(((who) * 32 + (tile)) * 8) + (ev)] = (unsigned long long)clock64();                 \
+    if ((p).trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (tile) < 64)            \
+      (p).trace[(((who) * 64 + (tile)) * 8) + (ev)] = (unsigned long long)clock64();                 \
   } while (0)
 #else
 #define B200_CTX_STAMP(p, who, tile, ev) do {} while (0)

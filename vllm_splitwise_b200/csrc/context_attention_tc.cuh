@@ -532,14 +532,34 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       issue_k(t, t);
       cp_async_commit();
     }
-    for (int i = 0; i < n_tiles; ++i) {
-      cp_async_wait_upto(min(kStages - 1, n_tiles - 1 - i));  // tiles issued after tile i may still be in flight
+    // A landed tile is announced AHEAD of the refill that follows it in program order -- or the refill goes first when
+    // its stage has already drained -- see the loaders of context_attention_tc256.cuh (r05 trace: the announcement of a
+    // tile that had long landed sat behind the wait for the previous stage plus the issue of the next tile's copies).
+    int issued = min(kStages, n_tiles);  // tile groups committed so far
+    auto announce_k = [&](int t) {
       fence_proxy_async_smem();
-      mbar_arrive(&bar->k_full[i % kStages]);
-      if (i + kStages < n_tiles) {
+      mbar_arrive(&bar->k_full[t % kStages]);
+    };
+    cp_async_wait_upto(issued - 1);
+    announce_k(0);
+    for (int i = 0; i < n_tiles; ++i) {
+      const bool more = i + kStages < n_tiles;
+      bool refilled = false;
+      if (more && __all_sync(0xffffffffu, mbar_test(&bar->k_empty[i % kStages], (i / kStages) & 1))) {
+        issue_k(i + kStages, i % kStages);
+        cp_async_commit();
+        ++issued;
+        refilled = true;
+      }
+      if (i + 1 < n_tiles) {
+        cp_async_wait_upto(issued - (i + 2));  // groups younger than tile i + 1
+        announce_k(i + 1);
+      }
+      if (more && !refilled) {
         mbar_wait(&bar->k_empty[i % kStages], (i / kStages) & 1);
         issue_k(i + kStages, i % kStages);
         cp_async_commit();
+        ++issued;
       }
     }
    }
@@ -564,23 +584,42 @@ __global__ void __launch_bounds__(kThreads, 1) context_attn_tc_kernel(const CtxA
       issue_v(t, t);
       cp_async_commit();
     }
-    for (int i = 0; i < n_tiles; ++i) {
-      cp_async_wait_upto(min(kStages - 1, n_tiles - 1 - i));
-      if (i < n_ctx_tiles && i * kBN + kBN > ctx_len && ((ctx_len - i * kBN) & 7)) {
+    auto announce_v = [&](int t) {  // this thread's copies of tile t have landed
+      if (t < n_ctx_tiles && t * kBN + kBN > ctx_len && ((ctx_len - t * kBN) & 7)) {
         // the token octet that straddles ctx_len: slots past the end are stale cache memory (may be NaN / Inf)
-        asm volatile("bar.sync 1, %0;" ::"n"(kVLoaderThreads) : "memory");  // every V loader's copies of tile i landed
-        const int tgb = (ctx_len - i * kBN) >> 3, rem = (ctx_len - i * kBN) & 7;
+        asm volatile("bar.sync 1, %0;" ::"n"(kVLoaderThreads) : "memory");  // every V loader's copies of tile t landed
+        const int tgb = (ctx_len - t * kBN) >> 3, rem = (ctx_len - t * kBN) & 7;
         for (int d = lt; d < kD; d += kVLoaderThreads) {
-          MT* gp = reinterpret_cast<MT*>(&v_s[(i % kStages) * TILE_UNITS + tgb * kD + d]);
+          MT* gp = reinterpret_cast<MT*>(&v_s[(t % kStages) * TILE_UNITS + tgb * kD + d]);
           for (int x = rem; x < 8; ++x) gp[x] = MT(0.f);
         }
       }
       fence_proxy_async_smem();
-      mbar_arrive(&bar->v_full[i % kStages]);
-      if (i + kStages < n_tiles) {
+      mbar_arrive(&bar->v_full[t % kStages]);
+    };
+    int issued = min(kStages, n_tiles);
+    if (n_tiles > 0) {
+      cp_async_wait_upto(issued - 1);
+      announce_v(0);
+    }
+    for (int i = 0; i < n_tiles; ++i) {  // the K loader's order
+      const bool more = i + kStages < n_tiles;
+      bool refilled = false;
+      if (more && __all_sync(0xffffffffu, mbar_test(&bar->v_empty[i % kStages], (i / kStages) & 1))) {
+        issue_v(i + kStages, i % kStages);
+        cp_async_commit();
+        ++issued;
+        refilled = true;
+      }
+      if (i + 1 < n_tiles) {
+        cp_async_wait_upto(issued - (i + 2));
+        announce_v(i + 1);
+      }
+      if (more && !refilled) {
         mbar_wait(&bar->v_empty[i % kStages], (i / kStages) & 1);
         issue_v(i + kStages, i % kStages);
         cp_async_commit();
+        ++issued;
       }
     }
   }
