@@ -56,6 +56,9 @@ AttnParams base_params(const b200_paged_attn_args_t* a) {
   p.q_stride = a->q_stride;
   p.kv_block_stride = a->kv_block_stride;
   p.kv_head_stride = a->kv_head_stride;
+#ifdef B200_ATTN_TRACE
+  p.trace = getenv("B200_ATTN_TRACE_PTR") ? reinterpret_cast<unsigned long long*>(strtoull(getenv("B200_ATTN_TRACE_PTR"), nullptr, 16)) : nullptr;
+#endif
   return p;
 }
 

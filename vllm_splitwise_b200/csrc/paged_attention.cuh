@@ -64,7 +64,20 @@ struct AttnParams {
   long long q_stride;
   long long kv_block_stride;
   long long kv_head_stride;
+#ifdef B200_ATTN_TRACE
+  unsigned long long* trace;  // development builds only (make TRACE=1): clock64 stamps of CTA 0, tools/attn_trace.py
+#endif
 };
+#ifdef B200_ATTN_TRACE
+// who: consumer warp 0-3; quad (k-th work unit of the CTA) < 32; event < 8
+#define B200_ATTN_STAMP(p, who, k, ev)                                                        \
+  do {                                                                                        \
+    if ((p).trace && blockIdx.x == 0 && (k) < 32 && (threadIdx.x & 31) == 0)                  \
+      (p).trace[(((who) * 32 + (k)) * 8) + (ev)] = (unsigned long long)clock64();             \
+  } while (0)
+#else
+#define B200_ATTN_STAMP(p, who, k, ev) do {} while (0)
+#endif
 
 constexpr int kConsumerWarps = 4;
 constexpr int kConsumerThreads = kConsumerWarps * 32;
@@ -405,6 +418,7 @@ __device__ __forceinline__ void attn_quad_mode(const AttnParams& p, unsigned cha
     mbar_wait(&iq_full[qs], (k / kQuadQueue) & 1);
     const long long entry = quad_q[qs];
     if (entry < 0) break;
+    B200_ATTN_STAMP(p, warp, k, 0);
     const long long quad = entry & ((1LL << 40) - 1);
     const int rounds = (int)(entry >> 40);  // the longest of the four items, from the producer
     const long long item = 4 * quad + warp;
@@ -421,16 +435,21 @@ __device__ __forceinline__ void attn_quad_mode(const AttnParams& p, unsigned cha
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(&iq_empty[qs]);  // every warp arrives, with or without an item
+    B200_ATTN_STAMP(p, warp, k, 1);
     for (int r = 0; r < rounds; ++r) {
       unsigned char* ks = stages + (size_t)slot * Impl::kStageBytes;
       mbar_wait(&full_bar[slot], parity);
+      if (r == 0) B200_ATTN_STAMP(p, warp, k, 2);
+      if (r == 1) B200_ATTN_STAMP(p, warp, k, 5);
       if (r < my_n) Impl::block(st, p, it, ks, ks + Impl::kKBytes, it.b0 + r, nullptr, warp, lane);
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty_bar[slot]);
       slot += NW;
       if (slot >= nst) { slot -= nst; parity ^= 1u; }
     }
+    B200_ATTN_STAMP(p, warp, k, 3);
     if (my_n > 0) Impl::store_partial(st, p, it, lane);
+    B200_ATTN_STAMP(p, warp, k, 4);
   }
 }
 
