@@ -217,3 +217,55 @@ def test_graph_replay_overlapping_eager_calls(ops):
         assert ok, f"graph replay {it}: max err {err}"
         ok, err = _close(outs_b[it], ref_b)
         assert ok, f"eager call {it}: max err {err}"
+
+
+def _quad_ragged_case(kv_cache_dtype, block_size, use_alibi, seed):
+    """Enough (sequence, head tile, partition) items for the v2 quad mode (>= 1.5 quads per resident CTA), with context
+    lengths on and around the 512-token partition edges, odd and even partition counts, and one-token contexts."""
+    rng = random.Random(seed)
+    edge = [1, 15, 511, 512, 513, 1023, 1024, 1025, 1535, 1536, 1537, 2047, 2048, 2049, 3071, 3072, 3073, 4095, 4096]
+    ctx = edge + [rng.randint(1, 4096) for _ in range(256 - len(edge))]
+    ctx[-1] = 4096
+    return make_attention_inputs(num_seqs=256, num_heads=(16, 2), head_size=128, block_size=block_size,
+                                 dtype=torch.bfloat16, kv_cache_dtype=kv_cache_dtype, num_blocks=4096, context_lens=ctx,
+                                 use_alibi=use_alibi, seed=seed)
+
+
+@pytest.mark.parametrize("kv_cache_dtype,block_size,use_alibi", [("auto", 16, False), ("fp8_e5m2", 16, True),
+                                                                 ("fp8_e5m2", 32, False)])
+def test_v2_quad_mode_ragged_partitions(ops, kv_cache_dtype, block_size, use_alibi):
+    """v2 signature on the tensor-core consumer, quad mode (every warp owns whole partitions): output, and the
+    partials of every partition a sequence has, against the oracle.  Run again with two partitions per warp-item
+    forced by test_v2_pair_mode_in_a_subprocess."""
+    from oracle import paged_kv_oracle as O
+    a = _quad_ragged_case(kv_cache_dtype, block_size, use_alibi, seed=21)
+    out, es, ml, tmp = run_v2(ops, a)
+    ref = oracle_attention(a)
+    atol, rtol = (FP8_ATOL, FP8_RTOL) if kv_cache_dtype == "fp8_e5m2" else (ATOL, RTOL)
+    ok, err = _close(out, ref, atol, rtol)
+    assert ok, f"out max err {err}"
+    kc, vc = dequantized(a)
+    es_o, ml_o, tmp_o = O.v2_partials(a["q"], a["hq"] // a["hkv"], kc, vc, a["bt"], a["cl"], a["scale"], a["alibi"],
+                                      es.shape[2])
+    cl = a["cl"].tolist()
+    for s in range(0, len(cl), 7):
+        n = (cl[s] + 511) // 512
+        assert torch.allclose(ml[s, :, :n].cpu(), ml_o[s, :, :n].cpu(), atol=2e-3, rtol=1e-3), f"max_logits seq {s}"
+        assert torch.allclose(es[s, :, :n].cpu(), es_o[s, :, :n].cpu(), atol=3e-3, rtol=3e-3), f"exp_sums seq {s}"
+        ok, err = _close(tmp[s, :, :n].cpu(), tmp_o[s, :, :n].cpu(), atol, rtol)
+        assert ok, f"tmp_out seq {s} max err {err}"
+
+
+def test_v2_pair_mode_in_a_subprocess():
+    """Two partitions per warp-item are only used from six doubled quads per resident CTA (full-size C4 in
+    test_vs_reference_cuda_full_gpu.py); B200_ATTN_PAIR_MIN_QUADS=0 forces them for every quad-mode call in a child
+    process, which re-runs the ragged-partition test above, the guard-region quad case and the v2 tests."""
+    import os
+    import subprocess
+    import sys
+    child = dict(os.environ, B200_ATTN_PAIR_MIN_QUADS="0")
+    here = os.path.dirname(os.path.abspath(__file__))
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", os.path.join(here, "test_attention_long_gpu.py"),
+                        os.path.join(here, "test_guard_regions_gpu.py"), "-k", "quad_mode_ragged or v2_quad"],
+                       env=child, capture_output=True, text=True, timeout=900, cwd=os.path.dirname(here))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-1000:]

@@ -60,6 +60,7 @@ struct AttnParams {
   int nconsumers;        // consumer warps that take blocks (<= kConsumerWarps)
   int q_bulk;            // 1: the query rows of an item reach the consumers through shared memory (bulk copy)
   int quad;              // 1: v2 signature on the tensor-core consumer -- every consumer warp owns a whole item
+  int parts_per_item;    // quad mode: partitions one warp walks with ONE set of query fragments (1 or 2; 0 = 1)
   long long total_items; // max_num_partitions * num_seqs * tiles_per_seq
   long long q_stride;
   long long kv_block_stride;
@@ -112,8 +113,12 @@ __device__ __forceinline__ ItemInfo decode_item(const AttnParams& p, long long i
   it.ctx = ctx_known >= 0 ? ctx_known : p.context_lens[it.seq];
   it.nblk_ctx = (it.ctx + BS - 1) / BS;
   if (p.partition_blocks > 0) {
+    // parts_per_item = 2 (quad mode): the item covers partitions 2 * idx and 2 * idx + 1; it.part names the first
+    const int ppi = p.parts_per_item > 1 ? p.parts_per_item : 1;
+    const int item_blocks = p.partition_blocks * ppi;
+    it.part *= ppi;
     it.b0 = it.part * p.partition_blocks;
-    it.nblk = max(0, min(it.nblk_ctx, it.b0 + p.partition_blocks) - it.b0);
+    it.nblk = max(0, min(it.nblk_ctx, it.b0 + item_blocks) - it.b0);
     it.nparts = (it.nblk_ctx + p.partition_blocks - 1) / p.partition_blocks;
   } else {
     it.b0 = 0;
@@ -364,7 +369,7 @@ __device__ __forceinline__ void attn_quad_mode(const AttnParams& p, unsigned cha
           const int part = (int)(ni / per_part);
           const int seq = (int)(ni - (long long)part * per_part) / p.tiles_per_seq;
           ctx_next = p.context_lens[seq];
-          const int b = part * p.partition_blocks + (lane >> 2);
+          const int b = part * p.partition_blocks * (p.parts_per_item > 1 ? p.parts_per_item : 1) + (lane >> 2);
           if (lane < G && b < p.max_num_blocks_per_seq) phys_n = p.block_tables[(long long)seq * p.max_num_blocks_per_seq + b];
         }
         stage_next = 2;
@@ -436,12 +441,23 @@ __device__ __forceinline__ void attn_quad_mode(const AttnParams& p, unsigned cha
     __syncwarp();
     if (lane == 0) mbar_arrive(&iq_empty[qs]);  // every warp arrives, with or without an item
     B200_ATTN_STAMP(p, warp, k, 1);
+    const int b_first = it.b0;
+    int part_end = p.partition_blocks;  // first round of the item's next partition
     for (int r = 0; r < rounds; ++r) {
       unsigned char* ks = stages + (size_t)slot * Impl::kStageBytes;
       mbar_wait(&full_bar[slot], parity);
       if (r == 0) B200_ATTN_STAMP(p, warp, k, 2);
       if (r == 1) B200_ATTN_STAMP(p, warp, k, 5);
-      if (r < my_n) Impl::block(st, p, it, ks, ks + Impl::kKBytes, it.b0 + r, nullptr, warp, lane);
+      if (r < my_n) {
+        if (r > 0 && r == part_end) {
+          // two partitions per item: the first one is complete -- store it, keep the query fragments, start over
+          Impl::store_partial(st, p, it, lane);
+          Impl::init(st);
+          ++it.part;
+          part_end += p.partition_blocks;
+        }
+        Impl::block(st, p, it, ks, ks + Impl::kKBytes, b_first + r, nullptr, warp, lane);
+      }
       __syncwarp();
       if (lane == 0) mbar_arrive(&empty_bar[slot]);
       slot += NW;
@@ -929,6 +945,24 @@ int launch_attn(const AttnParams& p_in, int smem_budget, int sms, cudaStream_t s
   // quads for 296 CTAs the reference benchmark shape loses 7 %, with 512 quads C3 tp=8 gains 13 %)
   p.quad = Impl::kQuad && !no_quad && p.always_partials && nwa == kConsumerWarps && p.partition_blocks > 0 &&
            (p.total_items + 3) / 4 >= grid * 3 / 2;
+  p.parts_per_item = 1;
+  if (p.quad) {
+    // Two partitions per warp-item: the per-item prologue (item decode, query fragments: ~2 100 cycles per 32-block
+    // partition, profiles/r05_attn_trace_c4_v2.txt) is paid once for both, the partials are still written per
+    // partition.  Only with at least six of the doubled quads per resident CTA -- with fewer, the tail of whole
+    // quads costs more than the prologues (measured: C4, 6.9 per CTA, 0.843 -> 0.904; ctx 32 768 at batch 16, 3.5 per
+    // CTA, 1.03 -> 1.00).
+    static const bool no_pair = getenv("B200_ATTN_NO_PAIR") != nullptr;  // A/B knob
+    static const long long pair_min =  // test knob: doubled quads per resident CTA from which pairs are used
+        getenv("B200_ATTN_PAIR_MIN_QUADS") ? atoll(getenv("B200_ATTN_PAIR_MIN_QUADS")) : 6;
+    const long long per_part = (long long)p.num_seqs * p.tiles_per_seq;
+    const long long np = p.total_items / per_part;
+    const long long pair_items = ((np + 1) / 2) * per_part;
+    if (!no_pair && np >= 2 && (pair_items + 3) / 4 >= grid * pair_min) {
+      p.parts_per_item = 2;
+      p.total_items = pair_items;
+    }
+  }
   const long long units = p.quad ? (p.total_items + 3) / 4 : p.total_items;
   if (grid > units) grid = units;
   B200_CUDA_TRY(launch_kernel(kern, dim3((unsigned)grid), dim3(kAttnThreads), (size_t)smem, stream, /*pdl=*/true, p));
