@@ -1,5 +1,5 @@
 #!/usr/bin/env bash
-# decode consumer with Q.K^T one block ahead (MmaImpl::qk / softmax_pv): parity, then the driver bench line
+# decode attention after a kernel change: the attention-side GPU tests, then the driver bench line with its extras
 set -uo pipefail
 OUT=gpurun_out/r05tp
 mkdir -p $OUT
